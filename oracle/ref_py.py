@@ -1,0 +1,157 @@
+"""ctypes binding of oracle/_ref/libref_driver.so — TEST INFRASTRUCTURE ONLY.
+
+Runs the UNMODIFIED reference (compiled by oracle/Makefile from /root/reference)
+over a batch of MPC instances. Imported only by tests/, __graft_entry__.smoke()
+and bench.py's cpu_baseline / --impl reference legs; never by the product path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "_ref", "libref_driver.so")
+
+c_int = C.c_longlong
+c_float = C.c_double
+
+
+class OSQPSettings(C.Structure):
+    """Layout of reference include/types.h:139-176 for the default desktop build
+    (EMBEDDED undefined, PROFILING defined, DLONG, double)."""
+    _fields_ = [
+        ("rho", c_float), ("sigma", c_float), ("scaling", c_int),
+        ("adaptive_rho", c_int), ("adaptive_rho_interval", c_int),
+        ("adaptive_rho_tolerance", c_float), ("adaptive_rho_fraction", c_float),
+        ("max_iter", c_int), ("eps_abs", c_float), ("eps_rel", c_float),
+        ("eps_prim_inf", c_float), ("eps_dual_inf", c_float), ("alpha", c_float),
+        ("linsys_solver", C.c_int),
+        ("delta", c_float), ("polish", c_int), ("polish_refine_iter", c_int), ("verbose", c_int),
+        ("scaled_termination", c_int), ("check_termination", c_int), ("warm_start", c_int),
+        ("time_limit", c_float),
+    ]
+
+
+def available() -> bool:
+    return os.path.exists(_LIB)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(_LIB)
+        L.refb_create.restype = C.c_void_p
+        L.refb_create.argtypes = [c_int] * 6 + [C.c_void_p] * 5 + [C.POINTER(OSQPSettings), c_int] + \
+            [C.c_void_p] * 4 + [C.c_int, C.c_int]
+        for name, args in [
+            ("refb_solve", [C.c_void_p, C.c_int]),
+            ("refb_get", [C.c_void_p] * 12),
+            ("refb_update_bounds", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
+            ("refb_partial_update_bounds", [C.c_void_p, c_int, c_int, C.c_void_p, C.c_void_p, C.c_int]),
+            ("refb_update_lin_cost", [C.c_void_p, C.c_void_p, C.c_int]),
+            ("refb_warm_start", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
+            ("refb_update_horizon", [C.c_void_p, c_int, C.c_int]),
+            ("refb_update_rho", [C.c_void_p, C.c_void_p, C.c_int]),
+            ("refb_kkt_solve", [C.c_void_p, c_int, C.c_void_p]),
+            ("refb_dims", [C.c_void_p, C.c_void_p, C.c_void_p]),
+            ("refb_free", [C.c_void_p]),
+            ("refb_default_settings", [C.POINTER(OSQPSettings)]),
+        ]:
+            getattr(L, name).argtypes = args
+        assert L.refb_sizeof_settings() == C.sizeof(OSQPSettings)
+        _lib = L
+    return _lib
+
+
+def default_settings(**kw) -> OSQPSettings:
+    s = OSQPSettings()
+    lib().refb_default_settings(C.byref(s))
+    for k, v in kw.items():
+        setattr(s, k, v)
+    return s
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class RefBatch:
+    """A batch of reference workspaces. path: 'recursive' | 'stock'."""
+
+    def __init__(self, model, N, Nmax, q, l, u, settings: OSQPSettings, path="recursive",
+                 rho=None, nthreads=None):
+        L = lib()
+        self.nthreads = nthreads or L.refb_max_threads()
+        self.model, self.N, self.Nmax = model, N, Nmax
+        mats = model.stage_matrices()
+        self._keep = mats
+        mm = np.array([t[0] for t in mats], np.int64)
+        nn = np.array([t[1] for t in mats], np.int64)
+        PP = (C.c_void_p * 7)(*[t[2].ctypes.data for t in mats])
+        II = (C.c_void_p * 7)(*[t[3].ctypes.data for t in mats])
+        XX = (C.c_void_p * 7)(*[t[4].ctypes.data for t in mats])
+        self.batch = q.shape[0]
+        self.nmax, self.mmax = q.shape[1], l.shape[1]
+        q = np.ascontiguousarray(q, np.float64); l = np.ascontiguousarray(l, np.float64)
+        u = np.ascontiguousarray(u, np.float64)
+        rho = None if rho is None else np.ascontiguousarray(rho, np.float64)
+        self.h = L.refb_create(model.nx, model.nu, model.ny, model.nt, N, Nmax, _p(mm), _p(nn),
+                               C.cast(PP, C.c_void_p), C.cast(II, C.c_void_p), C.cast(XX, C.c_void_p),
+                               C.byref(settings), self.batch, _p(q), _p(l), _p(u), _p(rho),
+                               0 if path == "recursive" else 1, self.nthreads)
+
+    def dims(self):
+        n, m = c_int(), c_int()
+        lib().refb_dims(self.h, C.byref(n), C.byref(m))
+        return n.value, m.value
+
+    def solve(self):
+        return lib().refb_solve(self.h, self.nthreads)
+
+    def get(self):
+        B = self.batch
+        out = dict(x=np.zeros((B, self.nmax)), y=np.zeros((B, self.mmax)),
+                   iter=np.zeros(B, np.int64), status=np.zeros(B, np.int64), obj=np.zeros(B),
+                   pri_res=np.zeros(B), dua_res=np.zeros(B), rho_updates=np.zeros(B, np.int64),
+                   rho_estimate=np.zeros(B), setup_time=np.zeros(B), solve_time=np.zeros(B))
+        lib().refb_get(self.h, *[_p(out[k]) for k in
+                                 ("x", "y", "iter", "status", "obj", "pri_res", "dua_res",
+                                  "rho_updates", "rho_estimate", "setup_time", "solve_time")])
+        return out
+
+    def update_bounds(self, l, u):
+        return lib().refb_update_bounds(self.h, _p(np.ascontiguousarray(l)), _p(np.ascontiguousarray(u)), self.nthreads)
+
+    def partial_update_bounds(self, start, stop, l, u):
+        return lib().refb_partial_update_bounds(self.h, start, stop, _p(np.ascontiguousarray(l)),
+                                                _p(np.ascontiguousarray(u)), self.nthreads)
+
+    def update_lin_cost(self, q):
+        return lib().refb_update_lin_cost(self.h, _p(np.ascontiguousarray(q)), self.nthreads)
+
+    def warm_start(self, x=None, y=None):
+        x = None if x is None else np.ascontiguousarray(x)
+        y = None if y is None else np.ascontiguousarray(y)
+        return lib().refb_warm_start(self.h, _p(x), _p(y), self.nthreads)
+
+    def update_horizon(self, N):
+        rc = lib().refb_update_horizon(self.h, N, self.nthreads)
+        self.N = N
+        return rc
+
+    def update_rho(self, rho):
+        return lib().refb_update_rho(self.h, _p(np.ascontiguousarray(rho, np.float64)), self.nthreads)
+
+    def kkt_solve(self, k, rhs):
+        rhs = np.ascontiguousarray(rhs, np.float64).copy()
+        lib().refb_kkt_solve(self.h, k, _p(rhs))
+        return rhs
+
+    def free(self):
+        if self.h:
+            lib().refb_free(self.h)
+            self.h = None
