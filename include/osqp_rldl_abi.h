@@ -1,0 +1,412 @@
+/*
+ * osqp_rldl_abi.h — C ABI of librldl_b200.so
+ *
+ * B200-native (sm_100a, FP64) implementation of the recursive-LDL KKT path of
+ * laperss/osqp-recursive-ldl and the OSQP ADMM iteration around it, behind the
+ * reference's own C API.  A C program written against the reference's headers
+ * (include/osqp.h, include/recursive_ldl.h, include/types.h, include/constants.h)
+ * links against librldl_b200.so unchanged: every struct below is layout-identical
+ * to the reference's default desktop build (DLONG, double, PRINTING, PROFILING,
+ * EMBEDDED undefined — reference CMakeLists.txt:50-84) and every scalar entry
+ * point keeps the reference's name, argument meaning and return convention.
+ * Each declaration cites the reference interface it replaces.
+ *
+ * Scalar entry points act as a batch of one.  The throughput path is the additive
+ * `rldl_batch_*` family at the bottom: one handle = many independent MPC QP
+ * instances sharing one stage model, resident in HBM across calls.
+ *
+ * No CPU fallback exists: every entry point that computes needs a CUDA device and
+ * returns an error (after printing why) when none is usable.
+ */
+#ifndef OSQP_RLDL_ABI_H
+#define OSQP_RLDL_ABI_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library is built with -fvisibility=hidden */
+#endif
+
+/* ---- scalar types: reference include/glob_opts.h:73-84 (DLONG on, DFLOAT off) ---- */
+typedef long long c_int;
+typedef double    c_float;
+
+/* ---- status / error codes: reference include/constants.h:18-51 ---- */
+#define OSQP_DUAL_INFEASIBLE_INACCURATE   (4)
+#define OSQP_PRIMAL_INFEASIBLE_INACCURATE (3)
+#define OSQP_SOLVED_INACCURATE            (2)
+#define OSQP_SOLVED                       (1)
+#define OSQP_MAX_ITER_REACHED             (-2)
+#define OSQP_PRIMAL_INFEASIBLE            (-3)
+#define OSQP_DUAL_INFEASIBLE              (-4)
+#define OSQP_SIGINT                       (-5)
+#define OSQP_TIME_LIMIT_REACHED           (-6)
+#define OSQP_NON_CVX                      (-7)
+#define OSQP_UNSOLVED                     (-10)
+
+enum linsys_solver_type { QDLDL_SOLVER, MKL_PARDISO_SOLVER };
+
+enum osqp_error_type {
+  OSQP_DATA_VALIDATION_ERROR = 1,
+  OSQP_SETTINGS_VALIDATION_ERROR,
+  OSQP_LINSYS_SOLVER_LOAD_ERROR,
+  OSQP_LINSYS_SOLVER_INIT_ERROR,
+  OSQP_NONCVX_ERROR,
+  OSQP_MEM_ALLOC_ERROR,
+  OSQP_WORKSPACE_NOT_INIT_ERROR,
+};
+
+/* defaults and limits: reference include/constants.h:59-114 */
+#define OSQP_INFTY   ((c_float)1e30)
+/* The reference defines OSQP_NAN as (c_float)0x7fc00000UL, i.e. the finite double
+ * 2143289344.0, not an IEEE NaN (constants.h:95). "No solution" vectors are filled
+ * with exactly that value, so we keep it. */
+#define OSQP_NAN     ((c_float)0x7fc00000UL)
+#define RHO_MIN              (1e-06)
+#define RHO_MAX              (1e06)
+#define RHO_EQ_OVER_RHO_INEQ (1e03)
+#define RHO_TOL              (1e-04)
+#define MIN_SCALING          (1e-04)
+
+/* ---- data structures: reference include/types.h ---- */
+
+/* types.h:21-29 — compressed-sparse-column matrix (nz == -1) or triplets */
+typedef struct {
+  c_int    nzmax;
+  c_int    m;
+  c_int    n;
+  c_int   *p;
+  c_int   *i;
+  c_float *x;
+  c_int    nz;
+} csc;
+
+typedef struct linsys_solver LinSysSolver; /* types.h:35, vtable at types.h:298-319 */
+typedef struct OSQP_TIMER OSQPTimer;       /* types.h:40, opaque */
+
+/* types.h:45-52 */
+typedef struct {
+  c_float  c;
+  c_float *D;
+  c_float *E;
+  c_float  cinv;
+  c_float *Dinv;
+  c_float *Einv;
+} OSQPScaling;
+
+/* types.h:57-60 */
+typedef struct {
+  c_float *x;
+  c_float *y;
+} OSQPSolution;
+
+/* types.h:66-91 */
+typedef struct {
+  c_int   iter;
+  char    status[32];
+  c_int   status_val;
+  c_int   status_polish;
+  c_float obj_val;
+  c_float pri_res;
+  c_float dua_res;
+  c_float setup_time;
+  c_float solve_time;
+  c_float update_time;
+  c_float polish_time;
+  c_float run_time;
+  c_int   rho_updates;
+  c_float rho_estimate;
+} OSQPInfo;
+
+/* types.h:99-114 (polish is out of scope; the struct is kept for layout only) */
+typedef struct {
+  csc     *Ared;
+  c_int    n_low;
+  c_int    n_upp;
+  c_int   *A_to_Alow;
+  c_int   *A_to_Aupp;
+  c_int   *Alow_to_A;
+  c_int   *Aupp_to_A;
+  c_float *x;
+  c_float *z;
+  c_float *y;
+  c_float  obj_val;
+  c_float  pri_res;
+  c_float  dua_res;
+} OSQPPolish;
+
+/* types.h:125-133 */
+typedef struct {
+  c_int    n;
+  c_int    m;
+  csc     *P;
+  csc     *A;
+  c_float *q;
+  c_float *l;
+  c_float *u;
+} OSQPData;
+
+/* types.h:139-176 */
+typedef struct {
+  c_float rho;
+  c_float sigma;
+  c_int   scaling;
+  c_int   adaptive_rho;
+  c_int   adaptive_rho_interval;
+  c_float adaptive_rho_tolerance;
+  c_float adaptive_rho_fraction;
+  c_int   max_iter;
+  c_float eps_abs;
+  c_float eps_rel;
+  c_float eps_prim_inf;
+  c_float eps_dual_inf;
+  c_float alpha;
+  enum linsys_solver_type linsys_solver;
+  c_float delta;
+  c_int   polish;
+  c_int   polish_refine_iter;
+  c_int   verbose;
+  c_int   scaled_termination;
+  c_int   check_termination;
+  c_int   warm_start;
+  c_float time_limit;
+} OSQPSettings;
+
+/* types.h:182-289.  Host mirror of one instance.  The iterate / residual vectors
+ * are refreshed from the device after every solve, so code that peeks at
+ * work->x, work->y, work->z, work->delta_x (dual-infeasibility certificate) or
+ * work->delta_y (primal-infeasibility certificate) keeps working. */
+typedef struct {
+  OSQPData     *data;
+  LinSysSolver *linsys_solver;
+  OSQPPolish   *pol;
+  c_float *rho_vec;
+  c_float *rho_inv_vec;
+  c_int   *constr_type;
+  c_float *x;
+  c_float *y;
+  c_float *z;
+  c_float *xz_tilde;
+  c_float *x_prev;
+  c_float *z_prev;
+  c_float *Ax;
+  c_float *Px;
+  c_float *Aty;
+  c_float *delta_y;
+  c_float *Atdelta_y;
+  c_float *delta_x;
+  c_float *Pdelta_x;
+  c_float *Adelta_x;
+  c_float *D_temp;
+  c_float *D_temp_A;
+  c_float *E_temp;
+  OSQPSettings *settings;
+  OSQPScaling  *scaling;
+  OSQPSolution *solution;
+  OSQPInfo     *info;
+  OSQPTimer    *timer;
+  c_int first_run;
+  c_int clear_update_time;
+  c_int rho_update_from_solve;
+  c_int summary_printed;
+} OSQPWorkspace;
+
+/* types.h:298-319 — the linear-system plug-in seam.  work->linsys_solver points
+ * at a private object whose leading members are exactly these; `solve` runs one
+ * KKT solve on the device (host vector in, host vector out), `update_rho_vec`
+ * re-runs the stage recursion. */
+struct linsys_solver {
+  enum linsys_solver_type type;
+  c_int (*solve)(LinSysSolver *self, c_float *b);
+  void  (*free)(LinSysSolver *self);
+  c_int (*update_matrices)(LinSysSolver *s, const csc *P, const csc *A);
+  c_int (*update_rho_vec)(LinSysSolver *s, const c_float *rho_vec);
+  c_int nthreads;
+};
+
+/* reference include/recursive_ldl.h:17-50.  Stage-block problem description.
+ * Q0 nu x nu, Qi (nx+nu)^2, QN nx x nx upper triangles; A0 (ny+nx) x nu,
+ * Ai (ny+nx) x (nx+nu), Aij = [0 0; -I 0], AN nt x nx.  The stage matrices are
+ * borrowed for the workspace lifetime, like in the reference.  The members from
+ * Amats on are the reference's CPU bookkeeping; this library leaves the ones it
+ * does not need NULL. */
+typedef struct {
+  OSQPData data;
+  c_int  Nmax;
+  c_int  N;
+  c_int  N0;
+  c_int  N_recursive_temp;
+  c_int  Nx;
+  c_int  Nplus;
+  c_int  nx;
+  c_int  ny;
+  c_int  nu;
+  c_int  nt;
+  c_int  nnz[2];
+  csc   *A0;
+  csc   *Ai;
+  csc   *Aij;
+  csc   *AN;
+  csc   *Q0;
+  csc   *Qi;
+  csc   *QN;
+  csc  **Amats;
+  csc  **Qmats;
+  csc  **X_even;
+  double *Ytemp;
+  csc   *Yhat;
+  csc   *Uhat;
+  csc   *Vhat;
+  csc   *Lz;
+  c_float *Dzinv;
+  c_int *Pz;
+  csc   *Ly;
+  c_float *Dyinv;
+  c_int *P0;
+} OSQPDataRLDL;
+
+/* =====================  reference include/osqp.h  ===================== */
+
+/* osqp.h:32 */
+void  osqp_set_default_settings(OSQPSettings *settings);
+/* osqp.h:58 — generic QP (no stage structure): handled as a single dense stage on
+ * the device; intended for the small problems of the reference's own tests. */
+c_int osqp_setup(OSQPWorkspace **workp, const OSQPData *data, const OSQPSettings *settings);
+/* osqp.h:78 */
+c_int osqp_solve(OSQPWorkspace *work);
+/* osqp.h:90 */
+c_int osqp_cleanup(OSQPWorkspace *work);
+/* osqp.h:114 */
+c_int osqp_update_lin_cost(OSQPWorkspace *work, const c_float *q_new);
+/* osqp.h:125 */
+c_int osqp_update_bounds(OSQPWorkspace *work, const c_float *l_new, const c_float *u_new);
+/* osqp.h:136 */
+c_int osqp_update_lower_bound(OSQPWorkspace *work, const c_float *l_new);
+/* osqp.h:146 */
+c_int osqp_update_upper_bound(OSQPWorkspace *work, const c_float *u_new);
+/* osqp.h:157 */
+c_int osqp_warm_start(OSQPWorkspace *work, const c_float *x, const c_float *y);
+/* osqp.h:168 */
+c_int osqp_warm_start_x(OSQPWorkspace *work, const c_float *x);
+/* osqp.h:178 */
+c_int osqp_warm_start_y(OSQPWorkspace *work, const c_float *y);
+/* osqp.h:200 */
+c_int osqp_update_P(OSQPWorkspace *work, const c_float *Px_new, const c_int *Px_new_idx, c_int P_new_n);
+/* osqp.h:221 */
+c_int osqp_update_A(OSQPWorkspace *work, const c_float *Ax_new, const c_int *Ax_new_idx, c_int A_new_n);
+/* osqp.h:250 */
+c_int osqp_update_P_A(OSQPWorkspace *work, const c_float *Px_new, const c_int *Px_new_idx, c_int P_new_n,
+                      const c_float *Ax_new, const c_int *Ax_new_idx, c_int A_new_n);
+/* osqp.h:264 */
+c_int osqp_update_rho(OSQPWorkspace *work, c_float rho_new);
+/* osqp.h:284-419 — settings setters */
+c_int osqp_update_max_iter(OSQPWorkspace *work, c_int max_iter_new);
+c_int osqp_update_eps_abs(OSQPWorkspace *work, c_float eps_abs_new);
+c_int osqp_update_eps_rel(OSQPWorkspace *work, c_float eps_rel_new);
+c_int osqp_update_eps_prim_inf(OSQPWorkspace *work, c_float eps_prim_inf_new);
+c_int osqp_update_eps_dual_inf(OSQPWorkspace *work, c_float eps_dual_inf_new);
+c_int osqp_update_alpha(OSQPWorkspace *work, c_float alpha_new);
+c_int osqp_update_warm_start(OSQPWorkspace *work, c_int warm_start_new);
+c_int osqp_update_scaled_termination(OSQPWorkspace *work, c_int scaled_termination_new);
+c_int osqp_update_check_termination(OSQPWorkspace *work, c_int check_termination_new);
+c_int osqp_update_delta(OSQPWorkspace *work, c_float delta_new);
+c_int osqp_update_polish(OSQPWorkspace *work, c_int polish_new);
+c_int osqp_update_polish_refine_iter(OSQPWorkspace *work, c_int polish_refine_iter_new);
+c_int osqp_update_verbose(OSQPWorkspace *work, c_int verbose_new);
+c_int osqp_update_time_limit(OSQPWorkspace *work, c_float time_limit_new);
+
+/* =====================  reference include/recursive_ldl.h:52-74  ===================== */
+
+/* recursive_ldl.h:66 (src/recursive_ldl.c:2018) — data->data.{n,m,q,l,u} sized for Nmax */
+c_int osqp_setup_recursive(OSQPWorkspace **workp, OSQPDataRLDL *data, const OSQPSettings *settings,
+                           c_int Nmax, c_int N, c_int nx, c_int nu, c_int ny, c_int nt);
+/* recursive_ldl.h:64 (src/recursive_ldl.c:2867) */
+c_int osqp_solve_recursive(OSQPWorkspace *work);
+/* recursive_ldl.h:60 (src/recursive_ldl.c:1973) — change the horizon to N, re-running
+ * only the tail of the stage recursion */
+c_int osqp_update_recursive(OSQPWorkspace *work, OSQPDataRLDL *data_rldl, c_int N);
+/* recursive_ldl.h:67 (src/recursive_ldl.c:2359) — head of N stages + tail of Nplus stages */
+c_int osqp_setup_combine_recursive(OSQPWorkspace **workp, OSQPDataRLDL *data, const OSQPSettings *settings,
+                                   c_int Nmax, c_int N, c_int Nplus, c_int nx, c_int nu, c_int ny, c_int nt);
+/* recursive_ldl.h:65 (src/recursive_ldl.c:2862) */
+c_int osqp_solve_combine_recursive(OSQPWorkspace *work);
+/* recursive_ldl.h:62 (src/recursive_ldl.c:2761) — grow/shrink the tail by deltaN stages */
+c_int osqp_update_Z_horizon(OSQPWorkspace *work, OSQPDataRLDL *data_rldl, c_int deltaN);
+/* recursive_ldl.h:61 (src/recursive_ldl.c:2757) — empty body in the reference; kept as a no-op */
+c_int osqp_update_X_horizon(OSQPWorkspace *work, OSQPDataRLDL *data_rldl, c_int deltaN);
+/* recursive_ldl.h:68 (src/recursive_ldl.c:2319) — no-op in the reference; kept as a no-op */
+c_int osqp_allocate_combine_recursive(OSQPWorkspace **workp, OSQPDataRLDL *data, const OSQPSettings *settings,
+                                      c_int Nmax, c_int nx, c_int nu, c_int ny, c_int nt);
+/* recursive_ldl.h:73 (src/recursive_ldl.c:119) — overwrite l,u on rows [start,stop) */
+c_int osqp_partial_update_bounds(OSQPWorkspace *work, c_int start, c_int stop,
+                                 const c_float *l_new, const c_float *u_new);
+/* recursive_ldl.h:78 (src/recursive_ldl.c:1340) — KKT dimensions and number of stored
+ * factor entries (here: doubles of the dense stage-block factor) */
+void  get_L_dimensions(OSQPWorkspace *work, c_int *n, c_int *m, c_int *nnz);
+/* recursive_ldl.h:52 (src/recursive_ldl.c:15) */
+void  cleanup_rldl(OSQPDataRLDL *data);
+
+/* =====================  additive batch API (new)  ===================== */
+/* One handle = `batch` independent QP instances that share the stage model in
+ * `model` (dims + Q0,Qi,QN,A0,Ai,Aij,AN) and differ in q, l, u (and optionally
+ * rho).  All instance data and the per-instance stage factors live in HBM for the
+ * lifetime of the handle; host arrays are row-major [batch][nmax] / [batch][mmax]
+ * with nmax = Nmax*(nx+nu), mmax = Nmax*(nx+ny)+nt, exactly the per-instance
+ * vectors the scalar API takes, one row per instance.  Functions return 0 on
+ * success and an osqp_error_type (or 1, like the reference's update calls) on
+ * invalid input.  Every function acts on the CUDA device that was current when
+ * the handle was created. */
+typedef struct RLDLBatch RLDLBatch;
+
+c_int rldl_batch_setup(RLDLBatch **out, const OSQPDataRLDL *model, const OSQPSettings *settings,
+                       c_int Nmax, c_int N, c_int nx, c_int nu, c_int ny, c_int nt, c_int batch,
+                       const c_float *q, const c_float *l, const c_float *u,
+                       const c_float *rho /* per-instance initial rho, or NULL */);
+/* batched osqp_solve_recursive: per-instance ADMM with on-device termination,
+ * infeasibility detection and adaptive-rho refactorisation */
+c_int rldl_batch_solve(RLDLBatch *b);
+/* batched osqp_update_bounds / osqp_partial_update_bounds / osqp_update_lin_cost */
+c_int rldl_batch_update_bounds(RLDLBatch *b, const c_float *l, const c_float *u);
+c_int rldl_batch_partial_update_bounds(RLDLBatch *b, c_int start, c_int stop,
+                                       const c_float *l /* [batch][stop-start] */,
+                                       const c_float *u);
+c_int rldl_batch_update_lin_cost(RLDLBatch *b, const c_float *q);
+/* batched osqp_warm_start (x or y may be NULL: osqp_warm_start_y / _x) */
+c_int rldl_batch_warm_start(RLDLBatch *b, const c_float *x, const c_float *y);
+/* batched osqp_update_recursive */
+c_int rldl_batch_update_horizon(RLDLBatch *b, c_int N);
+/* batched osqp_update_rho (per-instance value) */
+c_int rldl_batch_update_rho(RLDLBatch *b, const c_float *rho);
+/* re-run the full stage recursion (what osqp_setup_recursive does after allocation) */
+c_int rldl_batch_refactor(RLDLBatch *b);
+/* one KKT solve per instance: rhs [batch][n+m] (current sizes) is overwritten with
+ * [x_tilde ; z_tilde] — the batched form of linsys_solver->solve */
+c_int rldl_batch_kkt_solve(RLDLBatch *b, c_float *rhs);
+/* gather: x [batch][nmax], y [batch][mmax] (any pointer may be NULL) */
+c_int rldl_batch_get_solution(RLDLBatch *b, c_float *x, c_float *y);
+c_int rldl_batch_get_info(RLDLBatch *b, c_int *iter, c_int *status_val, c_float *obj_val,
+                          c_float *pri_res, c_float *dua_res, c_int *rho_updates,
+                          c_float *rho_estimate);
+/* settings of the whole batch (validated like the reference's osqp_update_* setters) */
+c_int rldl_batch_update_settings(RLDLBatch *b, const OSQPSettings *settings);
+void  rldl_batch_dims(const RLDLBatch *b, c_int *n, c_int *m, c_int *N, c_int *batch);
+/* device time of the last factorisation / ADMM launch in milliseconds (CUDA events) */
+void  rldl_batch_last_times(const RLDLBatch *b, double *factor_ms, double *solve_ms);
+/* algorithmic bytes per instance and ADMM iteration, algorithmic bytes of
+ * the last factorisation launch, and kernels launched so far on this handle */
+void  rldl_batch_counters(const RLDLBatch *b, double *admm_bytes, double *factor_bytes, c_int *launches);
+void  rldl_batch_free(RLDLBatch *b);
+
+/* device plumbing */
+c_int rldl_device_count(void);
+c_int rldl_set_device(c_int device);
+const char *rldl_version(void);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* OSQP_RLDL_ABI_H */

@@ -1,0 +1,528 @@
+// rldl_batch.cu — host side of the batch handle (RLDLBatch): model upload, HBM
+// residency of all per-instance data, kernel sequencing.  C++ above the C ABI; no
+// CPU compute path exists here — every numerical step is a kernel launch.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include "rldl_batch.h"
+
+namespace rldl {
+
+#define CK(call)                                                                            \
+  do {                                                                                      \
+    cudaError_t e_ = (call);                                                                \
+    if (e_ != cudaSuccess) {                                                                \
+      fprintf(stderr, "ERROR in %s: CUDA failure '%s' at %s:%d\n", __func__,                \
+              cudaGetErrorString(e_), __FILE__, __LINE__);                                  \
+      return OSQP_LINSYS_SOLVER_INIT_ERROR;                                                 \
+    }                                                                                       \
+  } while (0)
+
+// ------------------------------ model upload ------------------------------
+static std::vector<double> csc_dense(const csc *M, int rows, int cols, bool symmetrize) {
+  std::vector<double> D((size_t)rows * cols, 0.0);
+  for (c_int j = 0; j < M->n && j < cols; j++)
+    for (c_int p = M->p[j]; p < M->p[j + 1]; p++) {
+      const c_int i = M->i[p];
+      if (i < 0 || i >= rows) continue;
+      D[(size_t)i * cols + j] += M->x[p];
+      if (symmetrize && i != j) D[(size_t)j * cols + i] += M->x[p];
+    }
+  return D;
+}
+
+struct ModelBuilder {
+  std::vector<double> val;
+  std::vector<int> idx;
+  int add_dense(const std::vector<double> &D) {
+    const int off = (int)val.size();
+    val.insert(val.end(), D.begin(), D.end());
+    idx.resize(val.size(), 0);
+    return off;
+  }
+  // rows x cols dense row-major -> ELL; transpose=true builds the ELL of D'
+  Ell add_ell(const std::vector<double> &D, int rows, int cols, bool transpose) {
+    const int R = transpose ? cols : rows, Cn = transpose ? rows : cols;
+    auto at = [&](int r, int c) { return transpose ? D[(size_t)c * cols + r] : D[(size_t)r * cols + c]; };
+    int width = 1;
+    for (int r = 0; r < R; r++) {
+      int cnt = 0;
+      for (int c = 0; c < Cn; c++) cnt += at(r, c) != 0.0;
+      width = std::max(width, cnt);
+    }
+    Ell E;
+    E.rows = R; E.width = R ? width : 0; E.off = (int)val.size();
+    for (int r = 0; r < R; r++) {
+      int cnt = 0;
+      for (int c = 0; c < Cn; c++)
+        if (at(r, c) != 0.0) { val.push_back(at(r, c)); idx.push_back(c); cnt++; }
+      for (; cnt < width; cnt++) { val.push_back(0.0); idx.push_back(0); }
+    }
+    return E;
+  }
+};
+
+static bool check_dims(const csc *M, c_int m, c_int n) { return M && M->m == m && M->n == n && M->p; }
+
+c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc *A0, const csc *Ai,
+                          const csc *Aij, const csc *AN) {
+  ModelBuilder mb;
+  ModelDev &Md = M;
+  Md.nx = nx; Md.nu = nu; Md.ny = ny; Md.nt = nt; Md.a = a; Md.b = b;
+  memset(Md.sc, 0, sizeof(Md.sc));
+  if (!generic) {
+    if (!check_dims(Q0, nu, nu) || !check_dims(Qi, a, a) || !check_dims(QN, nx, nx) ||
+        !check_dims(A0, b, nu) || !check_dims(Ai, b, a) || !check_dims(AN, nt, nx) ||
+        (Aij && !check_dims(Aij, b, a))) {
+      fprintf(stderr, "ERROR in %s: stage matrix dimensions do not match nx,nu,ny,nt\n", __func__);
+      return OSQP_DATA_VALIDATION_ERROR;
+    }
+    if (Aij) {  // must be [0 0; -I 0] — hard-wired in the reference too (src/recursive_ldl.c:584-586)
+      std::vector<double> D = csc_dense(Aij, b, a, false);
+      for (int r = 0; r < b; r++)
+        for (int c = 0; c < a; c++) {
+          const double want = (r >= ny && c == r - ny) ? -1.0 : 0.0;
+          if (D[(size_t)r * a + c] != want) {
+            fprintf(stderr, "ERROR in %s: Aij must be [0 0; -I 0]\n", __func__);
+            return OSQP_DATA_VALIDATION_ERROR;
+          }
+        }
+    }
+    // class 0: stage 0, padded with nx phantom variables (identity pivot, zero coupling)
+    {
+      std::vector<double> q0 = csc_dense(Q0, nu, nu, true), a0 = csc_dense(A0, b, nu, false);
+      std::vector<double> Q((size_t)a * a, 0.0), C((size_t)ny * a, 0.0), F((size_t)nx * a, 0.0);
+      for (int i = 0; i < nx; i++) Q[(size_t)i * a + i] = 1.0;
+      for (int i = 0; i < nu; i++)
+        for (int j = 0; j < nu; j++) Q[(size_t)(nx + i) * a + nx + j] = q0[(size_t)i * nu + j];
+      for (int r = 0; r < ny; r++)
+        for (int j = 0; j < nu; j++) C[(size_t)r * a + nx + j] = a0[(size_t)r * nu + j];
+      for (int r = 0; r < nx; r++)
+        for (int j = 0; j < nu; j++) F[(size_t)r * a + nx + j] = a0[(size_t)(ny + r) * nu + j];
+      StageClass &s = Md.sc[0];
+      s.Q = mb.add_dense(Q);
+      s.C = mb.add_ell(C, ny, a, false); s.Ct = mb.add_ell(C, ny, a, true);
+      s.F = mb.add_ell(F, nx, a, false); s.Ft = mb.add_ell(F, nx, a, true);
+    }
+    {
+      std::vector<double> Q = csc_dense(Qi, a, a, true), A = csc_dense(Ai, b, a, false);
+      std::vector<double> C(A.begin(), A.begin() + (size_t)ny * a), F(A.begin() + (size_t)ny * a, A.end());
+      StageClass &s = Md.sc[1];
+      s.Q = mb.add_dense(Q);
+      s.C = mb.add_ell(C, ny, a, false); s.Ct = mb.add_ell(C, ny, a, true);
+      s.F = mb.add_ell(F, nx, a, false); s.Ft = mb.add_ell(F, nx, a, true);
+    }
+  }
+  {
+    if (generic && (!check_dims(QN, nx, nx) || !check_dims(AN, nt, nx))) {
+      fprintf(stderr, "ERROR in %s: P must be n x n and A m x n\n", __func__);
+      return OSQP_DATA_VALIDATION_ERROR;
+    }
+    std::vector<double> Q = csc_dense(QN, nx, nx, true), C = csc_dense(AN, nt, nx, false);
+    StageClass &s = Md.sc[2];
+    s.Q = mb.add_dense(Q);
+    s.C = mb.add_ell(C, nt, nx, false); s.Ct = mb.add_ell(C, nt, nx, true);
+    s.F.rows = s.F.width = s.F.off = 0; s.Ft = s.F;
+  }
+  if (d_mval) cudaFree(d_mval);
+  if (d_midx) cudaFree(d_midx);
+  d_mval = nullptr; d_midx = nullptr;
+  CK(cudaMalloc(&d_mval, mb.val.size() * sizeof(double)));
+  CK(cudaMalloc(&d_midx, mb.idx.size() * sizeof(int)));
+  CK(cudaMemcpy(d_mval, mb.val.data(), mb.val.size() * sizeof(double), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d_midx, mb.idx.data(), mb.idx.size() * sizeof(int), cudaMemcpyHostToDevice));
+  Md.val = d_mval; Md.idx = d_midx;
+  return 0;
+}
+
+// ------------------------------ settings ------------------------------
+c_int validate_settings(const OSQPSettings *s) {
+  // reference src/auxil.c:889-1061
+#define BAD(msg) do { fprintf(stderr, "ERROR in validate_settings: %s\n", msg); return 1; } while (0)
+  if (!s) BAD("Missing settings!");
+  if (s->scaling < 0) BAD("scaling must be nonnegative");
+  if (s->adaptive_rho != 0 && s->adaptive_rho != 1) BAD("adaptive_rho must be either 0 or 1");
+  if (s->adaptive_rho_interval < 0) BAD("adaptive_rho_interval must be nonnegative");
+  if (s->adaptive_rho_fraction <= 0) BAD("adaptive_rho_fraction must be positive");
+  if (s->adaptive_rho_tolerance < 1.0) BAD("adaptive_rho_tolerance must be >= 1");
+  if (s->polish_refine_iter < 0) BAD("polish_refine_iter must be nonnegative");
+  if (s->rho <= 0.0) BAD("rho must be positive");
+  if (s->sigma <= 0.0) BAD("sigma must be positive");
+  if (s->delta <= 0.0) BAD("delta must be positive");
+  if (s->max_iter <= 0) BAD("max_iter must be positive");
+  if (s->eps_abs < 0.0) BAD("eps_abs must be nonnegative");
+  if (s->eps_rel < 0.0) BAD("eps_rel must be nonnegative");
+  if (s->eps_rel == 0.0 && s->eps_abs == 0.0) BAD("at least one of eps_abs and eps_rel must be positive");
+  if (s->eps_prim_inf <= 0.0) BAD("eps_prim_inf must be positive");
+  if (s->eps_dual_inf <= 0.0) BAD("eps_dual_inf must be positive");
+  if (s->alpha <= 0.0 || s->alpha >= 2.0) BAD("alpha must be strictly between 0 and 2");
+  if (s->linsys_solver != QDLDL_SOLVER && s->linsys_solver != MKL_PARDISO_SOLVER) BAD("linsys_solver not recognized");
+  if (s->verbose != 0 && s->verbose != 1) BAD("verbose must be either 0 or 1");
+  if (s->scaled_termination != 0 && s->scaled_termination != 1) BAD("scaled_termination must be either 0 or 1");
+  if (s->check_termination < 0) BAD("check_termination must be nonnegative");
+  if (s->warm_start != 0 && s->warm_start != 1) BAD("warm_start must be either 0 or 1");
+  if (s->time_limit < 0.0) BAD("time_limit must be nonnegative");
+#undef BAD
+  return 0;
+}
+
+// Preconditions of this path: rejected loudly, never silently diverging.
+static c_int validate_scope(const OSQPSettings *s) {
+  if (s->scaling != 0) {
+    fprintf(stderr, "ERROR in rldl: scaling must be 0 (the reference's recursive path factors the unscaled stage blocks)\n");
+    return 1;
+  }
+  if (s->polish != 0) { fprintf(stderr, "ERROR in rldl: polish is not supported on this path\n"); return 1; }
+  if (s->linsys_solver != QDLDL_SOLVER) { fprintf(stderr, "ERROR in rldl: linsys_solver must be QDLDL_SOLVER\n"); return 1; }
+  return 0;
+}
+
+void Batch::push_settings() {
+  S.sigma = settings.sigma; S.alpha = settings.alpha;
+  S.eps_abs = settings.eps_abs; S.eps_rel = settings.eps_rel;
+  S.eps_prim_inf = settings.eps_prim_inf; S.eps_dual_inf = settings.eps_dual_inf;
+  S.adaptive_rho_tolerance = settings.adaptive_rho_tolerance;
+  S.max_iter = (int)settings.max_iter; S.check_termination = (int)settings.check_termination;
+  S.adaptive_rho = (int)settings.adaptive_rho;
+  // osqp.c:459-485 picks the automatic interval from wall-clock; a batch cannot, so the
+  // non-PROFILING rule of the reference (osqp.c:248-262) is used when the interval is 0.
+  int ai = (int)settings.adaptive_rho_interval;
+  if (settings.adaptive_rho && !ai) ai = settings.check_termination ? 4 * (int)settings.check_termination : 100;
+  S.adaptive_rho_interval = ai;
+}
+
+// ------------------------------ lifetime ------------------------------
+template <class T>
+static cudaError_t dalloc(T **p, size_t count) {
+  *p = nullptr;
+  if (!count) count = 1;
+  cudaError_t e = cudaMalloc((void **)p, count * sizeof(T));
+  if (e == cudaSuccess) e = cudaMemset(*p, 0, count * sizeof(T));
+  return e;
+}
+
+c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, const csc *A0,
+                    const csc *Ai, const csc *Aij, const csc *AN, const OSQPSettings *st, c_int Nmax,
+                    c_int N, c_int nx, c_int nu, c_int ny, c_int nt, c_int batch, const c_float *q,
+                    const c_float *l, const c_float *u, const c_float *rho, bool generic) {
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    fprintf(stderr, "ERROR in rldl: no usable CUDA device — this library has no CPU path\n");
+    return OSQP_LINSYS_SOLVER_LOAD_ERROR;
+  }
+  if (validate_settings(st)) return OSQP_SETTINGS_VALIDATION_ERROR;
+  if (validate_scope(st)) return OSQP_SETTINGS_VALIDATION_ERROR;
+  if (batch < 1 || nx < 1 || nu < 0 || ny < 0 || nt < 0 || (!generic && (N < 1 || N > Nmax))) {
+    fprintf(stderr, "ERROR in rldl: invalid dimensions (need 1 <= N <= Nmax, batch >= 1)\n");
+    return OSQP_DATA_VALIDATION_ERROR;
+  }
+  Batch *B = new Batch();
+  B->generic = generic;
+  B->nx = (int)nx; B->nu = (int)nu; B->ny = (int)ny; B->nt = (int)nt;
+  B->a = (int)(nx + nu); B->b = (int)(nx + ny);
+  B->N = generic ? 0 : (int)N; B->Nmax = generic ? 0 : (int)Nmax; B->batch = (int)batch;
+  B->nmax = generic ? (int)nx : (int)(Nmax * (nx + nu));
+  B->mmax = generic ? (int)nt : (int)(Nmax * (nx + ny) + nt);
+  B->settings = *st;
+  CK(cudaGetDevice(&B->device));
+  c_int rc = B->upload_model(Q0, Qi, QN, A0, Ai, Aij, AN);
+  if (rc) { delete B; return rc; }
+  const size_t per_f = factor_smem_doubles(B->a, B->nx, B->ny, B->nt) * sizeof(double);
+  const size_t per_a = admm_smem_doubles(B->a, B->nx, B->ny, B->nt) * sizeof(double);
+  if (per_f > 220 * 1024 || per_a > 220 * 1024) {
+    fprintf(stderr, "ERROR in rldl: stage blocks too large for on-chip staging (a=%d, nx=%d)\n", B->a, B->nx);
+    delete B;
+    return OSQP_DATA_VALIDATION_ERROR;
+  }
+  BatchDev &D = B->D;
+  memset(&D, 0, sizeof(D));
+  D.batch = B->batch; D.Nmax = B->Nmax; D.nmax = B->nmax; D.mmax = B->mmax;
+  D.xstride = (B->Nmax + 1) * B->a * B->a;
+  D.sstride = std::max(1, B->Nmax * B->nx * B->nx);
+  D.ykstride = (B->Nmax + 1) * B->a;
+  D.skstride = std::max(1, B->Nmax * B->nx);
+  const size_t bs = (size_t)B->batch;
+  CK(dalloc(&D.q, bs * D.nmax)); CK(dalloc(&D.l, bs * D.mmax)); CK(dalloc(&D.u, bs * D.mmax));
+  CK(dalloc(&D.rho_vec, bs * D.mmax));
+  CK(dalloc(&D.x, bs * D.nmax)); CK(dalloc(&D.z, bs * D.mmax)); CK(dalloc(&D.y, bs * D.mmax));
+  CK(dalloc(&D.dx, bs * D.nmax)); CK(dalloc(&D.dy, bs * D.mmax));
+  CK(dalloc(&D.Xinv, bs * D.xstride)); CK(dalloc(&D.Sinv, bs * D.sstride));
+  CK(dalloc(&D.yk, bs * D.ykstride)); CK(dalloc(&D.sk, bs * D.skstride));
+  CK(dalloc(&D.rho, bs)); CK(dalloc(&D.iter, bs)); CK(dalloc(&D.status, bs));
+  CK(dalloc(&D.obj, bs)); CK(dalloc(&D.pri, bs)); CK(dalloc(&D.dua, bs)); CK(dalloc(&D.rho_est, bs));
+  CK(dalloc(&D.rho_updates, bs)); CK(dalloc(&D.fact_flag, bs));
+  CK(dalloc(&B->d_changed, bs));
+  CK(cudaStreamCreateWithFlags(&B->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&B->ev0)); CK(cudaEventCreate(&B->ev1));
+  B->set_sizes();
+  B->push_settings();
+  // per-instance data
+  CK(cudaMemcpyAsync(D.q, q, bs * D.nmax * sizeof(double), cudaMemcpyHostToDevice, B->stream));
+  CK(cudaMemcpyAsync(D.l, l, bs * D.mmax * sizeof(double), cudaMemcpyHostToDevice, B->stream));
+  CK(cudaMemcpyAsync(D.u, u, bs * D.mmax * sizeof(double), cudaMemcpyHostToDevice, B->stream));
+  if (rho) {
+    for (size_t i = 0; i < bs; i++)
+      if (!(rho[i] > 0.0)) { fprintf(stderr, "ERROR in rldl: rho must be positive\n"); delete B; return OSQP_SETTINGS_VALIDATION_ERROR; }
+    CK(cudaMemcpyAsync(D.rho, rho, bs * sizeof(double), cudaMemcpyHostToDevice, B->stream));
+  } else {
+    CK(launch_fill(D.rho, st->rho, bs, B->stream));
+    B->launches++;
+  }
+  std::vector<int> st0(bs, OSQP_UNSOLVED);
+  CK(cudaMemcpyAsync(D.status, st0.data(), bs * sizeof(int), cudaMemcpyHostToDevice, B->stream));
+  CK(cudaStreamSynchronize(B->stream));
+  // set_rho_vec (auxil.c:79) + full stage recursion (recursive_ldl.c:1139)
+  CK(launch_set_rho_vec(D, D.mmax, nullptr, B->stream));
+  B->launches++;
+  rc = B->factor(0, false);
+  if (rc) { delete B; return rc; }
+  *out = B;
+  return 0;
+}
+
+void Batch::set_sizes() {
+  D.N = N;
+  D.n = generic ? nx : N * a;
+  D.m = generic ? nt : N * b + nt;
+}
+
+Batch::~Batch() {
+  cudaSetDevice(device);
+  double *dp[] = {D.q, D.l, D.u, D.rho_vec, D.x, D.z, D.y, D.dx, D.dy, D.Xinv, D.Sinv, D.yk, D.sk,
+                  D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage};
+  for (double *p : dp) if (p) cudaFree(p);
+  if (D.iter) cudaFree(D.iter);
+  int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx};
+  for (int *p : ip) if (p) cudaFree(p);
+  if (h_pin) cudaFreeHost(h_pin);
+  if (ev0) cudaEventDestroy(ev0);
+  if (ev1) cudaEventDestroy(ev1);
+  if (stream) cudaStreamDestroy(stream);
+}
+
+c_int Batch::ensure_stage(size_t doubles) {
+  if (doubles <= stage_cap) return 0;
+  if (d_stage) cudaFree(d_stage);
+  d_stage = nullptr; stage_cap = 0;
+  CK(cudaMalloc(&d_stage, doubles * sizeof(double)));
+  stage_cap = doubles;
+  return 0;
+}
+
+// ------------------------------ operations ------------------------------
+c_int Batch::factor(int k0, bool only_flagged) {
+  CK(cudaSetDevice(device));
+  CK(cudaEventRecord(ev0, stream));
+  CK(launch_factor(M, D, settings.sigma, k0, only_flagged ? d_changed : nullptr, stream));
+  launches++;
+  CK(cudaEventRecord(ev1, stream));
+  CK(cudaStreamSynchronize(stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, ev0, ev1);
+  last_factor_ms = ms;
+  // algorithmic bytes: factor written once, rho_vec read once, per stage and instance
+  const double per_stage = (double)a * a + (double)nx * nx + b;
+  factor_bytes = 8.0 * batch * ((N - k0) * per_stage + (double)nx * nx + nt);
+  return 0;
+}
+
+c_int Batch::solve() {
+  CK(cudaSetDevice(device));
+  CK(cudaEventRecord(ev0, stream));
+  CK(launch_admm(M, D, S, (int)settings.warm_start, stream));
+  launches++;
+  CK(cudaEventRecord(ev1, stream));
+  CK(cudaStreamSynchronize(stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, ev0, ev1);
+  last_solve_ms = ms;
+  return 0;
+}
+
+c_int Batch::retype_and_refactor() {
+  // update_rho_vec (auxil.c:103-145): re-type rows; refactor instances whose types changed
+  CK(launch_set_rho_vec(D, D.m, d_changed, stream));
+  launches++;
+  std::vector<int> ch(batch);
+  CK(cudaMemcpyAsync(ch.data(), d_changed, batch * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  bool any = false;
+  for (int v : ch) any |= v != 0;
+  if (any) return factor(0, true);
+  return 0;
+}
+
+c_int Batch::reset_info() {
+  std::vector<int> st0(batch, OSQP_UNSOLVED);
+  CK(cudaMemcpyAsync(D.status, st0.data(), batch * sizeof(int), cudaMemcpyHostToDevice, stream));
+  CK(cudaMemsetAsync(D.rho_updates, 0, batch * sizeof(int), stream));
+  CK(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+c_int Batch::update_bounds(const c_float *l, const c_float *u, bool have_l, bool have_u) {
+  CK(cudaSetDevice(device));
+  const size_t bytes = (size_t)batch * D.mmax * sizeof(double);
+  if (have_l) CK(cudaMemcpyAsync(D.l, l, bytes, cudaMemcpyHostToDevice, stream));
+  if (have_u) CK(cudaMemcpyAsync(D.u, u, bytes, cudaMemcpyHostToDevice, stream));
+  c_int rc = reset_info();
+  if (rc) return rc;
+  return retype_and_refactor();
+}
+
+c_int Batch::partial_update_bounds(c_int start, c_int stop, const c_float *l, const c_float *u) {
+  CK(cudaSetDevice(device));
+  const int len = (int)(stop - start);
+  const size_t cnt = (size_t)batch * len;
+  c_int rc = ensure_stage(2 * cnt);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(d_stage, l, cnt * sizeof(double), cudaMemcpyHostToDevice, stream));
+  CK(cudaMemcpyAsync(d_stage + cnt, u, cnt * sizeof(double), cudaMemcpyHostToDevice, stream));
+  CK(launch_scatter_rows(D.l, D.mmax, d_stage, len, (int)start, batch, stream));
+  CK(launch_scatter_rows(D.u, D.mmax, d_stage + cnt, len, (int)start, batch, stream));
+  launches += 2;
+  rc = reset_info();
+  if (rc) return rc;
+  // The reference re-types the rows but never refactors (src/recursive_ldl.c:160-189, F6),
+  // which leaves factor and rho_vec inconsistent when a type changes; we keep them consistent.
+  return retype_and_refactor();
+}
+
+c_int Batch::update_lin_cost(const c_float *q) {
+  CK(cudaSetDevice(device));
+  CK(cudaMemcpyAsync(D.q, q, (size_t)batch * D.nmax * sizeof(double), cudaMemcpyHostToDevice, stream));
+  return reset_info();
+}
+
+c_int Batch::warm_start(const c_float *x, const c_float *y) {
+  CK(cudaSetDevice(device));
+  settings.warm_start = 1;  // osqp.c:935
+  if (x) CK(cudaMemcpyAsync(D.x, x, (size_t)batch * D.nmax * sizeof(double), cudaMemcpyHostToDevice, stream));
+  if (y) CK(cudaMemcpyAsync(D.y, y, (size_t)batch * D.mmax * sizeof(double), cudaMemcpyHostToDevice, stream));
+  if (x) { CK(launch_warm_start_z(M, D, stream)); launches++; }
+  CK(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+c_int Batch::update_horizon(c_int Nnew) {
+  CK(cudaSetDevice(device));
+  if (generic) return -1;
+  if (Nnew > Nmax || Nnew < 1) return -1;
+  if (Nnew == N) return 0;
+  const int k0 = std::min((int)Nnew, N);  // first stage whose pivots change
+  N = (int)Nnew;
+  set_sizes();
+  return factor(k0, false);
+}
+
+c_int Batch::update_rho(const c_float *rho) {
+  CK(cudaSetDevice(device));
+  for (int i = 0; i < batch; i++)
+    if (!(rho[i] > 0.0)) { fprintf(stderr, "ERROR in osqp_update_rho: rho must be positive\n"); return 1; }
+  CK(cudaMemcpyAsync(D.rho, rho, (size_t)batch * sizeof(double), cudaMemcpyHostToDevice, stream));
+  CK(launch_set_rho_vec(D, D.m, nullptr, stream));
+  launches++;
+  return factor(0, false);
+}
+
+c_int Batch::refactor() {
+  CK(cudaSetDevice(device));
+  CK(launch_set_rho_vec(D, D.mmax, nullptr, stream));
+  launches++;
+  return factor(0, false);
+}
+
+c_int Batch::kkt_solve(c_float *rhs) {
+  CK(cudaSetDevice(device));
+  const int ld = D.n + D.m;
+  const size_t cnt = (size_t)batch * ld;
+  c_int rc = ensure_stage(cnt);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(d_stage, rhs, cnt * sizeof(double), cudaMemcpyHostToDevice, stream));
+  CK(launch_kkt_solve(M, D, S, d_stage, ld, stream));
+  launches++;
+  CK(cudaMemcpyAsync(rhs, d_stage, cnt * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+static bool no_solution(int st) {
+  return st == OSQP_PRIMAL_INFEASIBLE || st == OSQP_PRIMAL_INFEASIBLE_INACCURATE ||
+         st == OSQP_DUAL_INFEASIBLE || st == OSQP_DUAL_INFEASIBLE_INACCURATE || st == OSQP_NON_CVX;
+}
+
+c_int Batch::get_solution(c_float *x, c_float *y) {
+  CK(cudaSetDevice(device));
+  std::vector<int> st(batch);
+  CK(cudaMemcpyAsync(st.data(), D.status, batch * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  if (x) CK(cudaMemcpyAsync(x, D.x, (size_t)batch * D.nmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (y) CK(cudaMemcpyAsync(y, D.y, (size_t)batch * D.mmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  for (int i = 0; i < batch; i++)
+    if (no_solution(st[i])) {  // store_solution, auxil.c:539-542
+      if (x) std::fill(x + (size_t)i * D.nmax, x + (size_t)i * D.nmax + D.n, (double)OSQP_NAN);
+      if (y) std::fill(y + (size_t)i * D.mmax, y + (size_t)i * D.mmax + D.m, (double)OSQP_NAN);
+    }
+  return 0;
+}
+
+c_int Batch::get_info(c_int *iter, c_int *status, c_float *obj, c_float *pri, c_float *dua,
+                      c_int *rho_updates, c_float *rho_est) {
+  CK(cudaSetDevice(device));
+  std::vector<int> st(batch), ru(batch);
+  if (iter) CK(cudaMemcpyAsync(iter, D.iter, batch * sizeof(long long), cudaMemcpyDeviceToHost, stream));
+  CK(cudaMemcpyAsync(st.data(), D.status, batch * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CK(cudaMemcpyAsync(ru.data(), D.rho_updates, batch * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  if (obj) CK(cudaMemcpyAsync(obj, D.obj, batch * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (pri) CK(cudaMemcpyAsync(pri, D.pri, batch * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (dua) CK(cudaMemcpyAsync(dua, D.dua, batch * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (rho_est) CK(cudaMemcpyAsync(rho_est, D.rho_est, batch * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  for (int i = 0; i < batch; i++) {
+    if (status) status[i] = st[i];
+    if (rho_updates) rho_updates[i] = ru[i];
+  }
+  return 0;
+}
+
+c_int Batch::fetch_vectors(int inst, c_float *x, c_float *y, c_float *z, c_float *dx, c_float *dy,
+                           c_float *rho_vec, c_float *rho) {
+  CK(cudaSetDevice(device));
+  const size_t vo = (size_t)inst * D.nmax, ro = (size_t)inst * D.mmax;
+  if (x) CK(cudaMemcpyAsync(x, D.x + vo, D.nmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (y) CK(cudaMemcpyAsync(y, D.y + ro, D.mmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (z) CK(cudaMemcpyAsync(z, D.z + ro, D.mmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (dx) CK(cudaMemcpyAsync(dx, D.dx + vo, D.nmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (dy) CK(cudaMemcpyAsync(dy, D.dy + ro, D.mmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (rho_vec) CK(cudaMemcpyAsync(rho_vec, D.rho_vec + ro, D.mmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  if (rho) CK(cudaMemcpyAsync(rho, D.rho + inst, sizeof(double), cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+c_int Batch::update_settings(const OSQPSettings *s) {
+  if (validate_settings(s)) return 1;
+  if (validate_scope(s)) return 1;
+  const double old_rho = settings.rho, old_sigma = settings.sigma;
+  settings = *s;
+  settings.rho = old_rho;  // rho changes go through update_rho
+  settings.sigma = old_sigma;
+  push_settings();
+  return 0;
+}
+
+double Batch::admm_bytes_per_iteration() const {
+  // per instance and ADMM iteration: the stage factor streamed once forward and once
+  // backward, plus first-read / last-write of the iterates and problem vectors
+  const double F = (double)N * ((double)a * a + (double)nx * nx) + (double)nx * nx;
+  const double vec = 3.0 * D.n + 7.0 * D.m;  // x(r,w) q ; z(r,w) y(r,w) l u rho
+  return 8.0 * (2.0 * F + vec);
+}
+
+}  // namespace rldl

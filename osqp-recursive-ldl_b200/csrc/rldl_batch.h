@@ -1,0 +1,63 @@
+// rldl_batch.h — the batch handle behind the C ABI (RLDLBatch == rldl::Batch)
+#pragma once
+#include <cuda_runtime.h>
+#include "../../include/osqp_rldl_abi.h"
+#include "rldl_device.h"
+#include "rldl_kernels.h"
+
+namespace rldl {
+
+c_int validate_settings(const OSQPSettings *s);
+
+struct Batch {
+  int device = 0;
+  bool generic = false;  // osqp_setup path: one dense stage (N == 0)
+  int nx = 0, nu = 0, ny = 0, nt = 0, a = 0, b = 0, N = 0, Nmax = 0, batch = 0, nmax = 0, mmax = 0;
+  OSQPSettings settings;
+  ModelDev M;
+  BatchDev D;
+  SettingsDev S;
+  double *d_mval = nullptr;
+  int *d_midx = nullptr;
+  int *d_changed = nullptr;
+  double *d_stage = nullptr;
+  size_t stage_cap = 0;
+  double *h_pin = nullptr;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double last_factor_ms = 0, last_solve_ms = 0, factor_bytes = 0;
+  long long launches = 0;
+
+  static c_int create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, const csc *A0,
+                      const csc *Ai, const csc *Aij, const csc *AN, const OSQPSettings *st, c_int Nmax,
+                      c_int N, c_int nx, c_int nu, c_int ny, c_int nt, c_int batch, const c_float *q,
+                      const c_float *l, const c_float *u, const c_float *rho, bool generic);
+  ~Batch();
+
+  c_int upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc *A0, const csc *Ai,
+                     const csc *Aij, const csc *AN);
+  void push_settings();
+  void set_sizes();
+  c_int ensure_stage(size_t doubles);
+  c_int factor(int k0, bool only_flagged);
+  c_int solve();
+  c_int retype_and_refactor();
+  c_int reset_info();
+  c_int update_bounds(const c_float *l, const c_float *u, bool have_l, bool have_u);
+  c_int partial_update_bounds(c_int start, c_int stop, const c_float *l, const c_float *u);
+  c_int update_lin_cost(const c_float *q);
+  c_int warm_start(const c_float *x, const c_float *y);
+  c_int update_horizon(c_int Nnew);
+  c_int update_rho(const c_float *rho);
+  c_int refactor();
+  c_int kkt_solve(c_float *rhs);
+  c_int get_solution(c_float *x, c_float *y);
+  c_int get_info(c_int *iter, c_int *status, c_float *obj, c_float *pri, c_float *dua,
+                 c_int *rho_updates, c_float *rho_est);
+  c_int fetch_vectors(int inst, c_float *x, c_float *y, c_float *z, c_float *dx, c_float *dy,
+                      c_float *rho_vec, c_float *rho);
+  c_int update_settings(const OSQPSettings *s);
+  double admm_bytes_per_iteration() const;
+};
+
+}  // namespace rldl

@@ -1,0 +1,72 @@
+// rldl_device.h — device-side data model shared by the kernels and the host API.
+//
+// Stage-ordered block elimination of the MPC KKT matrix (reference
+// src/recursive_ldl.c:1139-1318), re-designed for HBM
+// streaming.  Per stage k the KKT rows are
+//     v_k  : (Q_k + sigma I) v_k + C_k' nu^p_k + F_k' nu^d_k - J' nu^d_{k-1} = r^v_k
+//     p_k  : C_k v_k - diag(1/rho^p_k) nu^p_k                              = r^p_k
+//     d_k  : F_k v_k - J v_{k+1} - diag(1/rho^d_k) nu^d_k                  = r^d_k
+// (v_k = (x_k,u_k), C_k = path rows, F_k = [A B] dynamics rows, J = [I_nx 0]).
+// Pivot order inside a stage: path rows, stage variables, dynamics rows — an
+// algebraically equivalent ordering of the reference's (variables, all rows):
+//     M_k = Q_k + sigma I + C_k' diag(rho^p_k) C_k
+//     X_0 = M_0,  S_k = diag(1/rho^d_k) + F_k X_k^-1 F_k',  X_{k+1} = M_{k+1} + J' S_k^-1 J
+// The stored factor is the pair of inverted diagonal pivots per stage,
+//     Xinv_k (a x a)   and   Sinv_k (nx x nx),
+// so every block substitution is a small dense symmetric mat-vec with no
+// sequential dependence inside the block.  Stage 0 carries nx phantom variables
+// (identity pivot, zero coupling) so all stages have the same shape.
+#pragma once
+#include <cstdint>
+
+namespace rldl {
+
+// Row-wise ELL view of one small shared model matrix inside the model buffer.
+struct Ell {
+  int rows;
+  int width;  // entries per row (padded with idx 0 / val 0)
+  int off;    // offset of idx[] in ModelDev::idx and of val[] in ModelDev::val
+};
+
+struct StageClass {
+  int Q;      // offset (doubles) of the dense symmetric cost block, dim x dim
+  Ell C, Ct;  // path rows      (np x dim) and transpose
+  Ell F, Ft;  // dynamics rows  (nx x dim) and transpose (unused for the terminal class)
+};
+
+// Shared stage model: class 0 = stage 0 (phantom-padded), 1 = interior, 2 = terminal.
+struct ModelDev {
+  int nx, nu, ny, nt, a, b;
+  StageClass sc[3];
+  const double *val;
+  const int *idx;
+};
+
+struct SettingsDev {
+  double sigma, alpha, eps_abs, eps_rel, eps_prim_inf, eps_dual_inf;
+  double adaptive_rho_tolerance;
+  int max_iter, check_termination, adaptive_rho, adaptive_rho_interval;
+};
+
+// Per-instance arrays are instance-major with the strides below.
+struct BatchDev {
+  int batch, N, Nmax;
+  int n, m;                // current problem sizes (N*a, N*b+nt; N==0: nx, nt)
+  int nmax, mmax;          // vector strides
+  int xstride, sstride;    // factor strides (doubles): (Nmax+1)*a*a, Nmax*nx*nx
+  int ykstride, skstride;  // (Nmax+1)*a, Nmax*nx
+  double *q, *l, *u, *rho_vec;
+  double *x, *z, *y, *dx, *dy;
+  double *Xinv, *Sinv;
+  double *yk, *sk;
+  double *rho;             // current scalar rho per instance
+  long long *iter;
+  int *status;
+  double *obj, *pri, *dua, *rho_est;
+  int *rho_updates;
+  int *fact_flag;          // 0 ok, >0 = 1 + stage of the first non-positive pivot
+};
+
+constexpr int STATUS_FACTOR_ERROR = -7;  // reported as OSQP_NON_CVX
+
+}  // namespace rldl

@@ -1,0 +1,20 @@
+// rldl_kernels.h — host-callable launchers of the kernels in rldl_kernels.cu
+#pragma once
+#include <cuda_runtime.h>
+#include "rldl_device.h"
+
+namespace rldl {
+size_t factor_smem_doubles(int a, int nx, int ny, int nt);
+size_t admm_smem_doubles(int a, int nx, int ny, int nt);
+cudaError_t launch_set_rho_vec(const BatchDev &B, int m, int *changed, cudaStream_t st);
+cudaError_t launch_factor(const ModelDev &M, const BatchDev &B, double sigma, int k0,
+                          const int *only_flagged, cudaStream_t st);
+cudaError_t launch_admm(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
+                        cudaStream_t st);
+cudaError_t launch_kkt_solve(const ModelDev &M, const BatchDev &B, const SettingsDev &S, double *rhs,
+                             int ld, cudaStream_t st);
+cudaError_t launch_warm_start_z(const ModelDev &M, const BatchDev &B, cudaStream_t st);
+cudaError_t launch_fill(double *p, double v, size_t n, cudaStream_t st);
+cudaError_t launch_scatter_rows(double *dst, int ld, const double *src, int len, int start, int batch,
+                                cudaStream_t st);
+}  // namespace rldl
