@@ -155,3 +155,61 @@ class RefBatch:
         if self.h:
             lib().refb_free(self.h)
             self.h = None
+
+
+# ---------------------------------------------------------------------------
+# Process isolation.  The reference's recursive path corrupts the heap on some
+# shapes (L buffers sized from nnz(P), one write past L->p when
+# N == Nmax), which can abort the *calling* process much later.  Tests and the
+# bench therefore run every reference job in a throw-away child process.
+# ---------------------------------------------------------------------------
+def run_ops(spec):
+    """Execute a scripted sequence on one RefBatch (in THIS process).
+
+    spec = dict(model=MPCModel, N=, Nmax=, q=, l=, u=, settings=dict, path=, rho=None,
+                nthreads=None, ops=[(name, *args), ...])
+    ops: ("solve",) ("get",) ("update_bounds", l, u) ("partial_update_bounds", s, e, l, u)
+         ("update_lin_cost", q) ("warm_start", x, y) ("update_horizon", N) ("update_rho", rho)
+         ("kkt_solve", k, rhs) ("dims",)
+    Returns a list with one entry per op (return code, dict or array) plus timing of
+    the constructor as result[-1] = dict(setup_wall=, solve_wall=[...]).
+    """
+    import time
+    t0 = time.perf_counter()
+    rb = RefBatch(spec["model"], spec["N"], spec["Nmax"], spec["q"], spec["l"], spec["u"],
+                  default_settings(**spec["settings"]), path=spec.get("path", "recursive"),
+                  rho=spec.get("rho"), nthreads=spec.get("nthreads"))
+    setup_wall = time.perf_counter() - t0
+    res, solve_wall = [], []
+    for op in spec["ops"]:
+        name, args = op[0], op[1:]
+        if name == "solve":
+            t0 = time.perf_counter()
+            res.append(rb.solve())
+            solve_wall.append(time.perf_counter() - t0)
+        else:
+            res.append(getattr(rb, name)(*args))
+    res.append(dict(setup_wall=setup_wall, solve_wall=solve_wall, nthreads=rb.nthreads))
+    return res  # the batch is leaked on purpose: the process is about to exit
+
+
+def run_isolated(spec, timeout=1800):
+    """run_ops(spec) in a child interpreter (pickle in / pickle out through a temp dir)."""
+    import pickle
+    import subprocess
+    import sys
+    import tempfile
+    root = os.path.dirname(_HERE)
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout = os.path.join(td, "in.pkl"), os.path.join(td, "out.pkl")
+        with open(fin, "wb") as f:
+            pickle.dump(spec, f, protocol=4)
+        env = dict(os.environ)
+        env["PYTHONPATH"] = os.pathsep.join([root, os.path.join(root, "osqp-recursive-ldl_b200"),
+                                             env.get("PYTHONPATH", "")])
+        cp = subprocess.run([sys.executable, "-m", "oracle.ref_worker", fin, fout], env=env, cwd=root,
+                            timeout=timeout, capture_output=True, text=True)
+        if not os.path.exists(fout):
+            raise RuntimeError(f"reference worker failed (rc={cp.returncode}): {cp.stderr[-2000:]}")
+        with open(fout, "rb") as f:
+            return pickle.load(f)

@@ -13,9 +13,20 @@ BASE = dict(scaling=0, polish=0, verbose=0, time_limit=0.0, check_termination=25
 REL_TOL = 1e-6  # north_star: x, y, obj within 1e-6 relative in FP64
 
 
-def settings_pair(**kw):
+def settings_dict(**kw):
     d = dict(BASE); d.update(kw)
-    return R.default_settings(**d), ref_py.default_settings(**d)
+    return d
+
+
+def gpu_settings(**kw):
+    return R.default_settings(**settings_dict(**kw))
+
+
+def ref_run(mdl, N, Nmax, q, l, u, ops, path="recursive", rho=None, nthreads=None, **kw):
+    """Run a scripted op sequence on the UNMODIFIED reference in a child process."""
+    spec = dict(model=mdl, N=N, Nmax=Nmax, q=q, l=l, u=u, settings=settings_dict(**kw), path=path,
+                rho=rho, nthreads=nthreads, ops=ops)
+    return ref_py.run_isolated(spec)
 
 
 def rel_err(a, b):
