@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""bench.py — batched MPC QP solves/s through librldl_b200 (C ABI) on 1..8 B200.
+
+Workload (BASELINE.json configs[4], "C5"): the docs quadcopter MPC (nx=12, nu=4, N=50,
+box constraints, n=800, m=1412), 65536 independent instances with random x0, split
+evenly across the ranks (strong scaling; instances share nothing, so there is no
+collective on the solve path — torch.distributed is only the barrier / max-reduce).
+
+One step = the hot path over the whole batch: full stage-wise KKT factorisation
+(rldl_batch_refactor) + cold-start ADMM solve to convergence (rldl_batch_solve).
+  value  : instances solved per second, data resident in HBM (CUDA events on the
+           library's launching stream, max over ranks)
+  e2e    : same through the host-buffer API: rldl_batch_update_bounds(l,u) +
+           rldl_batch_update_lin_cost(q) from pinned host memory, refactor, solve,
+           rldl_batch_get_solution(x,y) + rldl_batch_get_info back to pinned host memory
+--impl reference times the UNMODIFIED reference (oracle/_ref: osqp_setup_recursive +
+osqp_solve_recursive) on the host cores over a bounded sample of the same instances.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "osqp-recursive-ldl_b200"))
+
+import numpy as np  # noqa: E402
+
+SETTINGS = dict(scaling=0, polish=0, verbose=0, time_limit=0.0, check_termination=25, eps_abs=1e-5,
+                eps_rel=1e-5, eps_prim_inf=1e-4, eps_dual_inf=1e-4, alpha=1.6, sigma=1e-6, rho=0.1,
+                max_iter=4000, warm_start=0, adaptive_rho=0, adaptive_rho_interval=25)
+METRIC = "batched MPC QP solves/sec"
+UNIT = "solves/s"
+SEED = 1234
+
+
+def workload(name, total_batch):
+    from rldl_b200 import mpc
+    cfg = dict(mpc.CONFIGS[name])
+    if total_batch:
+        cfg["batch"] = total_batch
+    mdl = mpc.make_model(cfg)
+    return cfg, mdl
+
+
+def config_dict(name, cfg, n_gpus, extra=None):
+    d = {"workload": f"{name}: {cfg['model']} MPC nx={cfg['nx']} nu={cfg['nu']} N={cfg['N']}, "
+                     f"batch {cfg['batch']} split over {n_gpus} GPU(s), cold start, eps 1e-5, rho 0.1, "
+                     f"step = full stage factorisation + ADMM solve to convergence per instance",
+         "batch": cfg["batch"], "nx": cfg["nx"], "nu": cfg["nu"], "N": cfg["N"],
+         "l2": "per-GPU working set (factors + iterates) is far larger than the 126 MB L2; no flush needed"}
+    if extra:
+        d.update(extra)
+    return d
+
+
+# ----------------------------------------------------------------------------
+# reference arm / cpu_baseline: the unmodified reference on the host cores
+# ----------------------------------------------------------------------------
+def ref_sample_size(cores):
+    return int(min(2048, max(64, 32 * cores)))
+
+
+def run_reference_sample(mdl, cfg, sample, seed_offset=0):
+    """setup + solve of `sample` instances of the workload on all host cores (child process).
+    Returns (solves_per_s, seconds, threads, mean_iter)."""
+    from rldl_b200 import mpc
+    from oracle import ref_py
+    N = cfg["N"]
+    x0 = mpc.sample_x0(mdl, cfg["batch"], SEED)[seed_offset:seed_offset + sample]
+    q, l, u = mdl.vectors(x0, N)
+    res = ref_py.run_isolated(dict(model=mdl, N=N, Nmax=N, q=q, l=l, u=u, settings=SETTINGS,
+                                   path="recursive", ops=[("solve",), ("get",)]))
+    t = res[-1]
+    secs = t["setup_wall"] + t["solve_wall"][0]
+    out = res[1]
+    assert (out["status"] == 1).all(), "reference did not solve every sampled instance"
+    return sample / secs, secs, t["nthreads"], float(out["iter"].mean())
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cfg, mdl = workload(args.workload, args.batch)
+    cores = os.cpu_count() or 1
+    sample = min(ref_sample_size(cores), cfg["batch"])
+    for _ in range(args.warmup):
+        run_reference_sample(mdl, cfg, min(sample, 4 * cores))
+    tot_s, tot_n, thr, its = 0.0, 0, cores, 0.0
+    for k in range(args.steps):
+        off = (k * sample) % max(1, cfg["batch"] - sample + 1)
+        v, secs, thr, it = run_reference_sample(mdl, cfg, sample, off)
+        tot_s += secs; tot_n += sample; its += it
+    value = tot_n / tot_s
+    desc = (f"{sample} instances of the workload per step (osqp_setup_recursive + osqp_solve_recursive each), "
+            f"{thr} pthreads over instances, mean {its / args.steps:.0f} ADMM iterations")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": config_dict(args.workload, cfg, args.gpus),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": thr, "kind": "reference", "sample": desc},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ----------------------------------------------------------------------------
+# clocks sampling (B200_PROFILING.md recipe)
+# ----------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.split(",") for r in open(self.f.name).read().strip().splitlines() if r.strip()]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            r = [c.strip() for c in r]
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons),
+                       samples=len(sm))
+        return out
+
+
+# ----------------------------------------------------------------------------
+# B200 arm
+# ----------------------------------------------------------------------------
+def main_b200(args):
+    import torch
+    import rldl_b200 as R
+    from rldl_b200 import mpc
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: librldl_b200 has no CPU path")
+    torch.cuda.set_device(local)
+    lib = R.lib()
+    if lib.rldl_set_device(local):
+        raise SystemExit("rldl_set_device failed")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    cfg, mdl = workload(args.workload, args.batch)
+    N, total = cfg["N"], cfg["batch"]
+    lo, hi = rank * total // world, (rank + 1) * total // world
+    mine = hi - lo
+    x0 = mpc.sample_x0(mdl, total, SEED)[lo:hi]
+    q_np, l_np, u_np = mdl.vectors(x0, N)
+    nmax, mmax = q_np.shape[1], l_np.shape[1]
+    # pinned host staging (the C ABI takes plain host pointers)
+    pin = lambda a: torch.from_numpy(a).pin_memory()
+    q_h, l_h, u_h = pin(q_np), pin(l_np), pin(u_np)
+    x_h = torch.empty((mine, nmax), dtype=torch.float64).pin_memory()
+    y_h = torch.empty((mine, mmax), dtype=torch.float64).pin_memory()
+    info_h = {k: torch.empty(mine, dtype=(torch.int64 if k in ("iter", "status", "rho_updates") else torch.float64)).pin_memory()
+              for k in ("iter", "status", "obj", "pri", "dua", "rho_updates", "rho_est")}
+    del q_np, l_np, u_np
+
+    gb = R.Batch(mdl, N, N, q_h.numpy(), l_h.numpy(), u_h.numpy(), R.default_settings(**SETTINGS))
+    stream = torch.cuda.ExternalStream(gb.stream())
+    P = lambda t: t.data_ptr()
+
+    def step_device():
+        assert gb.refactor() == 0
+        assert gb.solve() == 0
+        return gb.last_times()
+
+    def step_e2e():
+        assert lib.rldl_batch_update_bounds(gb.h, P(l_h), P(u_h)) == 0
+        assert lib.rldl_batch_update_lin_cost(gb.h, P(q_h)) == 0
+        assert gb.refactor() == 0
+        assert gb.solve() == 0
+        assert lib.rldl_batch_get_solution(gb.h, P(x_h), P(y_h)) == 0
+        assert lib.rldl_batch_get_info(gb.h, *[P(info_h[k]) for k in
+                                               ("iter", "status", "obj", "pri", "dua", "rho_updates", "rho_est")]) == 0
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        parts = [fn() for _ in range(steps)]
+        e1.record(stream)
+        e1.synchronize()
+        barrier()
+        return allmax(e0.elapsed_time(e1)), parts
+
+    for _ in range(args.warmup):
+        step_device()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    _, _, l0 = gb.counters()
+    ms_dev, parts = timed(step_device, args.steps)
+    _, _, l1 = gb.counters()
+    clocks = sampler.stop() if sampler else None
+    launches = allsum(float(l1 - l0))
+
+    # parity-relevant facts of the timed solves
+    step_e2e()  # also refreshes info_h / warms the e2e path
+    iters = info_h["iter"].numpy().astype(np.float64)
+    status = info_h["status"].numpy()
+    solved = allsum(float((status == 1).sum()))
+    iter_sum = float(iters.sum())
+    for _ in range(max(0, args.warmup - 1)):
+        step_e2e()
+    ms_e2e, _ = timed(step_e2e, args.steps)
+
+    value = total * args.steps / (ms_dev * 1e-3)
+    e2e_value = total * args.steps / (ms_e2e * 1e-3)
+    h2d = allsum(float(8 * (l_h.numel() + u_h.numel() + q_h.numel())))
+    d2h = allsum(float(8 * (x_h.numel() + y_h.numel()) + sum(t.numel() * 8 for t in info_h.values())))
+
+    # roofline of the dominant kernel (the fused ADMM kernel): algorithmic bytes per launch
+    # = sum over this rank's instances of iterations x bytes/iteration, over the
+    # kernel's own CUDA-event duration measured inside the library on its launching stream
+    admm_bytes, factor_bytes, _ = gb.counters()
+    f_ms = float(np.mean([p[0] for p in parts])); s_ms = float(np.mean([p[1] for p in parts]))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = iter_sum * admm_bytes / (s_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": "k_admm (fused KKT solve + ADMM step, whole solve loop)",
+            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
+            "traffic": None, "launch_ms": s_ms, "algorithmic_bytes_per_launch": iter_sum * admm_bytes,
+            "factor_kernel": {"launch_ms": f_ms, "achieved": factor_bytes / (f_ms * 1e-3) / 1e9,
+                              "frac": factor_bytes / (f_ms * 1e-3) / 1e9 / peak}}
+    mean_iter = allsum(iter_sum) / total
+    gb.free()
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": config_dict(args.workload, cfg, world,
+                                      {"mean_admm_iterations": mean_iter, "solved_fraction": solved / total}),
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "ms_per_step": ms_e2e / args.steps},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof}
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            sample = min(ref_sample_size(cores), total)
+            v, secs, thr, it = run_reference_sample(mdl, cfg, sample)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": thr, "kind": "reference",
+                                    "sample": f"first {sample} instances of the workload, osqp_setup_recursive + "
+                                              f"osqp_solve_recursive each, {thr} pthreads, {secs:.2f} s wall, "
+                                              f"mean {it:.0f} ADMM iterations"}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C5")
+    ap.add_argument("--batch", type=int, default=0, help="override the total batch (debug)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return main_reference(args)
+    return main_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

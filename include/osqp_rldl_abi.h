@@ -396,6 +396,9 @@ void  rldl_batch_last_times(const RLDLBatch *b, double *factor_ms, double *solve
 /* algorithmic bytes per instance and ADMM iteration, algorithmic bytes of
  * the last factorisation launch, and kernels launched so far on this handle */
 void  rldl_batch_counters(const RLDLBatch *b, double *admm_bytes, double *factor_bytes, c_int *launches);
+/* the CUDA stream (cudaStream_t) every launch and copy of this handle is issued on, so a
+ * caller can bracket calls with its own events on the launching stream */
+void *rldl_batch_stream(const RLDLBatch *b);
 void  rldl_batch_free(RLDLBatch *b);
 
 /* device plumbing */

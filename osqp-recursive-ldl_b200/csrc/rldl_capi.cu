@@ -764,6 +764,7 @@ void rldl_batch_counters(const RLDLBatch *h, double *admm_bytes, double *factor_
   if (factor_bytes) *factor_bytes = h->b->factor_bytes;
   if (launches) *launches = h->b->launches;
 }
+void *rldl_batch_stream(const RLDLBatch *h) { return (h && h->b) ? (void *)h->b->stream : nullptr; }
 void rldl_batch_free(RLDLBatch *h) {
   if (!h) return;
   delete h->b;
