@@ -136,7 +136,7 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
   CK(cudaMalloc(&d_midx, mb.idx.size() * sizeof(int)));
   CK(cudaMemcpy(d_mval, mb.val.data(), mb.val.size() * sizeof(double), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(d_midx, mb.idx.data(), mb.idx.size() * sizeof(int), cudaMemcpyHostToDevice));
-  Md.val = d_mval; Md.idx = d_midx;
+  Md.val = d_mval; Md.idx = d_midx; Md.nval = (int)mb.val.size();
   return 0;
 }
 
@@ -258,6 +258,15 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(dalloc(&D.obj, bs)); CK(dalloc(&D.pri, bs)); CK(dalloc(&D.dua, bs)); CK(dalloc(&D.rho_est, bs));
   CK(dalloc(&D.rho_updates, bs)); CK(dalloc(&D.fact_flag, bs));
   CK(dalloc(&B->d_changed, bs));
+  B->streaming = !generic && stream_supported(B->M, B->N);
+  {
+    auto ev = [](int v) { return (v + 1) & ~1; };
+    D.qa = ev(B->a); D.PX = ev(B->a * (B->a + 1) / 2); D.PS = ev(B->nx * (B->nx + 1) / 2); D.bb = ev(B->b);
+    D.RS = D.qa + D.PX + D.PS + 3 * D.bb;
+    D.rec_stride = (long long)(B->Nmax + 1) * D.RS;
+    CK(dalloc(&D.rec, B->streaming ? bs * (size_t)D.rec_stride : 1));
+    CK(dalloc(&D.work_counter, 1));
+  }
   CK(cudaStreamCreateWithFlags(&B->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&B->ev0)); CK(cudaEventCreate(&B->ev1));
   B->set_sizes();
@@ -295,10 +304,10 @@ void Batch::set_sizes() {
 Batch::~Batch() {
   cudaSetDevice(device);
   double *dp[] = {D.q, D.l, D.u, D.rho_vec, D.x, D.z, D.y, D.dx, D.dy, D.Xinv, D.Sinv, D.yk, D.sk,
-                  D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage};
+                  D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec};
   for (double *p : dp) if (p) cudaFree(p);
   if (D.iter) cudaFree(D.iter);
-  int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx};
+  int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx, D.work_counter};
   for (int *p : ip) if (p) cudaFree(p);
   if (h_pin) cudaFreeHost(h_pin);
   if (ev0) cudaEventDestroy(ev0);
@@ -321,6 +330,10 @@ c_int Batch::factor(int k0, bool only_flagged) {
   CK(cudaEventRecord(ev0, stream));
   CK(launch_factor(M, D, settings.sigma, k0, only_flagged ? d_changed : nullptr, stream));
   launches++;
+  if (streaming) {
+    CK(launch_pack_records(M, D, only_flagged ? 0 : k0, 3, stream));
+    launches++;
+  }
   CK(cudaEventRecord(ev1, stream));
   CK(cudaStreamSynchronize(stream));
   float ms = 0;
@@ -335,13 +348,25 @@ c_int Batch::factor(int k0, bool only_flagged) {
 c_int Batch::solve() {
   CK(cudaSetDevice(device));
   CK(cudaEventRecord(ev0, stream));
-  CK(launch_admm(M, D, S, (int)settings.warm_start, stream));
+  if (use_stream()) CK(launch_admm_stream(M, D, S, (int)settings.warm_start, stream));
+  else CK(launch_admm(M, D, S, (int)settings.warm_start, stream));
   launches++;
   CK(cudaEventRecord(ev1, stream));
   CK(cudaStreamSynchronize(stream));
   float ms = 0;
   cudaEventElapsedTime(&ms, ev0, ev1);
   last_solve_ms = ms;
+  return 0;
+}
+
+bool Batch::use_stream() const {
+  return streaming && !settings.adaptive_rho && kernel_choice != 1;
+}
+
+c_int Batch::pack(int k0, int parts) {
+  if (!streaming) return 0;
+  CK(launch_pack_records(M, D, k0, parts, stream));
+  launches++;
   return 0;
 }
 
@@ -373,7 +398,9 @@ c_int Batch::update_bounds(const c_float *l, const c_float *u, bool have_l, bool
   if (have_u) CK(cudaMemcpyAsync(D.u, u, bytes, cudaMemcpyHostToDevice, stream));
   c_int rc = reset_info();
   if (rc) return rc;
-  return retype_and_refactor();
+  rc = retype_and_refactor();
+  if (rc) return rc;
+  return pack(0, 2);
 }
 
 c_int Batch::partial_update_bounds(c_int start, c_int stop, const c_float *l, const c_float *u) {
@@ -391,12 +418,16 @@ c_int Batch::partial_update_bounds(c_int start, c_int stop, const c_float *l, co
   if (rc) return rc;
   // The reference re-types the rows but never refactors (src/recursive_ldl.c:160-189, F6),
   // which leaves factor and rho_vec inconsistent when a type changes; we keep them consistent.
-  return retype_and_refactor();
+  rc = retype_and_refactor();
+  if (rc) return rc;
+  return pack(0, 2);
 }
 
 c_int Batch::update_lin_cost(const c_float *q) {
   CK(cudaSetDevice(device));
   CK(cudaMemcpyAsync(D.q, q, (size_t)batch * D.nmax * sizeof(double), cudaMemcpyHostToDevice, stream));
+  c_int rc = pack(0, 2);
+  if (rc) return rc;
   return reset_info();
 }
 
@@ -518,8 +549,15 @@ c_int Batch::update_settings(const OSQPSettings *s) {
 }
 
 double Batch::admm_bytes_per_iteration() const {
-  // per instance and ADMM iteration: the stage factor streamed once forward and once
-  // backward, plus first-read / last-write of the iterates and problem vectors
+  // Algorithmic HBM bytes per instance and ADMM iteration.
+  if (use_stream()) {
+    // streaming kernel: every stage record is streamed once forward ([q|Xinv|Sinv|rho]) and once
+    // backward ([Xinv|Sinv|rho|l|u]); the iterates x,z,y are counted first-read + last-write only
+    const double fwd = D.qa + D.PX + D.PS + D.bb, bwd = D.PX + D.PS + 3.0 * D.bb;
+    return 8.0 * ((N + 1) * (fwd + bwd) + 2.0 * (D.n + 2.0 * D.m));
+  }
+  // generic kernel: the full (unpacked) pivot inverses streamed once forward and once backward,
+  // plus first-read / last-write of the iterates and problem vectors
   const double F = (double)N * ((double)a * a + (double)nx * nx) + (double)nx * nx;
   const double vec = 3.0 * D.n + 7.0 * D.m;  // x(r,w) q ; z(r,w) y(r,w) l u rho
   return 8.0 * (2.0 * F + vec);

@@ -12,6 +12,8 @@ c_int validate_settings(const OSQPSettings *s);
 struct Batch {
   int device = 0;
   bool generic = false;  // osqp_setup path: one dense stage (N == 0)
+  int kernel_choice = 0;   // 0 auto, 1 force the generic (runtime-shape) ADMM kernel
+  bool streaming = false;  // shapes the streaming kernels cover (rldl_stream.cu)
   int nx = 0, nu = 0, ny = 0, nt = 0, a = 0, b = 0, N = 0, Nmax = 0, batch = 0, nmax = 0, mmax = 0;
   OSQPSettings settings;
   ModelDev M;
@@ -40,6 +42,8 @@ struct Batch {
   void set_sizes();
   c_int ensure_stage(size_t doubles);
   c_int factor(int k0, bool only_flagged);
+  c_int pack(int k0, int parts);
+  bool use_stream() const;
   c_int solve();
   c_int retype_and_refactor();
   c_int reset_info();

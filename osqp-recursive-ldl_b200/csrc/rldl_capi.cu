@@ -764,6 +764,12 @@ void rldl_batch_counters(const RLDLBatch *h, double *admm_bytes, double *factor_
   if (factor_bytes) *factor_bytes = h->b->factor_bytes;
   if (launches) *launches = h->b->launches;
 }
+c_int rldl_batch_select_kernel(RLDLBatch *h, c_int which) {
+  HB(h);
+  if (which < 0 || which > 1) return 1;
+  h->b->kernel_choice = (int)which;
+  return 0;
+}
 void *rldl_batch_stream(const RLDLBatch *h) { return (h && h->b) ? (void *)h->b->stream : nullptr; }
 void rldl_batch_free(RLDLBatch *h) {
   if (!h) return;

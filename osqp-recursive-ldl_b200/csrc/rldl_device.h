@@ -40,6 +40,7 @@ struct ModelDev {
   StageClass sc[3];
   const double *val;
   const int *idx;
+  int nval;  // entries in val[] / idx[] (the ELL part is copied to shared memory by the streaming kernels)
 };
 
 struct SettingsDev {
@@ -65,6 +66,14 @@ struct BatchDev {
   double *obj, *pri, *dua, *rho_est;
   int *rho_updates;
   int *fact_flag;          // 0 ok, >0 = 1 + stage of the first non-positive pivot
+  // Streaming layout (rldl_stream.cu): one record per (instance, stage), RS doubles:
+  //   [ q_k (qa) | Xinv_k packed (PX) | Sinv_k packed (PS) | rho_k (bb) | l_k (bb) | u_k (bb) ]
+  // packed = lower triangle, column-major, of the a x a / nx x nx symmetric pivot inverse;
+  // every part is padded to an even number of doubles (16-byte bulk-copy granularity).
+  double *rec;
+  int qa, PX, PS, bb, RS;
+  long long rec_stride;    // (Nmax+1)*RS doubles per instance
+  int *work_counter;       // dynamic instance queue of the persistent ADMM kernel
 };
 
 constexpr int STATUS_FACTOR_ERROR = -7;  // reported as OSQP_NON_CVX

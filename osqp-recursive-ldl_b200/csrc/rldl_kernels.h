@@ -17,4 +17,9 @@ cudaError_t launch_warm_start_z(const ModelDev &M, const BatchDev &B, cudaStream
 cudaError_t launch_fill(double *p, double v, size_t n, cudaStream_t st);
 cudaError_t launch_scatter_rows(double *dst, int ld, const double *src, int len, int start, int batch,
                                 cudaStream_t st);
+// streaming path (rldl_stream.cu)
+bool stream_supported(const ModelDev &M, int N);
+cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, int parts, cudaStream_t st);
+cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
+                               cudaStream_t st);
 }  // namespace rldl

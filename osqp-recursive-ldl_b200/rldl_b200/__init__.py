@@ -111,7 +111,7 @@ osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions clea
 rldl_batch_setup rldl_batch_solve rldl_batch_update_bounds rldl_batch_partial_update_bounds
 rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_update_horizon rldl_batch_update_rho
 rldl_batch_refactor rldl_batch_kkt_solve rldl_batch_get_solution rldl_batch_get_info
-rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream
+rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel
 rldl_batch_free
 rldl_device_count rldl_set_device rldl_version
 """.split()
@@ -183,6 +183,8 @@ def lib():
         fn.argtypes = args
         fn.restype = None if name in ("get_L_dimensions", "rldl_batch_dims", "rldl_batch_last_times",
                                       "rldl_batch_counters", "rldl_batch_free") else c_int
+    L.rldl_batch_select_kernel.argtypes = [vp, c_int]
+    L.rldl_batch_select_kernel.restype = c_int
     L.rldl_batch_stream.argtypes = [vp]
     L.rldl_batch_stream.restype = vp
     for name in ("max_iter", "warm_start", "scaled_termination", "check_termination", "polish",
@@ -311,6 +313,9 @@ class Batch:
         a, f, n = C.c_double(), C.c_double(), c_int()
         lib().rldl_batch_counters(self.h, C.byref(a), C.byref(f), C.byref(n))
         return a.value, f.value, n.value
+
+    def select_kernel(self, which):
+        return lib().rldl_batch_select_kernel(self.h, which)
 
     def stream(self):
         return lib().rldl_batch_stream(self.h)

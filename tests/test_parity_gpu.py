@@ -35,3 +35,19 @@ def test_cold_solve_matches_reference(name, batch):
     bad = compare(out, ref, n, m)
     assert not bad, bad[:5]
     gb.free()
+
+
+@pytest.mark.parametrize("name,batch", [("C1", 70), ("C3", 40), ("C4", 24)])
+def test_streaming_kernel_matches_generic_kernel(name, batch):
+    """The TMA-streaming ADMM kernel and the generic kernel run the same iteration."""
+    mdl, N, x0, q, l, u = problem(name, batch)
+    outs = []
+    for which in (0, 1):
+        gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+        assert gb.select_kernel(which) == 0
+        assert gb.solve() == 0
+        outs.append(gb.get())
+        n, m, _, _ = gb.dims()
+        gb.free()
+    bad = compare(outs[0], outs[1], n, m)
+    assert not bad, bad[:5]
