@@ -260,8 +260,7 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(dalloc(&B->d_changed, bs));
   B->streaming = !generic && stream_supported(B->M, B->N);
   {
-    auto ev = [](int v) { return (v + 1) & ~1; };
-    D.qa = ev(B->a); D.PX = ev(B->a * (B->a + 1) / 2); D.PS = ev(B->nx * (B->nx + 1) / 2); D.bb = ev(B->b);
+    stream_record_dims(B->a, B->nx, B->b, &D.qa, &D.PX, &D.PS, &D.bb);
     D.RS = D.qa + D.PX + D.PS + 3 * D.bb;
     D.rec_stride = (long long)(B->Nmax + 1) * D.RS;
     CK(dalloc(&D.rec, B->streaming ? bs * (size_t)D.rec_stride : 1));

@@ -1,21 +1,29 @@
-// rldl_stream.cu — the HBM-streaming ADMM kernel (sm_100a).
+// rldl_stream.cu — the HBM-streaming ADMM kernel (sm_100a), shape-specialised.
 //
 // One QP instance per group of G lanes (G = 8/16/32, the smallest power of two >= nx+nu),
 // persistent CTAs pulling instances from a device-side queue, the whole osqp_solve loop
 // (reference src/osqp.c:354-627) inside one launch.  Per ADMM iteration an instance walks
 // its N+1 stages forward and backward (the block substitution of SURVEY §8a "block form");
 // each stage step needs that stage's record
-//     [ q_k | Xinv_k packed | Sinv_k packed | rho_k | l_k | u_k ]
+//     [ q_k | Xinv_k | Sinv_k | rho_k | l_k | u_k ]
 // which is immutable during a solve and is streamed HBM -> shared memory by the TMA engine
-// (cp.async.bulk + mbarrier complete_tx) into a per-group ring, D stage steps ahead of the
-// arithmetic, so the dependent chain of small FP64 mat-vecs only ever touches shared memory.
-// The mutable iterates (x, z, y and the forward intermediates) stay in HBM/L2 in the flat
-// per-instance arrays and are register-prefetched one stage step ahead by the lane that
-// owns (wrote) them.
+// (cp.async.bulk + mbarrier complete_tx, SASS UBLKCP) into a per-group ring, D stage steps
+// ahead of the arithmetic, so the dependent chain of small FP64 mat-vecs only ever touches
+// shared memory.  The mutable iterates (x, z, y and the forward intermediates) stay in
+// HBM/L2 in the flat per-instance arrays and are register-prefetched one stage step ahead
+// by the lane that owns (wrote) them.
 //
-// The arithmetic of a stage step is the same as kkt_sweep<> in rldl_device_fn.cuh (same
-// formulas, same summation order); residuals, termination and infeasibility detection are
-// the shared group routines of that header.
+// Symmetric pivot inverses are stored "diagonal-packed": DP[d][i] = M(i, (i+d) mod n) for
+// d = 0..n/2 — half the bytes of the full matrix, and lane i (owner of row i) reads
+// DP[d][i] for the upper wrap and DP[d][(i-d) mod n] for the lower wrap, both conflict-free;
+// the input vector is kept doubled in shared memory so v[(i+d) mod n] is v2[i+d].
+//
+// The kernel is a template over the stage shape (nx+nu, nx, ny, nt) and the ELL width of the
+// path-constraint matrices so that every inner loop unrolls; shapes outside the table at the
+// bottom of this file use the generic kernel in rldl_kernels.cu.  The arithmetic follows
+// kkt_sweep<> in rldl_device_fn.cuh (reference src/auxil.c:164-228, qdldl_interface.c:559-585)
+// except that rho^-1 is a per-class precomputed reciprocal, as in the reference
+// (rho_inv_vec, src/auxil.c:96), instead of a division.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "rldl_device_fn.cuh"
@@ -28,59 +36,32 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)_
 __device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-// 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP); completes on `bar`.
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                   smem_u32(dst)),
-               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+// 1-D bulk async copy global -> shared (TMA engine); completes on `bar`.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
-__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
-  uint32_t ok;
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
-      "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
+      "{\n"
+      ".reg .pred p;\n"
+      "RLDL_WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra RLDL_DONE_%=;\n"
+      "bra RLDL_WAIT_%=;\n"
+      "RLDL_DONE_%=:\n"
+      "}" ::"r"(bar),
+      "r"(parity)
       : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
-  }
 }
 
-// Row `row` of an ELL matrix whose idx/val live in shared memory.
-__device__ __forceinline__ double ell_dot_s(const int *sidx, const double *sval, const Ell &E, int row,
-                                            const double *v) {
-  const int *ix = sidx + E.off + row * E.width;
-  const double *vv = sval + E.off + row * E.width;
-  double s = 0.0;
-  for (int e = 0; e < E.width; e++) s = fma(vv[e], v[ix[e]], s);
-  return s;
-}
-
-// y_i = sum_j M(i,j) v_j for a symmetric n x n matrix stored as its lower triangle,
-// column-major packed: (i,j), i >= j, at j*n - j*(j+1)/2 + i.  Two accumulators over even
-// and odd j, like sym_mv().
-__device__ __forceinline__ double sym_mv_packed(const double *__restrict__ P, int n, int i, const double *v) {
-  const int ci = i * n - (i * (i + 1)) / 2;
-  double s0 = 0.0, s1 = 0.0;
-  int cj = 0;  // j*n - j*(j+1)/2
-  int j = 0;
-  for (; j + 1 < n; j += 2) {
-    const int c1 = cj + n - (j + 1);
-    const int i0 = (j <= i) ? cj + i : ci + j;
-    const int i1 = (j + 1 <= i) ? c1 + i : ci + j + 1;
-    s0 = fma(P[i0], v[j], s0);
-    s1 = fma(P[i1], v[j + 1], s1);
-    cj = c1 + n - (j + 2);
-  }
-  if (j < n) s0 = fma(P[(j <= i) ? cj + i : ci + j], v[j], s0);
-  return s0 + s1;
-}
+__host__ __device__ inline int even_up(int v) { return (v + 1) & ~1; }
+// doubles of the diagonal-packed form of a symmetric n x n matrix
+__host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
 
 // ---------------------------------------------------------------------------
 // Record packing: (Xinv, Sinv, q, l, u, rho_vec) -> rec, stages k0..N of every instance.
@@ -108,29 +89,30 @@ __global__ void k_pack_records(ModelDev M, BatchDev B, int k0, int parts /*bit0 
       continue;
     }
     o -= B.qa;
-    if (o < B.PX) {  // Xinv_k, a x a packed (terminal: [Xinv_N 0; 0 I])
+    if (o < B.PX) {  // Xinv_k, a x a diagonal-packed (terminal: [Xinv_N 0; 0 I])
       if (!(parts & 1)) continue;
       double v = 0.0;
-      if (o < (a * (a + 1)) / 2) {
-        int j = 0, cs = 0;  // column start
-        while (o >= cs + (a - j)) { cs += a - j; j++; }
-        const int i = j + (o - cs);
+      if (o < dp_size(a)) {
+        const int d = o / a, i = o - d * a;
+        int j = i + d;
+        if (j >= a) j -= a;
         const double *Xk = B.Xinv + (size_t)inst * B.xstride + (size_t)k * a * a;
-        if (!term) v = Xk[j * a + i];
-        else v = (i < nx && j < nx) ? Xk[j * nx + i] : (i == j ? 1.0 : 0.0);
+        if (!term) v = (i >= j) ? Xk[j * a + i] : Xk[i * a + j];  // lower triangle of the stored inverse
+        else v = (i < nx && j < nx) ? ((i >= j) ? Xk[j * nx + i] : Xk[i * nx + j]) : (i == j ? 1.0 : 0.0);
       }
       *dst = v;
       continue;
     }
     o -= B.PX;
-    if (o < B.PS) {  // Sinv_k, nx x nx packed
+    if (o < B.PS) {  // Sinv_k, nx x nx diagonal-packed
       if (!(parts & 1)) continue;
       double v = 0.0;
-      if (!term && o < (nx * (nx + 1)) / 2) {
-        int j = 0, cs = 0;
-        while (o >= cs + (nx - j)) { cs += nx - j; j++; }
-        const int i = j + (o - cs);
-        v = B.Sinv[(size_t)inst * B.sstride + (size_t)k * nx * nx + j * nx + i];
+      if (!term && o < dp_size(nx)) {
+        const int d = o / nx, i = o - d * nx;
+        int j = i + d;
+        if (j >= nx) j -= nx;
+        const double *Sk = B.Sinv + (size_t)inst * B.sstride + (size_t)k * nx * nx;
+        v = (i >= j) ? Sk[j * nx + i] : Sk[i * nx + j];
       }
       *dst = v;
       continue;
@@ -157,105 +139,188 @@ cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, in
   return cudaGetLastError();
 }
 
+void stream_record_dims(int a, int nx, int b, int *qa, int *PX, int *PS, int *bb) {
+  *qa = even_up(a);
+  *PX = even_up(dp_size(a));
+  *PS = even_up(dp_size(nx));
+  *bb = even_up(b);
+}
+
 // ---------------------------------------------------------------------------
-// The persistent streaming ADMM kernel.
+// Compile-time shape of one specialisation
 // ---------------------------------------------------------------------------
+template <int A_, int NX_, int NY_, int NT_, int CW_>
+struct Shape {
+  static constexpr int A = A_, NX = NX_, NY = NY_, NT = NT_, CW = CW_;
+  static constexpr int B = NX + NY;
+  static constexpr int G = A <= 8 ? 8 : (A <= 16 ? 16 : 32);
+  static constexpr int GPW = 32 / G;
+  static constexpr int RMAX = NY > NT ? NY : NT;
+  static constexpr int NYT = (RMAX + G - 1) / G;
+  static constexpr int ROWS = NYT * G;
+  static constexpr int QA = (A + 1) & ~1, PX = ((A / 2 + 1) * A + 1) & ~1, PS = ((NX / 2 + 1) * NX + 1) & ~1,
+                       BB = (B + 1) & ~1;
+  static constexpr int RS = QA + PX + PS + 3 * BB;
+  static constexpr int XOFF = QA, SOFF = QA + PX, RHO = QA + PX + PS, LO = RHO + BB, UP = LO + BB;
+  static constexpr uint32_t FWD_BYTES = 8u * (QA + PX + PS + BB), BWD_BYTES = 8u * (PX + PS + 3 * BB);
+  // per-group scratch (doubles, every block even-sized)
+  static constexpr int AE = (A + 1) & ~1, NXE = (NX + 1) & ~1;
+  static constexpr int O_W = 0, O_TV2 = O_W + ROWS, O_YV = O_TV2 + 2 * AE, O_TD2 = O_YV + AE, O_SP = O_TD2 + 2 * NXE,
+                       O_VN2 = O_SP + NXE, O_VC = O_VN2 + 2 * NXE, O_NUD = O_VC + AE, O_GG2 = O_NUD + NXE,
+                       SC_SWEEP = O_GG2 + 2 * AE;
+  static constexpr int VM = (A > RMAX ? A : RMAX);
+  static constexpr int SC = SC_SWEEP > 8 * VM ? SC_SWEEP : 8 * VM;
+  // CTA-shared model block (doubles)
+  static constexpr int M_FD = 0, M_FDT = M_FD + 2 * A * NX, M_CV = M_FDT + 2 * A * NX, M_CTV = M_CV + 3 * ROWS * CW,
+                       M_CI = M_CTV + 3 * AE * CW,                       // ints from here: 3*ROWS*CW
+                       M_CTI = M_CI + (3 * ROWS * CW + 1) / 2,            // ints: 3*AE*CW
+                       M_END = (M_CTI + (3 * AE * CW + 1) / 2 + 1) & ~1;
+  static constexpr int WNX = (A - 1 - A / 2) > 0 ? (A - 1 - A / 2) : 1;
+  static constexpr int WNS = (NX - 1 - NX / 2) > 0 ? (NX - 1 - NX / 2) : 1;
+  __host__ __device__ static int group_doubles(int D) { return ((D * RS + D + SC) + 1) & ~1; }
+};
+
+// y_i = sum_j M(i,j) v_j from the diagonal-packed form.  Dpi = DP + i, v2i = v2 + i (v doubled),
+// wrap[d-1] = d*N + (i-d) mod N.
+template <int N, int WN>
+__device__ __forceinline__ double dmv(const double *__restrict__ Dp, const double *__restrict__ Dpi,
+                                      const double *__restrict__ v2i, const int (&wrap)[WN]) {
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+  for (int d = 0; d <= N / 2; d++) acc[d & 3] = fma(Dpi[d * N], v2i[d], acc[d & 3]);
+#pragma unroll
+  for (int d = 1; d <= N - 1 - N / 2; d++)
+    acc[(N / 2 + d) & 3] = fma(Dp[wrap[d - 1]], v2i[N - d], acc[(N / 2 + d) & 3]);
+  return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
+// sum_j Mcol[j*LD] * v[j], j < NJ  (Mcol already offset by the lane's row)
+template <int NJ, int LD>
+__device__ __forceinline__ double dense_mv(const double *__restrict__ Mcol, const double *__restrict__ v) {
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+  for (int j = 0; j < NJ; j++) acc[j & 3] = fma(Mcol[j * LD], v[j], acc[j & 3]);
+  return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
+template <int CW>
+__device__ __forceinline__ double ell_row(const double *__restrict__ val, const int *__restrict__ idx, int row,
+                                          const double *__restrict__ v) {
+  double s = 0.0;
+#pragma unroll
+  for (int e = 0; e < CW; e++) s = fma(val[row * CW + e], v[idx[row * CW + e]], s);
+  return s;
+}
+
 template <int NYT>
 struct MutVec {  // the mutable per-stage values a lane owns
   double x, zd, yd, yk, sk;
   double zp[NYT], yp[NYT];
 };
 
-struct StreamSmem {  // per-CTA shared memory carve-up (in doubles unless noted)
-  int model_val;     // ELL values copy
-  int model_idx;     // ELL indices copy (ints, stored after the doubles)
-  int group0;        // first per-group block
-  int group_stride;  // doubles per group
-  int ring;          // offset of ring inside the group block
-  int bars;          // offset of the D mbarriers inside the group block
-  int scratch;       // offset of scratch vectors inside the group block
-};
-
-__host__ __device__ inline int even_up(int v) { return (v + 1) & ~1; }
-
-__host__ __device__ inline StreamSmem stream_smem_layout(int nval, int RS, int D, int G, int NYT, int vm,
-                                                         int groups) {
-  StreamSmem L;
-  L.model_val = 0;
-  L.model_idx = even_up(nval);
-  L.group0 = L.model_idx + even_up((nval + 1) / 2);
-  L.ring = 0;
-  L.bars = D * RS;
-  L.scratch = L.bars + D;
-  int sc = (NYT + 9) * G;
-  if (8 * vm > sc) sc = 8 * vm;
-  L.group_stride = even_up(L.scratch + sc);
-  (void)groups;
-  return L;
-}
-
-template <int G, int NYT>
+// ---------------------------------------------------------------------------
+// The persistent streaming ADMM kernel
+// ---------------------------------------------------------------------------
+template <class SH>
 __global__ void __launch_bounds__(128) k_admm_stream(ModelDev M, BatchDev B, SettingsDev S, int warm_start, int D) {
+  constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, NT = SH::NT, CW = SH::CW, G = SH::G, NYT = SH::NYT,
+                ROWS = SH::ROWS, RS = SH::RS, BQ = SH::B;
   extern __shared__ __align__(16) double smem[];
-  constexpr int GPW = 32 / G;  // groups per warp
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int gl = lane & (G - 1), gw = lane / G;
   const unsigned gm = (G == 32) ? FULL : (((1u << G) - 1u) << (gw * G));
-  const int grp = wid * GPW + gw;
-  const int nx = M.nx, a = M.a, b = M.b, ny = M.ny, nt = M.nt, N = B.N, n = B.n, m = B.m;
-  int vm = a;
-  if (ny > vm) vm = ny;
-  if (nt > vm) vm = nt;
-  if (nx > vm) vm = nx;
-  const StreamSmem L = stream_smem_layout(M.nval, B.RS, D, G, NYT, vm, (blockDim.x >> 5) * GPW);
+  const int grp = wid * SH::GPW + gw;
+  const int N = B.N, n = B.n, m = B.m;
 
-  // CTA-shared copy of the model's ELL part
-  double *sval = smem + L.model_val;
-  int *sidx = reinterpret_cast<int *>(smem + L.model_idx);
-  for (int e = threadIdx.x; e < M.nval; e += blockDim.x) {
-    sval[e] = M.val[e];
-    sidx[e] = M.idx[e];
+  // ---- CTA-shared model block: dense dynamics rows F (class 0 / 1) and padded ELL of C, C' ----
+  double *Fd = smem + SH::M_FD, *FdT = smem + SH::M_FDT, *Cv = smem + SH::M_CV, *Ctv = smem + SH::M_CTV;
+  int *Ci = reinterpret_cast<int *>(smem + SH::M_CI), *Cti = reinterpret_cast<int *>(smem + SH::M_CTI);
+  for (int e = threadIdx.x; e < SH::M_END; e += blockDim.x) smem[e] = 0.0;
+  __syncthreads();
+  for (int t = threadIdx.x; t < 2 * NX; t += blockDim.x) {  // F rows of class 0 and 1
+    const int c = t / NX, r = t - c * NX;
+    const Ell &E = M.sc[c].F;
+    for (int e = 0; e < E.width; e++) {
+      const double v = M.val[E.off + r * E.width + e];
+      const int j = M.idx[E.off + r * E.width + e];
+      if (v != 0.0) {
+        Fd[c * A * NX + j * NX + r] = v;
+        FdT[c * A * NX + r * A + j] = v;
+      }
+    }
   }
-  double *gb = smem + L.group0 + (size_t)grp * L.group_stride;
-  double *ring = gb + L.ring;
-  uint64_t *bars = reinterpret_cast<uint64_t *>(gb + L.bars);
-  double *sc = gb + L.scratch;
-  double *w = sc, *tv = sc + NYT * G, *yvs = tv + G, *td = yvs + G, *sp = td + G, *nudv = sp + G,
-         *gg = nudv + G, *vb0 = gg + G, *vb1 = vb0 + G;
-  const Scratch rs = make_scratch(sc, vm);  // residual routines alias the sweep scratch
+  for (int t = threadIdx.x; t < 3 * ROWS; t += blockDim.x) {  // C rows
+    const int c = t / ROWS, r = t - c * ROWS;
+    const Ell &E = M.sc[c].C;
+    if (r < E.rows)
+      for (int e = 0; e < E.width && e < CW; e++) {
+        Cv[t * CW + e] = M.val[E.off + r * E.width + e];
+        Ci[t * CW + e] = M.idx[E.off + r * E.width + e];
+      }
+  }
+  for (int t = threadIdx.x; t < 3 * SH::AE; t += blockDim.x) {  // C' rows
+    const int c = t / SH::AE, r = t - c * SH::AE;
+    const Ell &E = M.sc[c].Ct;
+    if (r < E.rows)
+      for (int e = 0; e < E.width && e < CW; e++) {
+        Ctv[t * CW + e] = M.val[E.off + r * E.width + e];
+        Cti[t * CW + e] = M.idx[E.off + r * E.width + e];
+      }
+  }
+
+  // ---- per-group block: ring, barriers, scratch ----
+  double *gb = smem + SH::M_END + (size_t)grp * SH::group_doubles(D);
+  double *ring = gb;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(gb + D * RS);
+  double *sc = gb + D * RS + D;
+  double *w = sc + SH::O_W, *tv2 = sc + SH::O_TV2, *yvs = sc + SH::O_YV, *td2 = sc + SH::O_TD2, *sp = sc + SH::O_SP,
+         *vn2 = sc + SH::O_VN2, *vcur = sc + SH::O_VC, *nudv = sc + SH::O_NUD, *gg2 = sc + SH::O_GG2;
+  const Scratch rs = make_scratch(sc, SH::VM);  // residual routines alias the sweep scratch
   if (gl == 0)
     for (int d = 0; d < D; d++) mbar_init(&bars[d], 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
+  const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
 
-  const int qa = B.qa, PX = B.PX, PS = B.PS, bb = B.bb, RS = B.RS;
+  // lane constants of the diagonal-packed mat-vecs
+  int wrapX[SH::WNX], wrapS[SH::WNS];
+#pragma unroll
+  for (int d = 1; d <= A - 1 - A / 2; d++) wrapX[d - 1] = d * A + ((gl < A ? gl : 0) - d + A) % A;
+#pragma unroll
+  for (int d = 1; d <= NX - 1 - NX / 2; d++) wrapS[d - 1] = d * NX + ((gl < NX ? gl : 0) - d + NX) % NX;
+
   const int npos = 2 * (N + 1);
-  const uint32_t fwd_bytes = 8u * (qa + PX + PS + bb), bwd_bytes = 8u * (PX + PS + 3 * bb);
-  const double sigma = S.sigma, alpha = S.alpha;
-  uint32_t pk = 0;  // packets consumed so far by this group (ring position)
+  const double sigma = S.sigma, alpha = S.alpha, oma = 1.0 - S.alpha;
+  // ring state: consumer slot/phase, and the position (0..npos-1) of the next packet to issue
+  int slot = 0, ipos = 0;
+  uint32_t phase = 0;
 
   // per-instance state
   int inst = -1, iter = 0;
   bool have = false;
   const double *recb = nullptr;
   double *x = nullptr, *z = nullptr, *y = nullptr, *dx = nullptr, *dy = nullptr, *ykg = nullptr, *skg = nullptr;
+  double rho_in = 0.0, rho_eq = 0.0, inv_in = 0.0, inv_eq = 0.0, inv_min = 0.0;
   MutVec<NYT> cur;
 
-  auto issue = [&](int pos, uint32_t pidx) {  // group leader only
-    const int slot = pidx % D;
-    const bool fwd = pos <= N;
-    const int k = fwd ? pos : npos - 1 - pos;
-    const double *src = recb + (size_t)k * RS + (fwd ? 0 : qa);
-    const uint32_t bytes = fwd ? fwd_bytes : bwd_bytes;
-    mbar_expect_tx(&bars[slot], bytes);
-    bulk_g2s(ring + slot * RS + (fwd ? 0 : qa), src, bytes, &bars[slot]);
+  auto rinv_of = [&](double rv) -> double {  // reciprocal of a rho_vec entry (one of three classes)
+    return rv == rho_in ? inv_in : (rv == rho_eq ? inv_eq : (rv == kRhoMin ? inv_min : 1.0 / rv));
   };
-  auto load_mv = [&](MutVec<NYT> &r, int pos) {
-    const bool fwd = pos <= N;
-    const int k = fwd ? pos : npos - 1 - pos;
+  // leader only: issue the packet at position ipos into ring slot `s`, advance ipos
+  auto issue = [&](int s) {
+    const bool fwd = ipos <= N;
+    const int k = fwd ? ipos : npos - 1 - ipos;
+    const double *src = recb + (size_t)k * RS + (fwd ? 0 : SH::XOFF);
+    const uint32_t bytes = fwd ? SH::FWD_BYTES : SH::BWD_BYTES;
+    const uint32_t bar = bars_s + 8u * s;
+    mbar_expect_tx(bar, bytes);
+    bulk_g2s(ring_s + 8u * (s * RS + (fwd ? 0 : SH::XOFF)), src, bytes, bar);
+    ipos = (ipos + 1 == npos) ? 0 : ipos + 1;
+  };
+  auto load_mv = [&](MutVec<NYT> &r, int k, bool bwd) {
     const bool term = (k == N);
-    const int dim = term ? nx : a, np = term ? nt : ny;
-    const int xoff = k * a - nx, roff = k * b, ilo = (k == 0) ? nx : 0;
+    const int dim = term ? NX : A, np = term ? NT : NY;
+    const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
     r.x = (gl >= ilo && gl < dim) ? x[xoff + gl] : 0.0;
 #pragma unroll
     for (int t = 0; t < NYT; t++) {
@@ -264,10 +329,10 @@ __global__ void __launch_bounds__(128) k_admm_stream(ModelDev M, BatchDev B, Set
       if (rr < np) { r.zp[t] = z[roff + rr]; r.yp[t] = y[roff + rr]; }
     }
     r.zd = r.yd = r.yk = r.sk = 0.0;
-    if (!term && gl < nx) { r.zd = z[roff + ny + gl]; r.yd = y[roff + ny + gl]; }
-    if (!fwd && !term) {
-      if (gl < a) r.yk = ykg[k * a + gl];
-      if (gl < nx) r.sk = skg[k * nx + gl];
+    if (!term && gl < NX) { r.zd = z[roff + NY + gl]; r.yd = y[roff + NY + gl]; }
+    if (bwd && !term) {
+      if (gl < A) r.yk = ykg[k * A + gl];
+      if (gl < NX) r.sk = skg[k * NX + gl];
     }
   };
   // claim the next instance of the queue; sets up pointers, cold start, ring and registers
@@ -288,21 +353,38 @@ __global__ void __launch_bounds__(128) k_admm_stream(ModelDev M, BatchDev B, Set
     x = B.x + vo; z = B.z + ro; y = B.y + ro; dx = B.dx + vo; dy = B.dy + ro;
     ykg = B.yk + (size_t)inst * B.ykstride; skg = B.sk + (size_t)inst * B.skstride;
     recb = B.rec + (size_t)inst * B.rec_stride;
-    if (gl == 0)
-      for (int d = 0; d < D; d++) issue(d % npos, pk + d);
+    rho_in = B.rho[inst]; rho_eq = kRhoEq * rho_in;
+    inv_in = 1.0 / rho_in; inv_eq = 1.0 / rho_eq; inv_min = 1.0 / kRhoMin;
+    ipos = 0;
+    if (gl == 0) {
+      int s = slot;
+      for (int d = 0; d < D; d++) {
+        issue(s);
+        s = (s + 1 == D) ? 0 : s + 1;
+      }
+    }
+    ipos = __shfl_sync(gm, ipos, 0, G);
     if (!warm_start) {
       for (int i = gl; i < n; i += G) x[i] = 0.0;
       for (int r = gl; r < m; r += G) { z[r] = 0.0; y[r] = 0.0; }
     }
     __syncwarp(gm);
     iter = 0;
-    load_mv(cur, 0);
+    load_mv(cur, 0, false);
     return true;
+  };
+  auto consume_wait = [&]() { mbar_wait(bars_s + 8u * slot, phase); };
+  auto consume_done = [&]() {  // whole group has finished reading the slot: refill it D packets ahead
+    if (gl == 0) issue(slot);
+    else ipos = (ipos + 1 == npos) ? 0 : ipos + 1;
+    slot++;
+    if (slot == D) { slot = 0; phase ^= 1u; }
   };
   auto drain = [&]() {  // consume the D packets still in flight for the finished instance
     for (int d = 0; d < D; d++) {
-      mbar_wait(&bars[pk % D], (pk / D) & 1);
-      pk++;
+      consume_wait();
+      slot++;
+      if (slot == D) { slot = 0; phase ^= 1u; }
     }
     __syncwarp(gm);
   };
@@ -313,123 +395,124 @@ __global__ void __launch_bounds__(128) k_admm_stream(ModelDev M, BatchDev B, Set
       iter++;
       const bool can_check = S.check_termination && (iter % S.check_termination == 0);
       const bool store_delta = can_check || iter == S.max_iter;
-      double yv_reg = 0.0;  // this lane's y-vector entry of the last forward stage
-      int par = 0;
-      for (int pos = 0; pos < npos; pos++) {
-        const bool fwd = pos <= N;
-        const int k = fwd ? pos : npos - 1 - pos;
+      double yv_reg = 0.0;  // this lane's entry of Xinv*t of the last forward stage
+      MutVec<NYT> nxt;
+      // =============================== forward sweep ===============================
+      for (int k = 0; k <= N; k++) {
         const bool term = (k == N);
-        const StageClass &scl = M.sc[term ? 2 : (k == 0 ? 0 : 1)];
-        const int dim = term ? nx : a, np = term ? nt : ny;
-        const int xoff = k * a - nx, roff = k * b, ilo = (k == 0) ? nx : 0;
-        MutVec<NYT> nxt;
-        if (pos + 1 < npos) load_mv(nxt, pos + 1);
-        const double *slot = ring + (pk % D) * RS;
-        const double *sq = slot, *sX = slot + qa, *sS = sX + PX, *srho = sS + PS, *sl = srho + bb, *su = sl + bb;
-        mbar_wait(&bars[pk % D], (pk / D) & 1);
-        if (fwd) {
-          // ---- forward stage step (kkt_sweep<> forward, rldl_device_fn.cuh) ----
-          double g = 0.0;
-          if (gl >= ilo && gl < dim) g = sigma * cur.x - sq[gl];
+        const int cls = term ? 2 : (k == 0 ? 0 : 1);
+        const int dim = term ? NX : A, np = term ? NT : NY;
+        const int ilo = (k == 0) ? NX : 0;
+        if (!term) load_mv(nxt, k + 1, false);
+        else load_mv(nxt, N, true);
+        const double *sl_ = ring + slot * RS;
+        consume_wait();
+        double g = 0.0;
+        if (gl >= ilo && gl < dim) g = sigma * cur.x - sl_[gl];
 #pragma unroll
-          for (int t = 0; t < NYT; t++) {
-            const int rr = gl + G * t;
-            if (rr < np) w[rr] = srho[rr] * cur.zp[t] - cur.yp[t];
-          }
-          __syncwarp(gm);
-          double tt = 0.0;
-          if (gl < dim) {
-            tt = g + ell_dot_s(sidx, sval, scl.Ct, gl, w);
-            if (k > 0 && gl < nx) tt -= sp[gl];
-          }
-          tv[gl] = tt;
-          __syncwarp(gm);
-          double yvv = 0.0;
-          if (gl < a) yvv = sym_mv_packed(sX, a, gl, tv);
+        for (int t = 0; t < NYT; t++) {
+          const int rr = gl + G * t;
+          if (rr < np) w[rr] = sl_[SH::RHO + rr] * cur.zp[t] - cur.yp[t];
+        }
+        __syncwarp(gm);
+        double tt = 0.0;
+        if (gl < dim) {
+          tt = g + ell_row<CW>(Ctv + cls * SH::AE * CW, Cti + cls * SH::AE * CW, gl, w);
+          if (k > 0 && gl < NX) tt -= sp[gl];
+        }
+        if (gl < A) { tv2[gl] = tt; tv2[gl + A] = tt; }
+        __syncwarp(gm);
+        double yvv = 0.0;
+        if (gl < A) {
+          yvv = dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, tv2 + gl, wrapX);
           yvs[gl] = yvv;
-          yv_reg = yvv;
-          if (gl < dim) ykg[k * a + gl] = yvv;
+          if (gl < dim) ykg[k * A + gl] = yvv;
+        }
+        yv_reg = yvv;
+        __syncwarp(gm);
+        if (!term) {
+          if (gl < NX) {
+            const double ri = rinv_of(sl_[SH::RHO + NY + gl]);
+            const double tdv = (cur.zd - cur.yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
+            td2[gl] = tdv; td2[gl + NX] = tdv;
+          }
           __syncwarp(gm);
-          if (!term) {
-            if (gl < nx) {
-              const double rd = srho[ny + gl];
-              td[gl] = (cur.zd - cur.yd / rd) - ell_dot_s(sidx, sval, scl.F, gl, yvs);
-            }
-            __syncwarp(gm);
-            if (gl < nx) {
-              const double s = sym_mv_packed(sS, nx, gl, td);
-              sp[gl] = s;
-              skg[k * nx + gl] = s;
-            }
-            __syncwarp(gm);
+          if (gl < NX) {
+            const double sv = dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, td2 + gl, wrapS);
+            sp[gl] = sv;
+            skg[k * NX + gl] = sv;
           }
+          __syncwarp(gm);
+        }
+        consume_done();
+        cur = nxt;
+      }
+      // =============================== backward sweep ==============================
+      for (int k = N; k >= 0; k--) {
+        const bool term = (k == N);
+        const int cls = term ? 2 : (k == 0 ? 0 : 1);
+        const int dim = term ? NX : A, np = term ? NT : NY;
+        const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
+        if (k > 0) load_mv(nxt, k - 1, true);
+        const double *sl_ = ring + slot * RS;
+        consume_wait();
+        double vv = 0.0, nud = 0.0;
+        if (term) {
+          vv = yv_reg;
         } else {
-          // ---- backward stage step (kkt_sweep<> backward) ----
-          double *vcur = par ? vb1 : vb0;
-          const double *vprev = par ? vb0 : vb1;
-          double vv = 0.0, nud = 0.0;
-          if (term) {
-            vv = yv_reg;
-            vcur[gl] = vv;
-            __syncwarp(gm);
-          } else {
-            if (gl < nx) {
-              nud = -(cur.sk + sym_mv_packed(sS, nx, gl, vprev));
-              nudv[gl] = nud;
-            }
-            __syncwarp(gm);
-            if (gl < a) gg[gl] = ell_dot_s(sidx, sval, scl.Ft, gl, nudv);
-            __syncwarp(gm);
-            if (gl < a) vv = cur.yk - sym_mv_packed(sX, a, gl, gg);
-            vcur[gl] = vv;
-            __syncwarp(gm);
+          if (gl < NX) {
+            nud = -(cur.sk + dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, vn2 + gl, wrapS));
+            nudv[gl] = nud;
           }
-          MutVec<NYT> nw = cur;  // new iterate values of this stage (carried into forward stage 0)
+          __syncwarp(gm);
+          if (gl < A) {
+            const double ggv = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, nudv);
+            gg2[gl] = ggv; gg2[gl + A] = ggv;
+          }
+          __syncwarp(gm);
+          if (gl < A) vv = cur.yk - dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
+        }
+        if (gl < A) vcur[gl] = vv;
+        if (gl < NX) { vn2[gl] = vv; vn2[gl + NX] = vv; }
+        __syncwarp(gm);
+        MutVec<NYT> nw = cur;  // new iterate values of this stage (stage 0: carried into the next forward sweep)
 #pragma unroll
-          for (int t = 0; t < NYT; t++) {
-            const int rr = gl + G * t;
-            if (rr < np) {
-              const int ri = roff + rr;
-              const double zt = ell_dot_s(sidx, sval, scl.C, rr, vcur);
-              const double rho = srho[rr], zo = cur.zp[t], yo = cur.yp[t];
-              const double zh = alpha * zt + (1.0 - alpha) * zo;
-              const double zn = fmin(fmax(zh + yo / rho, sl[rr]), su[rr]);
-              const double d = rho * (zh - zn);
-              z[ri] = zn; y[ri] = yo + d;
-              nw.zp[t] = zn; nw.yp[t] = yo + d;
-              if (store_delta) dy[ri] = d;
-            }
-          }
-          if (!term && gl < nx) {
-            const int ri = roff + ny + gl;
-            const double rho = srho[ny + gl];
-            const double zo = cur.zd, yo = cur.yd;
-            const double zt = (zo - yo / rho) + nud / rho;
-            const double zh = alpha * zt + (1.0 - alpha) * zo;
-            const double zn = fmin(fmax(zh + yo / rho, sl[ny + gl]), su[ny + gl]);
+        for (int t = 0; t < NYT; t++) {
+          const int rr = gl + G * t;
+          if (rr < np) {
+            const int ri = roff + rr;
+            const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
+            const double rho = sl_[SH::RHO + rr], rinv = rinv_of(rho), zo = cur.zp[t], yo = cur.yp[t];
+            const double zh = alpha * zt + oma * zo;
+            const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
             z[ri] = zn; y[ri] = yo + d;
-            nw.zd = zn; nw.yd = yo + d;
+            nw.zp[t] = zn; nw.yp[t] = yo + d;
             if (store_delta) dy[ri] = d;
           }
-          if (gl >= ilo && gl < dim) {
-            const double xo = cur.x;
-            const double xn = alpha * vv + (1.0 - alpha) * xo;
-            x[xoff + gl] = xn;
-            nw.x = xn;
-            if (store_delta) dx[xoff + gl] = xn - xo;
-          }
-          par ^= 1;
-          if (pos + 1 == npos) nxt = nw;  // stage 0 feeds the next iteration's forward stage 0
-          __syncwarp(gm);
         }
-        // slot consumed by the whole group: refill it D packets ahead
-        if (gl == 0) {
-          int ip = pos + D;
-          while (ip >= npos) ip -= npos;
-          issue(ip, pk + D);
+        if (!term && gl < NX) {
+          const int ri = roff + NY + gl;
+          const double rho = sl_[SH::RHO + NY + gl], rinv = rinv_of(rho);
+          const double zo = cur.zd, yo = cur.yd;
+          const double zt = (zo - yo * rinv) + nud * rinv;
+          const double zh = alpha * zt + oma * zo;
+          const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
+          const double d = rho * (zh - zn);
+          z[ri] = zn; y[ri] = yo + d;
+          nw.zd = zn; nw.yd = yo + d;
+          if (store_delta) dy[ri] = d;
         }
-        pk++;
+        if (gl >= ilo && gl < dim) {
+          const double xo = cur.x;
+          const double xn = alpha * vv + oma * xo;
+          x[xoff + gl] = xn;
+          nw.x = xn;
+          if (store_delta) dx[xoff + gl] = xn - xo;
+        }
+        if (k == 0) nxt = nw;
+        __syncwarp(gm);
+        consume_done();
         cur = nxt;
       }
       // ---- iteration epilogue: residuals, termination (osqp.c:426-457, 524-567) ----
@@ -454,10 +537,9 @@ __global__ void __launch_bounds__(128) k_admm_stream(ModelDev M, BatchDev B, Set
         done = true;
       }
       if (done) {
-        const double rho = B.rho[inst];
         const bool has_sol = !(status == -3 || status == 3 || status == -4 || status == 4 || status == -7);
         if (has_sol) obj = R.obj;
-        const double rho_est = rho_estimate(R, rho);
+        const double rho_est = rho_estimate(R, rho_in);
         if (!has_sol) {  // store_solution (auxil.c:527-563)
           if (status == -3 || status == 3) {
             double nrm = 0.0;
@@ -493,34 +575,15 @@ __global__ void __launch_bounds__(128) k_admm_stream(ModelDev M, BatchDev B, Set
 }
 
 // ------------------------------- launcher --------------------------------
-int stream_group_lanes(int a) { return a <= 8 ? 8 : (a <= 16 ? 16 : (a <= 32 ? 32 : 0)); }
-
-bool stream_supported(const ModelDev &M, int N) {
-  const int G = stream_group_lanes(M.a);
-  if (!G || N < 1) return false;
-  const int rows = M.ny > M.nt ? M.ny : M.nt;
-  return (rows + G - 1) / G <= 4 && M.nx <= G && M.nu >= 0;
-}
-
-template <int G, int NYT>
+template <class SH>
 static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                                    cudaStream_t st) {
-  const int threads = 128, groups = (threads / 32) * (32 / G);
-  int vm = M.a;
-  if (M.ny > vm) vm = M.ny;
-  if (M.nt > vm) vm = M.nt;
-  if (M.nx > vm) vm = M.nx;
-  int D = 4;
+  const int threads = 128, groups = (threads / 32) * SH::GPW;
+  int D = 3;
   if (D > 2 * (B.N + 1)) D = 2 * (B.N + 1);
-  StreamSmem L = stream_smem_layout(M.nval, B.RS, D, G, NYT, vm, groups);
-  size_t shm = ((size_t)L.group0 + (size_t)groups * L.group_stride) * sizeof(double);
-  while (shm > 220 * 1024 && D > 2) {
-    D--;
-    L = stream_smem_layout(M.nval, B.RS, D, G, NYT, vm, groups);
-    shm = ((size_t)L.group0 + (size_t)groups * L.group_stride) * sizeof(double);
-  }
+  const size_t shm = ((size_t)SH::M_END + (size_t)groups * SH::group_doubles(D)) * sizeof(double);
   if (shm > 220 * 1024) return cudaErrorInvalidValue;
-  auto kern = k_admm_stream<G, NYT>;
+  auto kern = k_admm_stream<SH>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm);
   if (e != cudaSuccess) return e;
   int dev = 0, sms = 148, per_sm = 1;
@@ -538,17 +601,39 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   return cudaGetLastError();
 }
 
+// The specialisation table: (nx+nu, nx, ny, nt, ELL width of C) of the BASELINE.json shapes.
+#define RLDL_SHAPES(X) \
+  X(6, 4, 6, 4, 1)     \
+  X(16, 12, 16, 12, 1) \
+  X(11, 8, 11, 8, 1)
+
+static int max_c_width(const ModelDev &M) {
+  int wdt = 0;
+  for (int c = 0; c < 3; c++) {
+    if (M.sc[c].C.width > wdt) wdt = M.sc[c].C.width;
+    if (M.sc[c].Ct.width > wdt) wdt = M.sc[c].Ct.width;
+  }
+  return wdt;
+}
+
+bool stream_supported(const ModelDev &M, int N) {
+  if (N < 1) return false;
+  const int cw = max_c_width(M);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_) \
+  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_) return true;
+  RLDL_SHAPES(RLDL_X)
+#undef RLDL_X
+  return false;
+}
+
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                                cudaStream_t st) {
-  const int G = stream_group_lanes(M.a);
-  const int rows = M.ny > M.nt ? M.ny : M.nt;
-  const int nyt = (rows + G - 1) / G;
-#define RLDL_CASE(g, t) \
-  if (G == g && nyt == t) return launch_stream_t<g, t>(M, B, S, warm_start, st);
-  RLDL_CASE(8, 1) RLDL_CASE(8, 2) RLDL_CASE(8, 3) RLDL_CASE(8, 4)
-  RLDL_CASE(16, 1) RLDL_CASE(16, 2) RLDL_CASE(16, 3) RLDL_CASE(16, 4)
-  RLDL_CASE(32, 1) RLDL_CASE(32, 2) RLDL_CASE(32, 3) RLDL_CASE(32, 4)
-#undef RLDL_CASE
+  const int cw = max_c_width(M);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_)                                          \
+  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_)      \
+    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, S, warm_start, st);
+  RLDL_SHAPES(RLDL_X)
+#undef RLDL_X
   return cudaErrorInvalidValue;
 }
 
