@@ -103,6 +103,7 @@ static int setup_one(RefBatch *h, c_int k) {
     setup_AP_matrices(d, h->Nmax, h->N, h->nx, h->nu, h->ny, h->nt, h->mats[0], h->mats[1],
                       h->mats[2], h->mats[3], h->mats[4], h->mats[5], h->mats[6]);
     d->n = h->N * a; d->m = h->N * b + h->nt;
+    d->P->n = d->P->m = d->n; d->A->n = d->n; d->A->m = d->m; /* current horizon, not Nmax */
     d->P->nzmax = d->P->p[d->n]; d->A->nzmax = d->A->p[d->n];
     d->q = h->q + k * h->nmax; d->l = h->l + k * h->mmax; d->u = h->u + k * h->mmax;
     h->sdata[k] = d;

@@ -26,6 +26,7 @@
 // (rho_inv_vec, src/auxil.c:96), instead of a division.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include "rldl_device_fn.cuh"
 #include "rldl_kernels.h"
 
@@ -222,7 +223,7 @@ struct MutVec {  // the mutable per-stage values a lane owns
 // The persistent streaming ADMM kernel
 // ---------------------------------------------------------------------------
 template <class SH>
-__global__ void __launch_bounds__(128) k_admm_stream(ModelDev M, BatchDev B, SettingsDev S, int warm_start, int D) {
+__global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, SettingsDev S, int warm_start, int D) {
   constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, NT = SH::NT, CW = SH::CW, G = SH::G, NYT = SH::NYT,
                 ROWS = SH::ROWS, RS = SH::RS, BQ = SH::B;
   extern __shared__ __align__(16) double smem[];
@@ -579,7 +580,8 @@ template <class SH>
 static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                                    cudaStream_t st) {
   const int threads = 128, groups = (threads / 32) * SH::GPW;
-  int D = 3;
+  int D = 2;  // ring depth: two stage steps of look-ahead cover the HBM latency
+  if (const char *e = getenv("RLDL_RING_DEPTH")) D = atoi(e) > 1 ? atoi(e) : 2;
   if (D > 2 * (B.N + 1)) D = 2 * (B.N + 1);
   const size_t shm = ((size_t)SH::M_END + (size_t)groups * SH::group_doubles(D)) * sizeof(double);
   if (shm > 220 * 1024) return cudaErrorInvalidValue;
