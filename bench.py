@@ -72,8 +72,10 @@ def run_reference_sample(mdl, cfg, sample, seed_offset=0):
     from oracle import ref_py
     N = cfg["N"]
     x0 = mpc.sample_x0(mdl, cfg["batch"], SEED)[seed_offset:seed_offset + sample]
-    q, l, u = mdl.vectors(x0, N)
-    res = ref_py.run_isolated(dict(model=mdl, N=N, Nmax=N, q=q, l=l, u=u, settings=SETTINGS,
+    # Nmax = N+1: with N == Nmax the reference writes one element past L->p and reads the terminal
+    # rho from the wrong rows; results are identical, the heap stays intact
+    q, l, u = mdl.vectors(x0, N, N + 1)
+    res = ref_py.run_isolated(dict(model=mdl, N=N, Nmax=N + 1, q=q, l=l, u=u, settings=SETTINGS,
                                    path="recursive", ops=[("solve",), ("get",)]))
     t = res[-1]
     secs = t["setup_wall"] + t["solve_wall"][0]
@@ -162,6 +164,11 @@ class ClockSampler:
         return out
 
 
+def shard_range(rank, world, total):
+    """Contiguous instance range of one rank (instances share nothing: no data-path collective)."""
+    return rank * total // world, (rank + 1) * total // world
+
+
 # ----------------------------------------------------------------------------
 # B200 arm
 # ----------------------------------------------------------------------------
@@ -207,7 +214,7 @@ def main_b200(args):
 
     cfg, mdl = workload(args.workload, args.batch)
     N, total = cfg["N"], cfg["batch"]
-    lo, hi = rank * total // world, (rank + 1) * total // world
+    lo, hi = shard_range(rank, world, total)
     mine = hi - lo
     x0 = mpc.sample_x0(mdl, total, SEED)[lo:hi]
     q_np, l_np, u_np = mdl.vectors(x0, N)

@@ -183,7 +183,10 @@ def run_ops(spec):
     res, solve_wall = [], []
     for op in spec["ops"]:
         name, args = op[0], op[1:]
-        if name == "solve":
+        if name == "receding":       # ("receding", x0, T, shrink_every, feedback)
+            from oracle import scenarios
+            res.append(scenarios.receding_horizon(rb, spec["model"], spec["N"], spec["Nmax"], *args))
+        elif name == "solve":
             t0 = time.perf_counter()
             res.append(rb.solve())
             solve_wall.append(time.perf_counter() - t0)

@@ -357,3 +357,86 @@ def mpc_solver(model, N, q, l, u, settings: Settings, path="recursive"):
     n, m = P.shape[0], A.shape[0]
     kkt = StageKKT(blocks, nx, nu, ny, nt, N, settings.sigma) if path == "recursive" else DenseKKT(P, A, settings.sigma)
     return Solver(P, A, q[:n], l[:m], u[:m], kkt, settings)
+
+
+class OracleBatch:
+    """Batch facade over per-instance Solvers with the same surface as rldl_b200.Batch /
+    oracle.ref_py.RefBatch (solve, get, dims, update_bounds, warm_start, update_horizon...)."""
+
+    def __init__(self, model, N, Nmax, q, l, u, settings: dict, path="recursive", rho=None):
+        keys = vars(Settings()).keys()
+        self.model, self.N, self.Nmax, self.path = model, N, Nmax, path
+        self.q, self.l, self.u = np.array(q, float), np.array(l, float), np.array(u, float)
+        self.batch, self.nmax, self.mmax = q.shape[0], q.shape[1], l.shape[1]
+        self.sv = []
+        for k in range(self.batch):
+            s = Settings(**{kk: vv for kk, vv in settings.items() if kk in keys})
+            if rho is not None:
+                s.rho = float(rho[k])
+            self.sv.append(mpc_solver(model, N, self.q[k], self.l[k], self.u[k], s, path))
+        self.last = None
+
+    def dims(self):
+        return self.sv[0].n, self.sv[0].m
+
+    def solve(self):
+        self.last = [s.solve() for s in self.sv]
+        return 0
+
+    def get(self):
+        B, n, m = self.batch, *self.dims()
+        out = dict(x=np.zeros((B, self.nmax)), y=np.zeros((B, self.mmax)))
+        for key, dt in (("iter", np.int64), ("status", np.int64), ("obj", float), ("pri_res", float),
+                        ("dua_res", float), ("rho_updates", np.int64), ("rho_estimate", float)):
+            out[key] = np.array([r[key] for r in self.last], dt)
+        for k, r in enumerate(self.last):
+            out["x"][k, :n], out["y"][k, :m] = r["x"], r["y"]
+        return out
+
+    def update_bounds(self, l, u):
+        self.l, self.u = np.array(l, float), np.array(u, float)
+        for k, s in enumerate(self.sv):
+            s.update_bounds(self.l[k], self.u[k])
+        return 0
+
+    def update_lin_cost(self, q):
+        self.q = np.array(q, float)
+        for k, s in enumerate(self.sv):
+            s.update_lin_cost(self.q[k])
+        return 0
+
+    def warm_start(self, x=None, y=None):
+        for k, s in enumerate(self.sv):
+            s.warm_start(None if x is None else x[k], None if y is None else y[k])
+        return 0
+
+    def update_rho(self, rho):
+        for k, s in enumerate(self.sv):
+            s.update_rho(float(rho[k]))
+        return 0
+
+    def update_horizon(self, N):
+        """osqp_update_recursive (src/recursive_ldl.c:1973): new P/A sizes, tail re-factorisation."""
+        Pu, A = self.model.assemble(N)
+        Pu = Pu.toarray()
+        P, A = Pu + Pu.T - np.diag(np.diag(Pu)), A.toarray()
+        n, m = P.shape[0], A.shape[0]
+        for k, s in enumerate(self.sv):
+            xo, zo, yo = s.x, s.z, s.y
+            s.P, s.A, s.n, s.m = P, A, n, m
+            s.q, s.l, s.u = self.q[k, :n].copy(), self.l[k, :m].copy(), self.u[k, :m].copy()
+            s.rho_vec = set_rho_vec(s.l, s.u, s.rho)
+            if isinstance(s.kkt, StageKKT):
+                s.kkt.set_horizon(N, s.rho_vec)
+            else:
+                s.kkt = DenseKKT(P, A, s.s.sigma).factor(s.rho_vec)
+            s.x, s.z, s.y = np.zeros(n), np.zeros(m), np.zeros(m)
+            s.x[:min(n, xo.size)] = xo[:n]; s.z[:min(m, zo.size)] = zo[:m]; s.y[:min(m, yo.size)] = yo[:m]
+        self.N = N
+        return 0
+
+    def kkt_solve(self, k, rhs):
+        return self.sv[k].kkt.solve(np.asarray(rhs, float))
+
+    def free(self):
+        pass

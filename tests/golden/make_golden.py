@@ -1,0 +1,80 @@
+"""Generate tests/golden/*.npz from the UNMODIFIED reference (oracle/_ref, built by
+oracle/Makefile from /root/reference).  Run here (where /root/reference exists):
+
+    python tests/golden/make_golden.py
+
+Every fixture stores the inputs that are not re-derivable from the seeded generator
+(rldl_b200.mpc) and the reference's outputs (status, iter, obj, x, y).  The recursive path
+is run with Nmax = N+1 (with N == Nmax the reference writes one element
+past L->p and reads the terminal rho from the wrong rows)."""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+for p in (ROOT, os.path.join(ROOT, "osqp-recursive-ldl_b200"), os.path.join(ROOT, "tests")):
+    sys.path.insert(0, p)
+
+from common import problem, ref_run, settings_dict  # noqa: E402
+from rldl_b200 import mpc  # noqa: E402
+
+
+def save(name, **kw):
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **kw)
+    print("wrote", name, {k: getattr(v, "shape", v) for k, v in kw.items()})
+
+
+def cold(name, batch):
+    mdl, N, x0, q, l, u = problem(name, batch, Nmax=mpc.CONFIGS[name]["N"] + 1)
+    res = ref_run(mdl, N, N + 1, q, l, u, [("solve",), ("get",), ("dims",)])
+    r, (n, m) = res[1], res[2]
+    rng = np.random.default_rng(7)
+    rhs = rng.standard_normal((2, n + m))
+    kk = ref_run(mdl, N, N + 1, q, l, u, [("kkt_solve", k, rhs[k]) for k in range(2)])
+    save(f"cold_{name}", batch=batch, seed=1234, n=n, m=m, status=r["status"], iter=r["iter"], obj=r["obj"],
+         x=r["x"][:, :n], y=r["y"][:, :m], kkt_rhs=rhs, kkt_sol=np.stack(kk[:2]))
+
+
+def adaptive(name, batch):
+    """C4: adaptive rho on the reference's STOCK path (the recursive path segfaults, F1)."""
+    mdl, N, x0, q, l, u = problem(name, batch)
+    rho = np.where(np.arange(batch) % 2 == 0, 1e-3, 10.0)
+    res = ref_run(mdl, N, N, q, l, u, [("solve",), ("get",), ("dims",)], path="stock", rho=rho,
+                  adaptive_rho=1, adaptive_rho_interval=25, adaptive_rho_tolerance=1.5)
+    r, (n, m) = res[1], res[2]
+    save(f"adaptive_{name}", batch=batch, seed=1234, rho=rho, n=n, m=m, status=r["status"], iter=r["iter"],
+         obj=r["obj"], rho_updates=r["rho_updates"], x=r["x"][:, :n], y=r["y"][:, :m])
+
+
+def receding(name, batch, T, shrink_every):
+    cfg = mpc.CONFIGS[name]
+    mdl, N = mpc.make_model(cfg), cfg["N"]
+    x0 = mpc.sample_x0(mdl, batch, 4321)
+    q, l, u = mdl.vectors(x0, N, N + 1)
+    steps = ref_run(mdl, N, N + 1, q, l, u, [("receding", x0, T, shrink_every, None)], warm_start=1)[0]
+    kw = dict(batch=batch, seed=4321, T=T, shrink_every=shrink_every)
+    for t, s in enumerate(steps):
+        for key in ("N", "iter", "status", "obj", "x", "y", "u0"):
+            kw[f"{key}_{t}"] = s[key]
+    save(f"receding_{name}", **kw)
+
+
+def infeasible():
+    """Primal infeasible: stage-1 state box that the bounded input cannot reach."""
+    mdl, N, x0, q, l, u = problem("C1", 4, Nmax=21)
+    b = mdl.nx + mdl.ny
+    l[:, b:b + mdl.nx] = 10.0; u[:, b:b + mdl.nx] = 11.0
+    r = ref_run(mdl, N, N + 1, q, l, u, [("solve",), ("get",)])[1]
+    save("infeasible_C1", batch=4, seed=1234, status=r["status"], iter=r["iter"], obj=r["obj"])
+
+
+if __name__ == "__main__":
+    cold("C1", 16)
+    cold("C3", 6)
+    cold("C4", 6)
+    adaptive("C4", 8)
+    receding("C1", 6, 7, 2)
+    receding("C3", 3, 6, 2)
+    infeasible()
