@@ -60,6 +60,14 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       : "memory");
 }
 
+// 8-byte asynchronous global -> shared copy (SASS LDGSTS), grouped per stage step
+__device__ __forceinline__ void cp_async8(double *dst, const double *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 __host__ __device__ inline int even_up(int v) { return (v + 1) & ~1; }
 // doubles of the diagonal-packed form of a symmetric n x n matrix
 __host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
@@ -170,7 +178,11 @@ struct Shape {
                        O_VN2 = O_SP + NXE, O_VC = O_VN2 + 2 * NXE, O_NUD = O_VC + AE, O_GG2 = O_NUD + NXE,
                        SC_SWEEP = O_GG2 + 2 * AE;
   static constexpr int VM = (A > RMAX ? A : RMAX);
-  static constexpr int SC = SC_SWEEP > 8 * VM ? SC_SWEEP : 8 * VM;
+  // mutable-vector staging: 2 buffers x MVF fields x G lanes (x, zd, yd, yk, sk, zp[NYT], yp[NYT]),
+  // placed after the region the residual routines alias
+  static constexpr int MVF = 5 + 2 * NYT;
+  static constexpr int O_MV = SC_SWEEP > 8 * VM ? SC_SWEEP : 8 * VM;
+  static constexpr int SC = O_MV + 2 * MVF * G;
   // CTA-shared model block (doubles)
   static constexpr int M_FD = 0, M_FDT = M_FD + 2 * A * NX, M_CV = M_FDT + 2 * A * NX, M_CTV = M_CV + 3 * ROWS * CW,
                        M_CI = M_CTV + 3 * AE * CW,                       // ints from here: 3*ROWS*CW
@@ -213,11 +225,6 @@ __device__ __forceinline__ double ell_row(const double *__restrict__ val, const 
   return s;
 }
 
-template <int NYT>
-struct MutVec {  // the mutable per-stage values a lane owns
-  double x, zd, yd, yk, sk;
-  double zp[NYT], yp[NYT];
-};
 
 // ---------------------------------------------------------------------------
 // The persistent streaming ADMM kernel
@@ -302,7 +309,6 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   const double *recb = nullptr;
   double *x = nullptr, *z = nullptr, *y = nullptr, *dx = nullptr, *dy = nullptr, *ykg = nullptr, *skg = nullptr;
   double rho_in = 0.0, rho_eq = 0.0, inv_in = 0.0, inv_eq = 0.0, inv_min = 0.0;
-  MutVec<NYT> cur;
 
   auto rinv_of = [&](double rv) -> double {  // reciprocal of a rho_vec entry (one of three classes)
     return rv == rho_in ? inv_in : (rv == rho_eq ? inv_eq : (rv == kRhoMin ? inv_min : 1.0 / rv));
@@ -318,22 +324,32 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     bulk_g2s(ring_s + 8u * (s * RS + (fwd ? 0 : SH::XOFF)), src, bytes, bar);
     ipos = (ipos + 1 == npos) ? 0 : ipos + 1;
   };
-  auto load_mv = [&](MutVec<NYT> &r, int k, bool bwd) {
+  // Mutable per-stage values (iterates and forward intermediates) are staged global -> shared
+  // by 8-byte cp.async one stage step ahead; every lane copies and later reads only the entries
+  // it owns (and wrote), field f of lane gl at mv[f*G + gl].
+  constexpr int F_X = 0, F_ZD = 1, F_YD = 2, F_YK = 3, F_SK = 4, F_ZP = 5, F_YP = 5 + NYT;
+  double *mvb = sc + SH::O_MV;
+  int mvsel = 0;  // buffer holding the current stage step's values
+  auto load_mv = [&](double *mv, int k, bool bwd) {
     const bool term = (k == N);
     const int dim = term ? NX : A, np = term ? NT : NY;
     const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
-    r.x = (gl >= ilo && gl < dim) ? x[xoff + gl] : 0.0;
+    if (gl >= ilo && gl < dim) cp_async8(mv + F_X * G + gl, x + xoff + gl);
 #pragma unroll
     for (int t = 0; t < NYT; t++) {
       const int rr = gl + G * t;
-      r.zp[t] = 0.0; r.yp[t] = 0.0;
-      if (rr < np) { r.zp[t] = z[roff + rr]; r.yp[t] = y[roff + rr]; }
+      if (rr < np) {
+        cp_async8(mv + (F_ZP + t) * G + gl, z + roff + rr);
+        cp_async8(mv + (F_YP + t) * G + gl, y + roff + rr);
+      }
     }
-    r.zd = r.yd = r.yk = r.sk = 0.0;
-    if (!term && gl < NX) { r.zd = z[roff + NY + gl]; r.yd = y[roff + NY + gl]; }
+    if (!term && gl < NX) {
+      cp_async8(mv + F_ZD * G + gl, z + roff + NY + gl);
+      cp_async8(mv + F_YD * G + gl, y + roff + NY + gl);
+    }
     if (bwd && !term) {
-      if (gl < A) r.yk = ykg[k * A + gl];
-      if (gl < NX) r.sk = skg[k * NX + gl];
+      if (gl < A) cp_async8(mv + F_YK * G + gl, ykg + k * A + gl);
+      if (gl < NX) cp_async8(mv + F_SK * G + gl, skg + k * NX + gl);
     }
   };
   // claim the next instance of the queue; sets up pointers, cold start, ring and registers
@@ -371,7 +387,9 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     }
     __syncwarp(gm);
     iter = 0;
-    load_mv(cur, 0, false);
+    mvsel = 0;
+    load_mv(mvb, 0, false);
+    cp_async_commit();
     return true;
   };
   auto consume_wait = [&]() { mbar_wait(bars_s + 8u * slot, phase); };
@@ -382,6 +400,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     if (slot == D) { slot = 0; phase ^= 1u; }
   };
   auto drain = [&]() {  // consume the D packets still in flight for the finished instance
+    cp_async_wait<0>();
     for (int d = 0; d < D; d++) {
       consume_wait();
       slot++;
@@ -397,23 +416,24 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       const bool can_check = S.check_termination && (iter % S.check_termination == 0);
       const bool store_delta = can_check || iter == S.max_iter;
       double yv_reg = 0.0;  // this lane's entry of Xinv*t of the last forward stage
-      MutVec<NYT> nxt;
       // =============================== forward sweep ===============================
       for (int k = 0; k <= N; k++) {
         const bool term = (k == N);
         const int cls = term ? 2 : (k == 0 ? 0 : 1);
         const int dim = term ? NX : A, np = term ? NT : NY;
         const int ilo = (k == 0) ? NX : 0;
-        if (!term) load_mv(nxt, k + 1, false);
-        else load_mv(nxt, N, true);
+        const double *mv = mvb + mvsel * (SH::MVF * G);
+        load_mv(mvb + (mvsel ^ 1) * (SH::MVF * G), term ? N : k + 1, term);
+        cp_async_commit();
         const double *sl_ = ring + slot * RS;
+        cp_async_wait<1>();
         consume_wait();
         double g = 0.0;
-        if (gl >= ilo && gl < dim) g = sigma * cur.x - sl_[gl];
+        if (gl >= ilo && gl < dim) g = sigma * mv[F_X * G + gl] - sl_[gl];
 #pragma unroll
         for (int t = 0; t < NYT; t++) {
           const int rr = gl + G * t;
-          if (rr < np) w[rr] = sl_[SH::RHO + rr] * cur.zp[t] - cur.yp[t];
+          if (rr < np) w[rr] = sl_[SH::RHO + rr] * mv[(F_ZP + t) * G + gl] - mv[(F_YP + t) * G + gl];
         }
         __syncwarp(gm);
         double tt = 0.0;
@@ -434,7 +454,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         if (!term) {
           if (gl < NX) {
             const double ri = rinv_of(sl_[SH::RHO + NY + gl]);
-            const double tdv = (cur.zd - cur.yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
+            const double tdv = (mv[F_ZD * G + gl] - mv[F_YD * G + gl] * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
             td2[gl] = tdv; td2[gl + NX] = tdv;
           }
           __syncwarp(gm);
@@ -446,7 +466,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           __syncwarp(gm);
         }
         consume_done();
-        cur = nxt;
+        mvsel ^= 1;
       }
       // =============================== backward sweep ==============================
       for (int k = N; k >= 0; k--) {
@@ -454,15 +474,19 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         const int cls = term ? 2 : (k == 0 ? 0 : 1);
         const int dim = term ? NX : A, np = term ? NT : NY;
         const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
-        if (k > 0) load_mv(nxt, k - 1, true);
+        const double *mv = mvb + mvsel * (SH::MVF * G);
+        double *mvn = mvb + (mvsel ^ 1) * (SH::MVF * G);
+        if (k > 0) load_mv(mvn, k - 1, true);
+        cp_async_commit();
         const double *sl_ = ring + slot * RS;
+        cp_async_wait<1>();
         consume_wait();
         double vv = 0.0, nud = 0.0;
         if (term) {
           vv = yv_reg;
         } else {
           if (gl < NX) {
-            nud = -(cur.sk + dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, vn2 + gl, wrapS));
+            nud = -(mv[F_SK * G + gl] + dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, vn2 + gl, wrapS));
             nudv[gl] = nud;
           }
           __syncwarp(gm);
@@ -471,50 +495,49 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
             gg2[gl] = ggv; gg2[gl + A] = ggv;
           }
           __syncwarp(gm);
-          if (gl < A) vv = cur.yk - dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
+          if (gl < A) vv = mv[F_YK * G + gl] - dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
         }
         if (gl < A) vcur[gl] = vv;
         if (gl < NX) { vn2[gl] = vv; vn2[gl + NX] = vv; }
         __syncwarp(gm);
-        MutVec<NYT> nw = cur;  // new iterate values of this stage (stage 0: carried into the next forward sweep)
+        // new iterate values; at stage 0 they are also written into the buffer the next forward sweep reads
 #pragma unroll
         for (int t = 0; t < NYT; t++) {
           const int rr = gl + G * t;
           if (rr < np) {
             const int ri = roff + rr;
             const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
-            const double rho = sl_[SH::RHO + rr], rinv = rinv_of(rho), zo = cur.zp[t], yo = cur.yp[t];
+            const double rho = sl_[SH::RHO + rr], rinv = rinv_of(rho), zo = mv[(F_ZP + t) * G + gl], yo = mv[(F_YP + t) * G + gl];
             const double zh = alpha * zt + oma * zo;
             const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
             z[ri] = zn; y[ri] = yo + d;
-            nw.zp[t] = zn; nw.yp[t] = yo + d;
+            if (k == 0) { mvn[(F_ZP + t) * G + gl] = zn; mvn[(F_YP + t) * G + gl] = yo + d; }
             if (store_delta) dy[ri] = d;
           }
         }
         if (!term && gl < NX) {
           const int ri = roff + NY + gl;
           const double rho = sl_[SH::RHO + NY + gl], rinv = rinv_of(rho);
-          const double zo = cur.zd, yo = cur.yd;
+          const double zo = mv[F_ZD * G + gl], yo = mv[F_YD * G + gl];
           const double zt = (zo - yo * rinv) + nud * rinv;
           const double zh = alpha * zt + oma * zo;
           const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
           const double d = rho * (zh - zn);
           z[ri] = zn; y[ri] = yo + d;
-          nw.zd = zn; nw.yd = yo + d;
+          if (k == 0) { mvn[F_ZD * G + gl] = zn; mvn[F_YD * G + gl] = yo + d; }
           if (store_delta) dy[ri] = d;
         }
         if (gl >= ilo && gl < dim) {
-          const double xo = cur.x;
+          const double xo = mv[F_X * G + gl];
           const double xn = alpha * vv + oma * xo;
           x[xoff + gl] = xn;
-          nw.x = xn;
+          if (k == 0) mvn[F_X * G + gl] = xn;
           if (store_delta) dx[xoff + gl] = xn - xo;
         }
-        if (k == 0) nxt = nw;
         __syncwarp(gm);
         consume_done();
-        cur = nxt;
+        mvsel ^= 1;
       }
       // ---- iteration epilogue: residuals, termination (osqp.c:426-457, 524-567) ----
       bool done = false;
