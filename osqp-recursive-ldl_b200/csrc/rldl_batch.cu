@@ -264,7 +264,8 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
     D.RS = D.qa + D.PX + D.PS + 3 * D.bb;
     D.rec_stride = (long long)(B->Nmax + 1) * D.RS;
     CK(dalloc(&D.rec, B->streaming ? bs * (size_t)D.rec_stride : 1));
-    CK(dalloc(&D.work_counter, 1));
+    CK(dalloc(&D.sched, 2 + 2 * kSchedBuckets));
+    CK(dalloc(&D.sched_slots, B->streaming ? (size_t)kSchedBuckets * bs : 1));
   }
   CK(cudaStreamCreateWithFlags(&B->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&B->ev0)); CK(cudaEventCreate(&B->ev1));
@@ -306,7 +307,7 @@ Batch::~Batch() {
                   D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec};
   for (double *p : dp) if (p) cudaFree(p);
   if (D.iter) cudaFree(D.iter);
-  int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx, D.work_counter};
+  int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx, D.sched, D.sched_slots};
   for (int *p : ip) if (p) cudaFree(p);
   if (h_pin) cudaFreeHost(h_pin);
   if (ev0) cudaEventDestroy(ev0);
@@ -324,15 +325,22 @@ c_int Batch::ensure_stage(size_t doubles) {
 }
 
 // ------------------------------ operations ------------------------------
+c_int Batch::factor_launch(int k0, bool only_flagged) {
+  const int *fl = only_flagged ? d_changed : nullptr;
+  CK(launch_factor(M, D, settings.sigma, k0, fl, stream));
+  launches++;
+  if (streaming) {
+    CK(launch_pack_records(M, D, only_flagged ? 0 : k0, 3, fl, stream));
+    launches++;
+  }
+  return 0;
+}
+
 c_int Batch::factor(int k0, bool only_flagged) {
   CK(cudaSetDevice(device));
   CK(cudaEventRecord(ev0, stream));
-  CK(launch_factor(M, D, settings.sigma, k0, only_flagged ? d_changed : nullptr, stream));
-  launches++;
-  if (streaming) {
-    CK(launch_pack_records(M, D, only_flagged ? 0 : k0, 3, stream));
-    launches++;
-  }
+  c_int rc = factor_launch(k0, only_flagged);
+  if (rc) return rc;
   CK(cudaEventRecord(ev1, stream));
   CK(cudaStreamSynchronize(stream));
   float ms = 0;
@@ -347,9 +355,29 @@ c_int Batch::factor(int k0, bool only_flagged) {
 c_int Batch::solve() {
   CK(cudaSetDevice(device));
   CK(cudaEventRecord(ev0, stream));
-  if (use_stream()) CK(launch_admm_stream(M, D, S, (int)settings.warm_start, stream));
-  else CK(launch_admm(M, D, S, (int)settings.warm_start, stream));
-  launches++;
+  if (use_stream()) {
+    // Adaptive rho: an instance whose rho changes parks itself (osqp_update_rho, osqp.c:1268-1319, needs a
+    // full stage recursion); parked instances are re-typed, re-factorised and re-packed together, then resumed.
+    int resume = 0;
+    for (;;) {
+      CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, stream));
+      launches++;
+      if (!settings.adaptive_rho) break;
+      int parked = 0;
+      CK(cudaMemcpyAsync(&parked, D.sched + 1, sizeof(int), cudaMemcpyDeviceToHost, stream));
+      CK(cudaStreamSynchronize(stream));
+      if (!parked) break;
+      CK(launch_set_rho_vec(D, D.m, d_changed, stream));
+      launches++;
+      c_int rc = factor_launch(0, true);
+      if (rc) return rc;
+      resume = 1;
+      solve_rounds++;
+    }
+  } else {
+    CK(launch_admm(M, D, S, (int)settings.warm_start, stream));
+    launches++;
+  }
   CK(cudaEventRecord(ev1, stream));
   CK(cudaStreamSynchronize(stream));
   float ms = 0;
@@ -359,12 +387,12 @@ c_int Batch::solve() {
 }
 
 bool Batch::use_stream() const {
-  return streaming && !settings.adaptive_rho && kernel_choice != 1;
+  return streaming && kernel_choice != 1;
 }
 
 c_int Batch::pack(int k0, int parts) {
   if (!streaming) return 0;
-  CK(launch_pack_records(M, D, k0, parts, stream));
+  CK(launch_pack_records(M, D, k0, parts, nullptr, stream));
   launches++;
   return 0;
 }

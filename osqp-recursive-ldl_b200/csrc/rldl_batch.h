@@ -29,6 +29,7 @@ struct Batch {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double last_factor_ms = 0, last_solve_ms = 0, factor_bytes = 0;
   long long launches = 0;
+  long long solve_rounds = 0;  // extra ADMM launches caused by adaptive-rho refactorisations
 
   static c_int create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, const csc *A0,
                       const csc *Ai, const csc *Aij, const csc *AN, const OSQPSettings *st, c_int Nmax,
@@ -42,6 +43,7 @@ struct Batch {
   void set_sizes();
   c_int ensure_stage(size_t doubles);
   c_int factor(int k0, bool only_flagged);
+  c_int factor_launch(int k0, bool only_flagged);  // kernels only, no events / sync
   c_int pack(int k0, int parts);
   bool use_stream() const;
   c_int solve();

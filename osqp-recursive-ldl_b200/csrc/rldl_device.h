@@ -73,8 +73,15 @@ struct BatchDev {
   double *rec;
   int qa, PX, PS, bb, RS;
   long long rec_stride;    // (Nmax+1)*RS doubles per instance
-  int *work_counter;       // dynamic instance queue of the persistent ADMM kernel
+  // Device work scheduler of the persistent ADMM kernel (rldl_stream.cu):
+  //   sched[0] fresh-instance counter, sched[1] instances parked for a rho refactorisation,
+  //   sched[2 .. 2+kSchedBuckets) bucket heads, sched[2+kSchedBuckets .. 2+2*kSchedBuckets) bucket tails;
+  //   sched_slots[b*batch + (index mod batch)] = suspended instance, -1 = empty.
+  int *sched;
+  int *sched_slots;
 };
+
+constexpr int kSchedBuckets = 32;  // priority buckets: floor(2*log2(residual / tolerance)), clamped
 
 constexpr int STATUS_FACTOR_ERROR = -7;  // reported as OSQP_NON_CVX
 

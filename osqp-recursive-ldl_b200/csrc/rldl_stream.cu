@@ -11,7 +11,10 @@
 // ahead of the arithmetic, so the dependent chain of small FP64 mat-vecs only ever touches
 // shared memory.  The mutable iterates (x, z, y and the forward intermediates) stay in
 // HBM/L2 in the flat per-instance arrays and are register-prefetched one stage step ahead
-// by the lane that owns (wrote) them.
+// by the lane that owns (wrote) them.  Because all instance state lives in HBM between
+// iterations, instances are preemptible: a device-side priority scheduler (below) decides
+// at every termination check which instance a group serves next, and an adaptive-rho update
+// parks the instance for a batched re-factorisation launch and a resume.
 //
 // Symmetric pivot inverses are stored "diagonal-packed": DP[d][i] = M(i, (i+d) mod n) for
 // d = 0..n/2 — half the bytes of the full matrix, and lane i (owner of row i) reads
@@ -60,14 +63,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       : "memory");
 }
 
-// 8-byte asynchronous global -> shared copy (SASS LDGSTS), grouped per stage step
-__device__ __forceinline__ void cp_async8(double *dst, const double *src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
 __host__ __device__ inline int even_up(int v) { return (v + 1) & ~1; }
 // doubles of the diagonal-packed form of a symmetric n x n matrix
 __host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
@@ -76,7 +71,8 @@ __host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
 // Record packing: (Xinv, Sinv, q, l, u, rho_vec) -> rec, stages k0..N of every instance.
 // One thread per record element.
 // ---------------------------------------------------------------------------
-__global__ void k_pack_records(ModelDev M, BatchDev B, int k0, int parts /*bit0 factor, bit1 vectors*/) {
+__global__ void k_pack_records(ModelDev M, BatchDev B, int k0, int parts /*bit0 factor, bit1 vectors*/,
+                               const int *only_flagged) {
   const int a = M.a, nx = M.nx, b = M.b, nt = M.nt, N = B.N;
   const int ns = N + 1 - k0;
   const long long total = (long long)B.batch * ns * B.RS;
@@ -87,6 +83,7 @@ __global__ void k_pack_records(ModelDev M, BatchDev B, int k0, int parts /*bit0 
     const long long rest = t / B.RS;
     const int k = k0 + (int)(rest % ns);
     const int inst = (int)(rest / ns);
+    if (only_flagged && !only_flagged[inst]) continue;
     const bool term = (k == N);
     double *dst = B.rec + (long long)inst * B.rec_stride + (long long)k * B.RS + e;
     const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
@@ -139,12 +136,13 @@ __global__ void k_pack_records(ModelDev M, BatchDev B, int k0, int parts /*bit0 
   }
 }
 
-cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, int parts, cudaStream_t st) {
+cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,
+                                cudaStream_t st) {
   const long long total = (long long)B.batch * (B.N + 1 - k0) * B.RS;
   if (total <= 0) return cudaSuccess;
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 32) blocks = 148 * 32;
-  k_pack_records<<<(unsigned)blocks, 256, 0, st>>>(M, B, k0, parts);
+  k_pack_records<<<(unsigned)blocks, 256, 0, st>>>(M, B, k0, parts, only_flagged);
   return cudaGetLastError();
 }
 
@@ -178,11 +176,7 @@ struct Shape {
                        O_VN2 = O_SP + NXE, O_VC = O_VN2 + 2 * NXE, O_NUD = O_VC + AE, O_GG2 = O_NUD + NXE,
                        SC_SWEEP = O_GG2 + 2 * AE;
   static constexpr int VM = (A > RMAX ? A : RMAX);
-  // mutable-vector staging: 2 buffers x MVF fields x G lanes (x, zd, yd, yk, sk, zp[NYT], yp[NYT]),
-  // placed after the region the residual routines alias
-  static constexpr int MVF = 5 + 2 * NYT;
-  static constexpr int O_MV = SC_SWEEP > 8 * VM ? SC_SWEEP : 8 * VM;
-  static constexpr int SC = O_MV + 2 * MVF * G;
+  static constexpr int SC = SC_SWEEP > 8 * VM ? SC_SWEEP : 8 * VM;  // the residual routines alias the sweep scratch
   // CTA-shared model block (doubles)
   static constexpr int M_FD = 0, M_FDT = M_FD + 2 * A * NX, M_CV = M_FDT + 2 * A * NX, M_CTV = M_CV + 3 * ROWS * CW,
                        M_CI = M_CTV + 3 * AE * CW,                       // ints from here: 3*ROWS*CW
@@ -226,11 +220,67 @@ __device__ __forceinline__ double ell_row(const double *__restrict__ val, const 
 }
 
 
+template <int NYT>
+struct MutVec {  // the mutable per-stage values a lane owns (iterates and forward intermediates)
+  double x, zd, yd, yk, sk;
+  double zp[NYT], yp[NYT];
+};
+
+// ---------------------------------------------------------------------------
+// Device work scheduler.  Iteration counts inside a batch are heavy-tailed (C5: mean 330,
+// max 4000), and an instance is a strictly sequential chain, so the order in which instances
+// are started decides how long the kernel runs half-empty at the end.  Instances are therefore
+// preemptible at every termination check (all their state already lives in HBM): a group that
+// finds a more urgent instance waiting suspends its own into a priority bucket and resumes the
+// other.  Priority = how far the instance is from its tolerances, floor(2*log2(max(r_p/eps_p,
+// r_d/eps_d))) — the instances that will run longest are served first (measured: within 5 % of
+// the longest-first schedule computed with hindsight, 20 % shorter than first-come order).
+// Fresh instances outrank everything until their first check so that every instance gets a
+// priority early.  Buckets are multi-producer/multi-consumer rings of capacity `batch` (an
+// instance sits in at most one ring), heads claimed by CAS, slots handed over with atomicExch.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ int ld_volatile(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
+
+__device__ __forceinline__ void sched_push(const BatchDev &B, int b, int inst) {
+  const int idx = atomicAdd(B.sched + 2 + kSchedBuckets + b, 1);
+  int *sl = B.sched_slots + (size_t)b * B.batch + (idx % B.batch);
+  while (atomicCAS(sl, -1, inst) != -1) __nanosleep(32);
+}
+__device__ __forceinline__ int sched_pop(const BatchDev &B, int b) {
+  int *head = B.sched + 2 + b;
+  const int *tail = B.sched + 2 + kSchedBuckets + b;
+  for (;;) {
+    const int h = ld_volatile(head), t = ld_volatile(tail);
+    if (h >= t) return -1;
+    if (atomicCAS(head, h, h + 1) == h) {
+      int *sl = B.sched_slots + (size_t)b * B.batch + (h % B.batch);
+      int v;
+      while ((v = atomicExch(sl, -1)) < 0) __nanosleep(32);
+      return v;
+    }
+  }
+}
+// highest non-empty bucket (-1 if none); every lane of the group scans a strided share
+template <int G>
+__device__ __forceinline__ int sched_best(const BatchDev &B, int gl, unsigned gm) {
+  int best = -1;
+  for (int b = gl; b < kSchedBuckets; b += G)
+    if (ld_volatile(B.sched + 2 + kSchedBuckets + b) > ld_volatile(B.sched + 2 + b)) best = b;
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(gm, best, o));
+  return best;
+}
+
 // ---------------------------------------------------------------------------
 // The persistent streaming ADMM kernel
+//   resume = 0: every instance starts at iteration 0 (cold or warm start)
+//   resume = 1: only instances still OSQP_UNSOLVED continue from B.iter (after the host
+//               re-factorised the instances parked by an adaptive-rho update)
+//   s0     > 0: preemptive scheduling on; fresh instances run s0 iterations before they yield
 // ---------------------------------------------------------------------------
 template <class SH>
-__global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, SettingsDev S, int warm_start, int D) {
+__global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, SettingsDev S, int warm_start, int D,
+                                                        int resume, int s0) {
   constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, NT = SH::NT, CW = SH::CW, G = SH::G, NYT = SH::NYT,
                 ROWS = SH::ROWS, RS = SH::RS, BQ = SH::B;
   extern __shared__ __align__(16) double smem[];
@@ -299,6 +349,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
 
   const int npos = 2 * (N + 1);
   const double sigma = S.sigma, alpha = S.alpha, oma = 1.0 - S.alpha;
+  const bool sched_on = s0 > 0 && S.check_termination > 0;
   // ring state: consumer slot/phase, and the position (0..npos-1) of the next packet to issue
   int slot = 0, ipos = 0;
   uint32_t phase = 0;
@@ -309,6 +360,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   const double *recb = nullptr;
   double *x = nullptr, *z = nullptr, *y = nullptr, *dx = nullptr, *dy = nullptr, *ykg = nullptr, *skg = nullptr;
   double rho_in = 0.0, rho_eq = 0.0, inv_in = 0.0, inv_eq = 0.0, inv_min = 0.0;
+  MutVec<NYT> cur;
 
   auto rinv_of = [&](double rv) -> double {  // reciprocal of a rho_vec entry (one of three classes)
     return rv == rho_in ? inv_in : (rv == rho_eq ? inv_eq : (rv == kRhoMin ? inv_min : 1.0 / rv));
@@ -324,53 +376,73 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     bulk_g2s(ring_s + 8u * (s * RS + (fwd ? 0 : SH::XOFF)), src, bytes, bar);
     ipos = (ipos + 1 == npos) ? 0 : ipos + 1;
   };
-  // Mutable per-stage values (iterates and forward intermediates) are staged global -> shared
-  // by 8-byte cp.async one stage step ahead; every lane copies and later reads only the entries
-  // it owns (and wrote), field f of lane gl at mv[f*G + gl].
-  constexpr int F_X = 0, F_ZD = 1, F_YD = 2, F_YK = 3, F_SK = 4, F_ZP = 5, F_YP = 5 + NYT;
-  double *mvb = sc + SH::O_MV;
-  int mvsel = 0;  // buffer holding the current stage step's values
-  auto load_mv = [&](double *mv, int k, bool bwd) {
+  // Mutable per-stage values are register-prefetched one stage step ahead by the lane that owns
+  // (and wrote) them.  L2-only loads (ld.global.cg): an instance may have been advanced by a group
+  // on another SM since this SM last touched it, and L1 is not coherent across SMs.
+  auto load_mv = [&](MutVec<NYT> &r, int k, bool bwd) {
     const bool term = (k == N);
     const int dim = term ? NX : A, np = term ? NT : NY;
     const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
-    if (gl >= ilo && gl < dim) cp_async8(mv + F_X * G + gl, x + xoff + gl);
+    r.x = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
 #pragma unroll
     for (int t = 0; t < NYT; t++) {
       const int rr = gl + G * t;
-      if (rr < np) {
-        cp_async8(mv + (F_ZP + t) * G + gl, z + roff + rr);
-        cp_async8(mv + (F_YP + t) * G + gl, y + roff + rr);
-      }
+      r.zp[t] = 0.0; r.yp[t] = 0.0;
+      if (rr < np) { r.zp[t] = __ldcg(z + roff + rr); r.yp[t] = __ldcg(y + roff + rr); }
     }
-    if (!term && gl < NX) {
-      cp_async8(mv + F_ZD * G + gl, z + roff + NY + gl);
-      cp_async8(mv + F_YD * G + gl, y + roff + NY + gl);
-    }
+    r.zd = r.yd = r.yk = r.sk = 0.0;
+    if (!term && gl < NX) { r.zd = __ldcg(z + roff + NY + gl); r.yd = __ldcg(y + roff + NY + gl); }
     if (bwd && !term) {
-      if (gl < A) cp_async8(mv + F_YK * G + gl, ykg + k * A + gl);
-      if (gl < NX) cp_async8(mv + F_SK * G + gl, skg + k * NX + gl);
+      if (gl < A) r.yk = __ldcg(ykg + k * A + gl);
+      if (gl < NX) r.sk = __ldcg(skg + k * NX + gl);
     }
   };
-  // claim the next instance of the queue; sets up pointers, cold start, ring and registers
-  auto fetch = [&]() -> bool {
+  // claim an instance: fresh ones first, then the most urgent suspended one, provided its
+  // bucket is above `above`.  Returns the instance (group-uniform) or -1; *fresh tells which.
+  auto acquire = [&](int above, bool *fresh) -> int {
     for (;;) {
-      int i = 0;
-      if (gl == 0) i = atomicAdd(B.work_counter, 1);
-      i = __shfl_sync(gm, i, 0, G);
-      if (i >= B.batch) return false;
-      inst = i;
-      if (B.fact_flag[inst]) {  // failed factorisation: report non-convex, like a diverged solve
-        if (gl == 0) { B.status[inst] = -7; B.iter[inst] = 0; B.obj[inst] = kOsqpNan; }
-        continue;
+      int i = -1;
+      if (gl == 0 && ld_volatile(B.sched) < B.batch) {
+        i = atomicAdd(B.sched, 1);
+        if (i >= B.batch) i = -1;
       }
-      break;
+      i = __shfl_sync(gm, i, 0, G);
+      if (i >= 0) {
+        bool skip = false;
+        if (B.fact_flag[i]) {  // failed factorisation: report non-convex, like a diverged solve
+          if (gl == 0) { B.status[i] = -7; B.iter[i] = 0; B.obj[i] = kOsqpNan; }
+          skip = true;
+        } else if (resume && B.status[i] != -10) {
+          skip = true;  // finished in an earlier launch of this solve
+        }
+        if (skip) continue;
+        *fresh = true;
+        return i;
+      }
+      if (!sched_on) return -1;
+      const int best = sched_best<G>(B, gl, gm);
+      if (best <= above) return -1;
+      int v = -1;
+      if (gl == 0) v = sched_pop(B, best);
+      v = __shfl_sync(gm, v, 0, G);
+      if (v >= 0) {
+        *fresh = false;
+        return v;
+      }
     }
+  };
+  // take the next instance and set up pointers, iterates, ring and registers
+  auto start_next = [&]() -> bool {
+    bool fresh = true;
+    const int i = acquire(-1, &fresh);
+    if (i < 0) return false;
+    inst = i;
+    __threadfence();  // order the loads below after the hand-over of the instance
     const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
     x = B.x + vo; z = B.z + ro; y = B.y + ro; dx = B.dx + vo; dy = B.dy + ro;
     ykg = B.yk + (size_t)inst * B.ykstride; skg = B.sk + (size_t)inst * B.skstride;
     recb = B.rec + (size_t)inst * B.rec_stride;
-    rho_in = B.rho[inst]; rho_eq = kRhoEq * rho_in;
+    rho_in = __ldcg(B.rho + inst); rho_eq = kRhoEq * rho_in;
     inv_in = 1.0 / rho_in; inv_eq = 1.0 / rho_eq; inv_min = 1.0 / kRhoMin;
     ipos = 0;
     if (gl == 0) {
@@ -381,15 +453,18 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       }
     }
     ipos = __shfl_sync(gm, ipos, 0, G);
-    if (!warm_start) {
-      for (int i = gl; i < n; i += G) x[i] = 0.0;
-      for (int r = gl; r < m; r += G) { z[r] = 0.0; y[r] = 0.0; }
+    if (fresh && !resume) {
+      if (!warm_start) {
+        for (int i2 = gl; i2 < n; i2 += G) x[i2] = 0.0;
+        for (int r = gl; r < m; r += G) { z[r] = 0.0; y[r] = 0.0; }
+      }
+      if (gl == 0) B.status[inst] = -10;
+      iter = 0;
+    } else {
+      iter = (int)__ldcg(B.iter + inst);
     }
     __syncwarp(gm);
-    iter = 0;
-    mvsel = 0;
-    load_mv(mvb, 0, false);
-    cp_async_commit();
+    load_mv(cur, 0, false);
     return true;
   };
   auto consume_wait = [&]() { mbar_wait(bars_s + 8u * slot, phase); };
@@ -399,8 +474,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     slot++;
     if (slot == D) { slot = 0; phase ^= 1u; }
   };
-  auto drain = [&]() {  // consume the D packets still in flight for the finished instance
-    cp_async_wait<0>();
+  auto drain = [&]() {  // consume the D packets still in flight for the instance being left
     for (int d = 0; d < D; d++) {
       consume_wait();
       slot++;
@@ -409,31 +483,31 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     __syncwarp(gm);
   };
 
-  have = fetch();
+  have = start_next();
   while (__any_sync(FULL, have)) {
     if (have) {
       iter++;
       const bool can_check = S.check_termination && (iter % S.check_termination == 0);
+      const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval && (iter % S.adaptive_rho_interval == 0);
       const bool store_delta = can_check || iter == S.max_iter;
       double yv_reg = 0.0;  // this lane's entry of Xinv*t of the last forward stage
+      MutVec<NYT> nxt;
       // =============================== forward sweep ===============================
       for (int k = 0; k <= N; k++) {
         const bool term = (k == N);
         const int cls = term ? 2 : (k == 0 ? 0 : 1);
         const int dim = term ? NX : A, np = term ? NT : NY;
         const int ilo = (k == 0) ? NX : 0;
-        const double *mv = mvb + mvsel * (SH::MVF * G);
-        load_mv(mvb + (mvsel ^ 1) * (SH::MVF * G), term ? N : k + 1, term);
-        cp_async_commit();
+        if (!term) load_mv(nxt, k + 1, false);
+        else load_mv(nxt, N, true);
         const double *sl_ = ring + slot * RS;
-        cp_async_wait<1>();
         consume_wait();
         double g = 0.0;
-        if (gl >= ilo && gl < dim) g = sigma * mv[F_X * G + gl] - sl_[gl];
+        if (gl >= ilo && gl < dim) g = sigma * cur.x - sl_[gl];
 #pragma unroll
         for (int t = 0; t < NYT; t++) {
           const int rr = gl + G * t;
-          if (rr < np) w[rr] = sl_[SH::RHO + rr] * mv[(F_ZP + t) * G + gl] - mv[(F_YP + t) * G + gl];
+          if (rr < np) w[rr] = sl_[SH::RHO + rr] * cur.zp[t] - cur.yp[t];
         }
         __syncwarp(gm);
         double tt = 0.0;
@@ -454,7 +528,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         if (!term) {
           if (gl < NX) {
             const double ri = rinv_of(sl_[SH::RHO + NY + gl]);
-            const double tdv = (mv[F_ZD * G + gl] - mv[F_YD * G + gl] * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
+            const double tdv = (cur.zd - cur.yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
             td2[gl] = tdv; td2[gl + NX] = tdv;
           }
           __syncwarp(gm);
@@ -466,7 +540,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           __syncwarp(gm);
         }
         consume_done();
-        mvsel ^= 1;
+        cur = nxt;
       }
       // =============================== backward sweep ==============================
       for (int k = N; k >= 0; k--) {
@@ -474,19 +548,15 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         const int cls = term ? 2 : (k == 0 ? 0 : 1);
         const int dim = term ? NX : A, np = term ? NT : NY;
         const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
-        const double *mv = mvb + mvsel * (SH::MVF * G);
-        double *mvn = mvb + (mvsel ^ 1) * (SH::MVF * G);
-        if (k > 0) load_mv(mvn, k - 1, true);
-        cp_async_commit();
+        if (k > 0) load_mv(nxt, k - 1, true);
         const double *sl_ = ring + slot * RS;
-        cp_async_wait<1>();
         consume_wait();
         double vv = 0.0, nud = 0.0;
         if (term) {
           vv = yv_reg;
         } else {
           if (gl < NX) {
-            nud = -(mv[F_SK * G + gl] + dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, vn2 + gl, wrapS));
+            nud = -(cur.sk + dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, vn2 + gl, wrapS));
             nudv[gl] = nud;
           }
           __syncwarp(gm);
@@ -495,59 +565,68 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
             gg2[gl] = ggv; gg2[gl + A] = ggv;
           }
           __syncwarp(gm);
-          if (gl < A) vv = mv[F_YK * G + gl] - dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
+          if (gl < A) vv = cur.yk - dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
         }
         if (gl < A) vcur[gl] = vv;
         if (gl < NX) { vn2[gl] = vv; vn2[gl + NX] = vv; }
         __syncwarp(gm);
-        // new iterate values; at stage 0 they are also written into the buffer the next forward sweep reads
+        MutVec<NYT> nw = cur;  // new iterate values of this stage (stage 0: carried into the next forward sweep)
 #pragma unroll
         for (int t = 0; t < NYT; t++) {
           const int rr = gl + G * t;
           if (rr < np) {
             const int ri = roff + rr;
             const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
-            const double rho = sl_[SH::RHO + rr], rinv = rinv_of(rho), zo = mv[(F_ZP + t) * G + gl], yo = mv[(F_YP + t) * G + gl];
+            const double rho = sl_[SH::RHO + rr], rinv = rinv_of(rho), zo = cur.zp[t], yo = cur.yp[t];
             const double zh = alpha * zt + oma * zo;
             const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
             z[ri] = zn; y[ri] = yo + d;
-            if (k == 0) { mvn[(F_ZP + t) * G + gl] = zn; mvn[(F_YP + t) * G + gl] = yo + d; }
+            nw.zp[t] = zn; nw.yp[t] = yo + d;
             if (store_delta) dy[ri] = d;
           }
         }
         if (!term && gl < NX) {
           const int ri = roff + NY + gl;
           const double rho = sl_[SH::RHO + NY + gl], rinv = rinv_of(rho);
-          const double zo = mv[F_ZD * G + gl], yo = mv[F_YD * G + gl];
+          const double zo = cur.zd, yo = cur.yd;
           const double zt = (zo - yo * rinv) + nud * rinv;
           const double zh = alpha * zt + oma * zo;
           const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
           const double d = rho * (zh - zn);
           z[ri] = zn; y[ri] = yo + d;
-          if (k == 0) { mvn[F_ZD * G + gl] = zn; mvn[F_YD * G + gl] = yo + d; }
+          nw.zd = zn; nw.yd = yo + d;
           if (store_delta) dy[ri] = d;
         }
         if (gl >= ilo && gl < dim) {
-          const double xo = mv[F_X * G + gl];
+          const double xo = cur.x;
           const double xn = alpha * vv + oma * xo;
           x[xoff + gl] = xn;
-          if (k == 0) mvn[F_X * G + gl] = xn;
+          nw.x = xn;
           if (store_delta) dx[xoff + gl] = xn - xo;
         }
+        if (k == 0) nxt = nw;
         __syncwarp(gm);
         consume_done();
-        mvsel ^= 1;
+        cur = nxt;
       }
-      // ---- iteration epilogue: residuals, termination (osqp.c:426-457, 524-567) ----
-      bool done = false;
+      // ---- iteration epilogue: residuals, termination, rho adaptation (osqp.c:426-519, 524-567) ----
+      bool done = false, rho_changed = false;
       int status = -10;
-      double obj = 0.0;
+      double obj = 0.0, rho_new = rho_in;
       Resid R = {0, 0, 0, 0, 0, 0, 0, 0};
       if (can_check) {
         R = compute_residuals<G>(M, B, inst, gl, gm, rs);
         obj = R.obj;
         if (check_termination<G>(M, B, S, inst, gl, gm, rs, R, 0, &status, &obj)) done = true;
+      }
+      if (!done && can_adapt) {  // adapt_rho (auxil.c:57-77); the refactorisation itself is a separate launch
+        if (!can_check) { R = compute_residuals<G>(M, B, inst, gl, gm, rs); obj = R.obj; }
+        const double rn = rho_estimate(R, rho_in);
+        if (rn > rho_in * S.adaptive_rho_tolerance || rn < rho_in / S.adaptive_rho_tolerance) {
+          rho_changed = true;
+          rho_new = fmin(fmax(rn, kRhoMin), kRhoMax);
+        }
       }
       if (!done && iter == S.max_iter) {
         if (!can_check) {
@@ -560,10 +639,15 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         }
         done = true;
       }
+      if (rho_changed && gl == 0) {
+        B.rho[inst] = rho_new;
+        B.rho_updates[inst] += 1;
+        atomicAdd(B.sched + 1, 1);
+      }
       if (done) {
         const bool has_sol = !(status == -3 || status == 3 || status == -4 || status == 4 || status == -7);
         if (has_sol) obj = R.obj;
-        const double rho_est = rho_estimate(R, rho_in);
+        const double rho_est = rho_estimate(R, rho_new);
         if (!has_sol) {  // store_solution (auxil.c:527-563)
           if (status == -3 || status == 3) {
             double nrm = 0.0;
@@ -589,9 +673,37 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           B.rho_est[inst] = rho_est;
         }
         drain();
-        have = fetch();
+        have = start_next();
+      } else if (rho_changed) {
+        // parked: the host re-types rho_vec, re-factorises and re-packs this instance, then resumes it
+        if (gl == 0) B.iter[inst] = iter;
+        drain();
+        have = start_next();
       } else {
-        __syncwarp(gm);  // residual scratch aliases the sweep scratch
+        bool yield = false;
+        int myb = 0;
+        if (sched_on && can_check) {
+          // urgency of this instance: distance from its tolerances (auxil.c:259-288, 323-362)
+          const double ep = S.eps_abs + S.eps_rel * fmax(R.nz, R.nAx);
+          const double ed = S.eps_abs + S.eps_rel * fmax(fmax(R.nq, R.nAty), R.nPx);
+          const double ratio = fmax(R.pri / ep, R.dua / ed);
+          myb = ratio > 1.0 ? min(kSchedBuckets - 1, (int)(2.0 * log2(ratio))) : 0;
+          int fresh_left = 0;
+          if (gl == 0) fresh_left = ld_volatile(B.sched) < B.batch;
+          fresh_left = __shfl_sync(gm, fresh_left, 0, G);
+          if (fresh_left) yield = iter >= s0;
+          else yield = sched_best<G>(B, gl, gm) > myb;
+        }
+        if (yield) {
+          if (gl == 0) B.iter[inst] = iter;
+          __threadfence();  // this lane's iterate stores precede the hand-over
+          __syncwarp(gm);
+          if (gl == 0) sched_push(B, myb, inst);
+          drain();
+          have = start_next();
+        } else {
+          __syncwarp(gm);  // residual scratch aliases the sweep scratch
+        }
       }
     }
     __syncwarp();
@@ -601,11 +713,13 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
 // ------------------------------- launcher --------------------------------
 template <class SH>
 static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                   cudaStream_t st) {
+                                   int resume, cudaStream_t st) {
   const int threads = 128, groups = (threads / 32) * SH::GPW;
   int D = 2;  // ring depth: two stage steps of look-ahead cover the HBM latency
   if (const char *e = getenv("RLDL_RING_DEPTH")) D = atoi(e) > 1 ? atoi(e) : 2;
   if (D > 2 * (B.N + 1)) D = 2 * (B.N + 1);
+  int s0 = S.check_termination;  // fresh instances run up to their first check before they may yield
+  if (const char *e = getenv("RLDL_SCHED_S0")) s0 = atoi(e);
   const size_t shm = ((size_t)SH::M_END + (size_t)groups * SH::group_doubles(D)) * sizeof(double);
   if (shm > 220 * 1024) return cudaErrorInvalidValue;
   auto kern = k_admm_stream<SH>;
@@ -620,9 +734,14 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   long long grid = (long long)sms * per_sm;
   const long long need = ((long long)B.batch + groups - 1) / groups;
   if (grid > need) grid = need;
-  e = cudaMemsetAsync(B.work_counter, 0, sizeof(int), st);
+  // scheduler state: counters to 0, every ring slot to -1 (empty)
+  e = cudaMemsetAsync(B.sched, 0, (2 + 2 * kSchedBuckets) * sizeof(int), st);
   if (e != cudaSuccess) return e;
-  kern<<<(unsigned)grid, threads, shm, st>>>(M, B, S, warm_start, D);
+  if (!resume) {  // the rings are empty again at the end of every launch
+    e = cudaMemsetAsync(B.sched_slots, 0xff, (size_t)kSchedBuckets * B.batch * sizeof(int), st);
+    if (e != cudaSuccess) return e;
+  }
+  kern<<<(unsigned)grid, threads, shm, st>>>(M, B, S, warm_start, D, resume, s0);
   return cudaGetLastError();
 }
 
@@ -652,11 +771,11 @@ bool stream_supported(const ModelDev &M, int N) {
 }
 
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                               cudaStream_t st) {
+                               int resume, cudaStream_t st) {
   const int cw = max_c_width(M);
 #define RLDL_X(a_, nx_, ny_, nt_, cw_)                                          \
   if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_)      \
-    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, S, warm_start, st);
+    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, S, warm_start, resume, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;
