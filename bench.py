@@ -62,7 +62,8 @@ def config_dict(name, cfg, n_gpus, extra=None):
 # reference arm / cpu_baseline: the unmodified reference on the host cores
 # ----------------------------------------------------------------------------
 def ref_sample_size(cores):
-    return int(min(2048, max(64, 32 * cores)))
+    # about 20-30 core-seconds of reference work per step (C5: ~11 ms per instance and core)
+    return int(min(4096, max(256, 128 * cores)))
 
 
 def run_reference_sample(mdl, cfg, sample, seed_offset=0):
@@ -294,11 +295,18 @@ def main_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = iter_sum * admm_bytes / (s_ms * 1e-3) / 1e9
-    roof = {"bound": "hbm", "kernel": "k_admm (fused KKT solve + ADMM step, whole solve loop)",
+    # DRAM traffic of the same kernel from the committed ncu --set full capture
+    # (profiles/r01_stream_v4_ncu_full_c5_batch16384.txt: dram read 1.508 TB + write 0.217 TB for
+    # 1.595 TB algorithmic at batch 16384), scaled by the algorithmic bytes of this launch
+    traffic_ratio = (1.508469e12 + 217.423811e9) / 1595449656000.0
+    roof = {"bound": "hbm", "kernel": "k_admm_stream (fused KKT solve + ADMM step + termination, whole solve loop)",
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
-            "traffic": None, "launch_ms": s_ms, "algorithmic_bytes_per_launch": iter_sum * admm_bytes,
-            "factor_kernel": {"launch_ms": f_ms, "achieved": factor_bytes / (f_ms * 1e-3) / 1e9,
+            "traffic": traffic_ratio * iter_sum * admm_bytes,
+            "traffic_source": "ncu dram__bytes_read+write of this kernel at batch 16384 (x%.3f of algorithmic), scaled" % traffic_ratio,
+            "launch_ms": s_ms, "algorithmic_bytes_per_launch": iter_sum * admm_bytes,
+            "factor_kernel": {"kernel": "k_factor_stream (stage recursion, FP64-latency bound: ~10 flop/B)",
+                              "launch_ms": f_ms, "achieved": factor_bytes / (f_ms * 1e-3) / 1e9,
                               "frac": factor_bytes / (f_ms * 1e-3) / 1e9 / peak}}
     mean_iter = allsum(iter_sum) / total
     gb.free()

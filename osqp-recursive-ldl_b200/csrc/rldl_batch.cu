@@ -304,7 +304,7 @@ void Batch::set_sizes() {
 Batch::~Batch() {
   cudaSetDevice(device);
   double *dp[] = {D.q, D.l, D.u, D.rho_vec, D.x, D.z, D.y, D.dx, D.dy, D.Xinv, D.Sinv, D.yk, D.sk,
-                  D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec};
+                  D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec, d_l_alt, d_u_alt};
   for (double *p : dp) if (p) cudaFree(p);
   if (D.iter) cudaFree(D.iter);
   int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx, D.sched, D.sched_slots};
@@ -325,36 +325,67 @@ c_int Batch::ensure_stage(size_t doubles) {
 }
 
 // ------------------------------ operations ------------------------------
-c_int Batch::factor_launch(int k0, bool only_flagged) {
+c_int Batch::factor_launch(int k0, bool only_flagged, bool mark) {
   const int *fl = only_flagged ? d_changed : nullptr;
-  CK(launch_factor(M, D, settings.sigma, k0, fl, stream));
-  launches++;
   if (streaming) {
-    CK(launch_pack_records(M, D, only_flagged ? 0 : k0, 3, fl, stream));
+    // shape-specialised recursion writing the stage records directly; the unpacked pivot inverses are
+    // only produced while a generic-kernel consumer (rldl_batch_kkt_solve, select_kernel(1)) wants them
+    CK(launch_factor_stream(M, D, settings.sigma, k0, fl, need_unpacked ? 1 : 0, stream));
     launches++;
+    if (mark) CK(cudaEventRecord(ev1, stream));  // last_factor_ms times the recursion kernel alone
+    if (!need_unpacked) unpacked_valid = false;
+    CK(launch_pack_records(M, D, only_flagged ? 0 : k0, 2, fl, stream));
+    launches++;
+    records_stale = false;
+  } else {
+    CK(launch_factor(M, D, settings.sigma, k0, fl, stream));
+    launches++;
+    if (mark) CK(cudaEventRecord(ev1, stream));
+    unpacked_valid = true;
   }
+  return 0;
+}
+
+// Generic-kernel consumers read the unpacked pivot inverses: produce them (once) on demand.
+c_int Batch::ensure_unpacked() {
+  if (unpacked_valid) return 0;
+  need_unpacked = true;
+  c_int rc = factor_launch(0, false);
+  if (rc) return rc;
+  unpacked_valid = true;
   return 0;
 }
 
 c_int Batch::factor(int k0, bool only_flagged) {
   CK(cudaSetDevice(device));
   CK(cudaEventRecord(ev0, stream));
-  c_int rc = factor_launch(k0, only_flagged);
+  c_int rc = factor_launch(k0, only_flagged, true);
   if (rc) return rc;
-  CK(cudaEventRecord(ev1, stream));
   CK(cudaStreamSynchronize(stream));
   float ms = 0;
   cudaEventElapsedTime(&ms, ev0, ev1);
   last_factor_ms = ms;
-  // algorithmic bytes: factor written once, rho_vec read once, per stage and instance
-  const double per_stage = (double)a * a + (double)nx * nx + b;
-  factor_bytes = 8.0 * batch * ((N - k0) * per_stage + (double)nx * nx + nt);
+  // algorithmic bytes: pivot inverses written once (diagonal-packed records on the streaming path),
+  // rho_vec read once, per stage and instance
+  const double per_stage = streaming ? (double)D.PX + D.PS + b : (double)a * a + (double)nx * nx + b;
+  factor_bytes = 8.0 * batch * ((N - k0) * per_stage + (streaming ? (double)D.PX : (double)nx * nx) + nt);
   return 0;
 }
 
 c_int Batch::solve() {
   CK(cudaSetDevice(device));
   CK(cudaEventRecord(ev0, stream));
+  if (use_stream() && records_stale) {  // a generic-kernel adaptive solve re-factorised behind the records
+    CK(launch_set_rho_vec(D, D.m, nullptr, stream));
+    launches++;
+    c_int rc = factor_launch(0, false);
+    if (rc) return rc;
+  }
+  if (!use_stream()) {
+    c_int rc = ensure_unpacked();
+    if (rc) return rc;
+    if (streaming && settings.adaptive_rho) records_stale = true;
+  }
   if (use_stream()) {
     // Adaptive rho: an instance whose rho changes parks itself (osqp_update_rho, osqp.c:1268-1319, needs a
     // full stage recursion); parked instances are re-typed, re-factorised and re-packed together, then resumed.
@@ -418,11 +449,28 @@ c_int Batch::reset_info() {
   return 0;
 }
 
-c_int Batch::update_bounds(const c_float *l, const c_float *u, bool have_l, bool have_u) {
+c_int Batch::update_bounds(const c_float *l, const c_float *u, bool have_l, bool have_u, bool validate) {
   CK(cudaSetDevice(device));
   const size_t bytes = (size_t)batch * D.mmax * sizeof(double);
-  if (have_l) CK(cudaMemcpyAsync(D.l, l, bytes, cudaMemcpyHostToDevice, stream));
-  if (have_u) CK(cudaMemcpyAsync(D.u, u, bytes, cudaMemcpyHostToDevice, stream));
+  if (validate) {
+    // the new bounds land in a second pair of buffers, l <= u is checked on the device, and only then
+    // do they become current (invalid input leaves the problem untouched, osqp.c:793-801)
+    if (!d_l_alt) CK(cudaMalloc(&d_l_alt, bytes));
+    if (!d_u_alt) CK(cudaMalloc(&d_u_alt, bytes));
+    if (have_l) CK(cudaMemcpyAsync(d_l_alt, l, bytes, cudaMemcpyHostToDevice, stream));
+    if (have_u) CK(cudaMemcpyAsync(d_u_alt, u, bytes, cudaMemcpyHostToDevice, stream));
+    CK(launch_check_bounds(have_l ? d_l_alt : D.l, have_u ? d_u_alt : D.u, D.mmax, D.m, batch, D.sched + 1, stream));
+    launches++;
+    int bad = 0;
+    CK(cudaMemcpyAsync(&bad, D.sched + 1, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    if (bad) return 1;
+    if (have_l) std::swap(D.l, d_l_alt);
+    if (have_u) std::swap(D.u, d_u_alt);
+  } else {
+    if (have_l) CK(cudaMemcpyAsync(D.l, l, bytes, cudaMemcpyHostToDevice, stream));
+    if (have_u) CK(cudaMemcpyAsync(D.u, u, bytes, cudaMemcpyHostToDevice, stream));
+  }
   c_int rc = reset_info();
   if (rc) return rc;
   rc = retype_and_refactor();
@@ -500,7 +548,9 @@ c_int Batch::kkt_solve(c_float *rhs) {
   CK(cudaSetDevice(device));
   const int ld = D.n + D.m;
   const size_t cnt = (size_t)batch * ld;
-  c_int rc = ensure_stage(cnt);
+  c_int rc = ensure_unpacked();
+  if (rc) return rc;
+  rc = ensure_stage(cnt);
   if (rc) return rc;
   CK(cudaMemcpyAsync(d_stage, rhs, cnt * sizeof(double), cudaMemcpyHostToDevice, stream));
   CK(launch_kkt_solve(M, D, S, d_stage, ld, stream));

@@ -14,6 +14,9 @@ struct Batch {
   bool generic = false;  // osqp_setup path: one dense stage (N == 0)
   int kernel_choice = 0;   // 0 auto, 1 force the generic (runtime-shape) ADMM kernel
   bool streaming = false;  // shapes the streaming kernels cover (rldl_stream.cu)
+  bool need_unpacked = false;   // a generic-kernel consumer wants Xinv/Sinv unpacked as well as the records
+  bool unpacked_valid = false;  // D.Xinv / D.Sinv match the current factorisation
+  bool records_stale = false;   // the generic adaptive-rho kernel re-factorised without refreshing the records
   int nx = 0, nu = 0, ny = 0, nt = 0, a = 0, b = 0, N = 0, Nmax = 0, batch = 0, nmax = 0, mmax = 0;
   OSQPSettings settings;
   ModelDev M;
@@ -23,6 +26,7 @@ struct Batch {
   int *d_midx = nullptr;
   int *d_changed = nullptr;
   double *d_stage = nullptr;
+  double *d_l_alt = nullptr, *d_u_alt = nullptr;  // landing buffers of validated bound updates
   size_t stage_cap = 0;
   double *h_pin = nullptr;
   cudaStream_t stream = nullptr;
@@ -43,13 +47,14 @@ struct Batch {
   void set_sizes();
   c_int ensure_stage(size_t doubles);
   c_int factor(int k0, bool only_flagged);
-  c_int factor_launch(int k0, bool only_flagged);  // kernels only, no events / sync
+  c_int factor_launch(int k0, bool only_flagged, bool mark = false);  // kernels only, no events / sync
+  c_int ensure_unpacked();
   c_int pack(int k0, int parts);
   bool use_stream() const;
   c_int solve();
   c_int retype_and_refactor();
   c_int reset_info();
-  c_int update_bounds(const c_float *l, const c_float *u, bool have_l, bool have_u);
+  c_int update_bounds(const c_float *l, const c_float *u, bool have_l, bool have_u, bool validate = false);
   c_int partial_update_bounds(c_int start, c_int stop, const c_float *l, const c_float *u);
   c_int update_lin_cost(const c_float *q);
   c_int warm_start(const c_float *x, const c_float *y);

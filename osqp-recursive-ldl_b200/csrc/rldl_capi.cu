@@ -716,14 +716,9 @@ c_int rldl_batch_setup(RLDLBatch **out, const OSQPDataRLDL *model, const OSQPSet
 c_int rldl_batch_solve(RLDLBatch *h) { HB(h); return h->b->solve(); }
 c_int rldl_batch_update_bounds(RLDLBatch *h, const c_float *l, const c_float *u) {
   HB(h);
-  Batch *B = h->b;
-  for (int i = 0; i < B->batch; i++)
-    for (int r = 0; r < B->D.m; r++)
-      if (l[(size_t)i * B->mmax + r] > u[(size_t)i * B->mmax + r]) {
-        fprintf(stderr, "ERROR in rldl_batch_update_bounds: lower bound must be lower than or equal to upper bound\n");
-        return 1;
-      }
-  return B->update_bounds(l, u, true, true);
+  const c_int rc = h->b->update_bounds(l, u, true, true, true);  // l <= u is validated on the device
+  if (rc == 1) fprintf(stderr, "ERROR in rldl_batch_update_bounds: lower bound must be lower than or equal to upper bound\n");
+  return rc;
 }
 c_int rldl_batch_partial_update_bounds(RLDLBatch *h, c_int start, c_int stop, const c_float *l, const c_float *u) {
   HB(h);

@@ -203,6 +203,19 @@ __global__ void k_warm_start_z(ModelDev M, BatchDev B) {
       [&](int, double, double, double) {});
 }
 
+// l <= u over the active rows [0,m) of every instance (osqp_update_bounds precondition, osqp.c:793-801)
+__global__ void k_check_bounds(const double *l, const double *u, int ld, int m, int batch, int *bad) {
+  const size_t tot = (size_t)batch * m;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t st = (size_t)gridDim.x * blockDim.x;
+  int b = 0;
+  for (; i < tot; i += st) {
+    const size_t inst = i / m, r = i - inst * m;
+    if (l[inst * ld + r] > u[inst * ld + r]) b = 1;
+  }
+  if (__any_sync(FULL, b) && (threadIdx.x & 31) == 0) atomicOr(bad, 1);
+}
+
 __global__ void k_fill(double *p, double v, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t st = (size_t)gridDim.x * blockDim.x;
@@ -284,6 +297,14 @@ cudaError_t launch_warm_start_z(const ModelDev &M, const BatchDev &B, cudaStream
   cudaError_t e = cudaFuncSetAttribute(k_warm_start_z, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm);
   if (e != cudaSuccess) return e;
   k_warm_start_z<<<(B.batch + wpb - 1) / wpb, wpb * 32, shm, st>>>(M, B);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_check_bounds(const double *l, const double *u, int ld, int m, int batch, int *bad,
+                                cudaStream_t st) {
+  cudaError_t e = cudaMemsetAsync(bad, 0, sizeof(int), st);
+  if (e != cudaSuccess) return e;
+  k_check_bounds<<<148 * 8, 256, 0, st>>>(l, u, ld, m, batch, bad);
   return cudaGetLastError();
 }
 

@@ -14,6 +14,8 @@ cudaError_t launch_admm(const ModelDev &M, const BatchDev &B, const SettingsDev 
 cudaError_t launch_kkt_solve(const ModelDev &M, const BatchDev &B, const SettingsDev &S, double *rhs,
                              int ld, cudaStream_t st);
 cudaError_t launch_warm_start_z(const ModelDev &M, const BatchDev &B, cudaStream_t st);
+cudaError_t launch_check_bounds(const double *l, const double *u, int ld, int m, int batch, int *bad,
+                                cudaStream_t st);
 cudaError_t launch_fill(double *p, double v, size_t n, cudaStream_t st);
 cudaError_t launch_scatter_rows(double *dst, int ld, const double *src, int len, int start, int batch,
                                 cudaStream_t st);
@@ -24,4 +26,6 @@ cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, in
                                 cudaStream_t st);
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                                int resume, cudaStream_t st);
+cudaError_t launch_factor_stream(const ModelDev &M, const BatchDev &B, double sigma, int k0,
+                                 const int *only_flagged, int write_unpacked, cudaStream_t st);
 }  // namespace rldl

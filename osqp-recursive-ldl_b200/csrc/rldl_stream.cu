@@ -745,6 +745,245 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------
+// Shape-specialised stage recursion (reference src/recursive_ldl.c:1139-1318; tail restart
+// :946-1110): one instance per group of G lanes, lane i owns ROW i of the current pivot block in
+// registers.  Each SPD pivot block is inverted in place by symmetric sweeps (sweep operator:
+// after sweeping every pivot the block holds -inverse); the pivot row is broadcast through a
+// double-buffered shared-memory line, so a sweep costs A/2 broadcast LDS.128 + A DFMA per lane
+// and one __syncwarp.  The inverses are written straight into the stage records in the
+// diagonal-packed form the streaming ADMM kernel reads (and, on request, unpacked for the
+// generic kernels).  Requires ELL width 1 path rows (C' diag(rho) C diagonal), as the table.
+//   M_k = Q_k + sigma I + C' rho C;  X_0 = M_0;  S_k = diag(1/rho_d) + F X_k^-1 F';
+//   X_{k+1} = M_{k+1} + J' S_k^-1 J
+// ---------------------------------------------------------------------------
+template <int NP, int NE>
+__device__ __forceinline__ void sweep_rows(double (&X)[NP], double *rowbuf, int gl, unsigned gm, int &bad) {
+  // X = this lane's row of an NP x NP SPD block (lanes >= NP hold zero rows); NE = even_up(NP)
+#pragma unroll
+  for (int p = 0; p < NP; p++) {
+    double *buf = rowbuf + (p & 1) * NE;
+    if (gl == p) {
+#pragma unroll
+      for (int j = 0; j < NP; j++) buf[j] = X[j];
+    }
+    __syncwarp(gm);
+    double rp[NP];
+#pragma unroll
+    for (int j = 0; j < NP; j++) rp[j] = buf[j];
+    if (!(rp[p] > 0.0)) bad = 1;
+    const double d = 1.0 / rp[p];
+    const double f = (gl == p) ? (1.0 - d) : X[p] * d;
+#pragma unroll
+    for (int j = 0; j < NP; j++)
+      if (j != p) X[j] = fma(-f, rp[j], X[j]);
+    X[p] = (gl == p) ? -d : f;
+  }
+#pragma unroll
+  for (int j = 0; j < NP; j++) X[j] = -X[j];
+}
+
+template <class SH>
+__global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B, double sigma, int k0,
+                                                          const int *only_flagged, int write_unpacked) {
+  constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, CW = SH::CW, G = SH::G, RS = SH::RS, BQ = SH::B;
+  constexpr int AE = SH::AE, NXE = SH::NXE;
+  constexpr int TB = A * A > A * NXE ? A * A : A * NXE;          // transposition buffer (doubles)
+  constexpr int M_F = 0, M_FT = M_F + 2 * A * NX, M_Q = M_FT + 2 * A * NX, M_C2 = M_Q + 3 * A * A,
+                M_CI = M_C2 + 3 * AE, M_END = (M_CI + (3 * AE + 1) / 2 + 1) & ~1;
+  extern __shared__ __align__(16) double smem[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int gl = lane & (G - 1), gw = lane / G;
+  const unsigned gm = (G == 32) ? FULL : (((1u << G) - 1u) << (gw * G));
+  const int grp = wid * SH::GPW + gw, groups = (blockDim.x >> 5) * SH::GPW;
+  const int N = B.N;
+
+  // ---- CTA-shared model: dense F / F' (class 0, 1), Q blocks padded to A x A, squared C' entries ----
+  double *Fd = smem + M_F, *FdT = smem + M_FT, *Qs = smem + M_Q, *c2 = smem + M_C2;
+  int *ci = reinterpret_cast<int *>(smem + M_CI);
+  for (int e = threadIdx.x; e < M_END; e += blockDim.x) smem[e] = 0.0;
+  __syncthreads();
+  for (int t = threadIdx.x; t < 2 * NX; t += blockDim.x) {
+    const int c = t / NX, r = t - c * NX;
+    const Ell &E = M.sc[c].F;
+    for (int e = 0; e < E.width; e++) {
+      const double v = M.val[E.off + r * E.width + e];
+      const int j = M.idx[E.off + r * E.width + e];
+      if (v != 0.0) {
+        Fd[c * A * NX + j * NX + r] = v;
+        FdT[c * A * NX + r * A + j] = v;
+      }
+    }
+  }
+  for (int t = threadIdx.x; t < 3 * A * A; t += blockDim.x) {
+    const int c = t / (A * A), e = t - c * A * A, j = e / A, i = e - j * A;
+    const int dim = (c == 2) ? NX : A;
+    Qs[t] = (i < dim && j < dim) ? M.val[M.sc[c].Q + j * dim + i] : (i == j ? 1.0 : 0.0);
+  }
+  for (int t = threadIdx.x; t < 3 * AE; t += blockDim.x) {
+    const int c = t / AE, r = t - c * AE;
+    const Ell &E = M.sc[c].Ct;
+    if (r < E.rows && E.width > 0) {
+      const double v = M.val[E.off + r * E.width];
+      c2[t] = v * v;
+      ci[t] = M.idx[E.off + r * E.width];
+    }
+  }
+  __syncthreads();
+  double *gbuf = smem + M_END + (size_t)grp * (2 * AE + TB);
+  double *rowbuf = gbuf, *tb = gbuf + 2 * AE;
+
+  for (int inst = blockIdx.x * groups + grp; inst < B.batch; inst += gridDim.x * groups) {
+    if (only_flagged && !only_flagged[inst]) continue;
+    const double *rv = B.rho_vec + (size_t)inst * B.mmax;
+    double *rec = B.rec + (size_t)inst * B.rec_stride;
+    double Sx[NX];  // row gl of Sinv_{k-1} (lanes < NX)
+#pragma unroll
+    for (int j = 0; j < NX; j++) Sx[j] = 0.0;
+    if (k0 > 0 && gl < NX) {  // tail restart: Sinv_{k0-1} from its diagonal-packed record
+      const double *dp = rec + (size_t)(k0 - 1) * RS + SH::SOFF;
+#pragma unroll
+      for (int j = 0; j < NX; j++) {
+        int d = j - gl;
+        if (d < 0) d += NX;
+        Sx[j] = (d <= NX / 2) ? dp[d * NX + gl] : dp[(NX - d) * NX + j];
+      }
+    }
+    double Fr[A];  // row gl of F (lanes < NX), class 0 at stage 0, class 1 after
+    int flag = 0;
+    for (int k = k0; k <= N; k++) {
+      const bool term = (k == N);
+      const int cls = term ? 2 : (k == 0 ? 0 : 1);
+      const int dim = term ? NX : A;
+      const int roff = k * BQ;
+      double *rk = rec + (size_t)k * RS;
+      // ---- X_k row gl ----
+      double Xr[A];
+#pragma unroll
+      for (int j = 0; j < A; j++) Xr[j] = (gl < A) ? Qs[cls * A * A + j * A + gl] : 0.0;
+      if (gl < dim) {
+        double dg = sigma;
+        const double cc = c2[cls * AE + gl];
+        if (cc != 0.0) dg = fma(cc, rv[roff + ci[cls * AE + gl]], dg);
+#pragma unroll
+        for (int j = 0; j < A; j++)
+          if (j == gl) Xr[j] += dg;
+        if (k > 0 && gl < NX) {
+#pragma unroll
+          for (int j = 0; j < NX; j++) Xr[j] += Sx[j];
+        }
+      }
+      int bad = 0;
+      sweep_rows<A, AE>(Xr, rowbuf, gl, gm, bad);
+      if (bad && !flag) flag = 1 + k;
+      // ---- store Xinv_k: diagonal-packed into the record (and unpacked on request) ----
+      __syncwarp(gm);
+      if (gl < A) {
+#pragma unroll
+        for (int j = 0; j < A; j++) tb[j * A + gl] = Xr[j];  // symmetric: column-major == row-major
+      }
+      __syncwarp(gm);
+      if (gl < A) {
+#pragma unroll
+        for (int d = 0; d <= A / 2; d++) {
+          int j = gl + d;
+          if (j >= A) j -= A;
+          rk[SH::XOFF + d * A + gl] = tb[j * A + gl];
+        }
+      }
+      if (write_unpacked && gl < dim) {
+        double *Xk = B.Xinv + (size_t)inst * B.xstride + (size_t)k * A * A + (size_t)gl * dim;
+#pragma unroll
+        for (int j = 0; j < A; j++)
+          if (j < dim) Xk[j] = Xr[j];
+      }
+      if (term) break;
+      // ---- W = Xinv F' (row gl), S = diag(1/rho_d) + F W (row gl, lanes < NX) ----
+      if (k == k0 || k == 1) {
+#pragma unroll
+        for (int i = 0; i < A; i++) Fr[i] = (gl < NX) ? Fd[(k == 0 ? 0 : A * NX) + i * NX + gl] : 0.0;
+      }
+      const double *Ft = FdT + (k == 0 ? 0 : A * NX);
+      __syncwarp(gm);
+      if (gl < A) {
+#pragma unroll
+        for (int r = 0; r < NX; r++) {
+          double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+          for (int j = 0; j < A; j += 2) {
+            acc0 = fma(Xr[j], Ft[r * A + j], acc0);
+            if (j + 1 < A) acc1 = fma(Xr[j + 1], Ft[r * A + j + 1], acc1);
+          }
+          tb[gl * NXE + r] = acc0 + acc1;
+        }
+      }
+      __syncwarp(gm);
+#pragma unroll
+      for (int c = 0; c < NX; c++) Sx[c] = 0.0;
+#pragma unroll
+      for (int i = 0; i < A; i++) {
+#pragma unroll
+        for (int c = 0; c < NX; c++) Sx[c] = fma(Fr[i], tb[i * NXE + c], Sx[c]);
+      }
+      if (gl < NX) {
+        const double rinv = 1.0 / rv[roff + NY + gl];
+#pragma unroll
+        for (int c = 0; c < NX; c++)
+          if (c == gl) Sx[c] += rinv;
+      }
+      bad = 0;
+      sweep_rows<NX, NXE>(Sx, rowbuf, gl, gm, bad);
+      if (bad && !flag) flag = 1 + k;
+      // ---- store Sinv_k ----
+      __syncwarp(gm);
+      if (gl < NX) {
+#pragma unroll
+        for (int j = 0; j < NX; j++) tb[j * NX + gl] = Sx[j];
+      }
+      __syncwarp(gm);
+      if (gl < NX) {
+#pragma unroll
+        for (int d = 0; d <= NX / 2; d++) {
+          int j = gl + d;
+          if (j >= NX) j -= NX;
+          rk[SH::SOFF + d * NX + gl] = tb[j * NX + gl];
+        }
+        if (write_unpacked) {
+          double *Sk = B.Sinv + (size_t)inst * B.sstride + (size_t)k * NX * NX + (size_t)gl * NX;
+#pragma unroll
+          for (int j = 0; j < NX; j++) Sk[j] = Sx[j];
+        }
+      }
+      __syncwarp(gm);
+    }
+    if (gl == 0) B.fact_flag[inst] = flag;
+  }
+}
+
+template <class SH>
+static cudaError_t launch_factor_stream_t(const ModelDev &M, const BatchDev &B, double sigma, int k0,
+                                          const int *only_flagged, int write_unpacked, cudaStream_t st) {
+  constexpr int A = SH::A, NX = SH::NX, AE = SH::AE, NXE = SH::NXE;
+  constexpr int TB = A * A > A * NXE ? A * A : A * NXE;
+  constexpr int M_END = ((2 * A * NX) * 2 + 3 * A * A + 3 * AE + (3 * AE + 1) / 2 + 1) & ~1;
+  const int threads = 128, groups = (threads / 32) * SH::GPW;
+  const size_t shm = ((size_t)M_END + (size_t)groups * (2 * AE + TB)) * sizeof(double);
+  auto kern = k_factor_stream<SH>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm);
+  if (e != cudaSuccess) return e;
+  int dev = 0, sms = 148, per_sm = 1;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, shm);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) per_sm = 1;
+  long long grid = (long long)sms * per_sm;
+  const long long need = ((long long)B.batch + groups - 1) / groups;
+  if (grid > need) grid = need;
+  kern<<<(unsigned)grid, threads, shm, st>>>(M, B, sigma, k0, only_flagged, write_unpacked);
+  return cudaGetLastError();
+}
+
 // The specialisation table: (nx+nu, nx, ny, nt, ELL width of C) of the BASELINE.json shapes.
 #define RLDL_SHAPES(X) \
   X(6, 4, 6, 4, 1)     \
@@ -776,6 +1015,17 @@ cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const Setti
 #define RLDL_X(a_, nx_, ny_, nt_, cw_)                                          \
   if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_)      \
     return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, S, warm_start, resume, st);
+  RLDL_SHAPES(RLDL_X)
+#undef RLDL_X
+  return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_factor_stream(const ModelDev &M, const BatchDev &B, double sigma, int k0,
+                                 const int *only_flagged, int write_unpacked, cudaStream_t st) {
+  const int cw = max_c_width(M);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_)                                          \
+  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_)      \
+    return launch_factor_stream_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, sigma, k0, only_flagged, write_unpacked, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;

@@ -51,3 +51,60 @@ def test_streaming_kernel_matches_generic_kernel(name, batch):
         gb.free()
     bad = compare(outs[0], outs[1], n, m)
     assert not bad, bad[:5]
+
+
+def test_scheduler_does_not_change_results(monkeypatch):
+    """The device priority scheduler only reorders / migrates instances: with a batch large enough to
+    oversubscribe the groups and force preemptions, results are bitwise those of first-come order."""
+    mdl, N, x0, q, l, u = problem("C1", 40000)
+    outs = []
+    for s0 in ("0", "25"):
+        monkeypatch.setenv("RLDL_SCHED_S0", s0)
+        gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+        assert gb.solve() == 0
+        outs.append(gb.get())
+        gb.free()
+    assert (outs[0]["iter"] == outs[1]["iter"]).all() and (outs[0]["status"] == outs[1]["status"]).all()
+    assert np.array_equal(outs[0]["x"], outs[1]["x"]) and np.array_equal(outs[0]["y"], outs[1]["y"])
+    assert outs[0]["iter"].max() > outs[0]["iter"].min()  # the batch really is imbalanced
+
+
+@pytest.mark.parametrize("name,batch", [("C4", 48), ("C1", 64)])
+def test_adaptive_rho_streaming_matches_generic_kernel(name, batch):
+    """Adaptive rho: the streaming kernel parks an instance, the host re-factorises the parked ones in one
+    batched launch and resumes them; the generic kernel re-factorises in place.  Same iteration."""
+    mdl, N, x0, q, l, u = problem(name, batch)
+    rng = np.random.default_rng(5)
+    rho = rng.choice([1e-3, 0.1, 10.0], size=batch)
+    outs = []
+    for which in (0, 1):
+        gb = R.Batch(mdl, N, N, q, l, u, gpu_settings(adaptive_rho=1, adaptive_rho_interval=25,
+                                                      adaptive_rho_tolerance=1.5), rho=rho)
+        assert gb.select_kernel(which) == 0
+        assert gb.solve() == 0
+        outs.append(gb.get())
+        n, m, _, _ = gb.dims()
+        gb.free()
+    assert outs[0]["rho_updates"].sum() > 0
+    assert (outs[0]["rho_updates"] == outs[1]["rho_updates"]).all()
+    bad = compare(outs[0], outs[1], n, m)
+    assert not bad, bad[:5]
+    # rho_estimate is a ratio of converged (1e-6-sized) residuals: only its magnitude is comparable
+    assert np.allclose(outs[0]["rho_estimate"], outs[1]["rho_estimate"], rtol=0.5)
+
+
+def test_batch_update_bounds_rejects_l_above_u_and_keeps_problem():
+    """osqp_update_bounds semantics (osqp.c:793-801) for the batch entry point: validated on the device,
+    invalid input returns 1 and leaves the resident problem untouched."""
+    mdl, N, x0, q, l, u = problem("C1", 16)
+    gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+    assert gb.solve() == 0
+    ref = gb.get()
+    lbad = l.copy()
+    lbad[3, 7] = u[3, 7] + 1.0
+    assert gb.update_bounds(lbad, u) == 1
+    assert gb.solve() == 0
+    out = gb.get()
+    assert (out["iter"] == ref["iter"]).all() and np.array_equal(out["x"], ref["x"])
+    assert gb.update_bounds(l, u) == 0
+    gb.free()
