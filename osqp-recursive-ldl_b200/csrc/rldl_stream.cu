@@ -172,11 +172,15 @@ struct Shape {
   static constexpr uint32_t FWD_BYTES = 8u * (QA + PX + PS + BB), BWD_BYTES = 8u * (PX + PS + 3 * BB);
   // per-group scratch (doubles, every block even-sized)
   static constexpr int AE = (A + 1) & ~1, NXE = (NX + 1) & ~1;
+  // the vectors of the forward sweep (w, tv2, yv, td2, sp) and of the backward sweep (vn2, vc, nud, gg2)
+  // are never live together, so the two sets share one region (4 CTAs/SM need <= 56 KB per CTA)
   static constexpr int O_W = 0, O_TV2 = O_W + ROWS, O_YV = O_TV2 + 2 * AE, O_TD2 = O_YV + AE, O_SP = O_TD2 + 2 * NXE,
-                       O_VN2 = O_SP + NXE, O_VC = O_VN2 + 2 * NXE, O_NUD = O_VC + AE, O_GG2 = O_NUD + NXE,
-                       SC_SWEEP = O_GG2 + 2 * AE;
+                       SC_FWD = O_SP + NXE;
+  static constexpr int O_VN2 = 0, O_VC = O_VN2 + 2 * NXE, O_NUD = O_VC + AE, O_GG2 = O_NUD + NXE, SC_BWD = O_GG2 + 2 * AE;
+  static constexpr int SC_SWEEP = SC_FWD > SC_BWD ? SC_FWD : SC_BWD;
   static constexpr int VM = (A > RMAX ? A : RMAX);
-  static constexpr int SC = SC_SWEEP > 8 * VM ? SC_SWEEP : 8 * VM;  // the residual routines alias the sweep scratch
+  // the residual routines (5 vectors of VM doubles) alias the sweep scratch between iterations
+  static constexpr int SC = SC_SWEEP > 5 * VM ? SC_SWEEP : 5 * VM;
   // CTA-shared model block (doubles)
   static constexpr int M_FD = 0, M_FDT = M_FD + 2 * A * NX, M_CV = M_FDT + 2 * A * NX, M_CTV = M_CV + 3 * ROWS * CW,
                        M_CI = M_CTV + 3 * AE * CW,                       // ints from here: 3*ROWS*CW
@@ -333,7 +337,9 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   double *sc = gb + D * RS + D;
   double *w = sc + SH::O_W, *tv2 = sc + SH::O_TV2, *yvs = sc + SH::O_YV, *td2 = sc + SH::O_TD2, *sp = sc + SH::O_SP,
          *vn2 = sc + SH::O_VN2, *vcur = sc + SH::O_VC, *nudv = sc + SH::O_NUD, *gg2 = sc + SH::O_GG2;
-  const Scratch rs = make_scratch(sc, SH::VM);  // residual routines alias the sweep scratch
+  Scratch rs;  // residual routines alias the sweep scratch; product_sweep touches v, w, vn, td, sp only
+  rs.v = sc; rs.w = sc + SH::VM; rs.vn = sc + 2 * SH::VM; rs.td = sc + 3 * SH::VM; rs.sp = sc + 4 * SH::VM;
+  rs.g = rs.yv = rs.nud = nullptr;
   if (gl == 0)
     for (int d = 0; d < D; d++) mbar_init(&bars[d], 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -731,6 +737,11 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, shm);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
+  // 3 CTAs/SM already saturate HBM (measured 5.1 TB/s algorithmic); a 4th only lengthens every instance's
+  // iteration (bandwidth is shared equally) and with it the critical path of the longest instance
+  int cap = 3;
+  if (const char *e = getenv("RLDL_CTAS_PER_SM")) cap = atoi(e) > 0 ? atoi(e) : cap;
+  if (per_sm > cap) per_sm = cap;
   long long grid = (long long)sms * per_sm;
   const long long need = ((long long)B.batch + groups - 1) / groups;
   if (grid > need) grid = need;
