@@ -374,6 +374,11 @@ c_int rldl_batch_partial_update_bounds(RLDLBatch *b, c_int start, c_int stop,
 c_int rldl_batch_update_lin_cost(RLDLBatch *b, const c_float *q);
 /* batched osqp_warm_start (x or y may be NULL: osqp_warm_start_y / _x) */
 c_int rldl_batch_warm_start(RLDLBatch *b, const c_float *x, const c_float *y);
+/* receding-horizon warm start without a host round trip: the resident (x, y) of the last solve are
+ * moved one stage towards the origin on the device (x[0:n-a] <- x[a:n], y[0:m-b] <- y[b:m], tails kept —
+ * what a reference user does with memmove before osqp_warm_start, osqp.c:929-994); z = A x is formed
+ * at the next solve, after any horizon / bound update made in between */
+c_int rldl_batch_warm_start_shift(RLDLBatch *b);
 /* batched osqp_update_recursive */
 c_int rldl_batch_update_horizon(RLDLBatch *b, c_int N);
 /* batched osqp_update_rho (per-instance value) */

@@ -15,12 +15,13 @@ def shift_one_stage(x, y, n, m, a, b):
     return xs, ys
 
 
-def receding_horizon(api, mdl, N0, Nmax, x0, T, shrink_every=2, feedback=None):
+def receding_horizon(api, mdl, N0, Nmax, x0, T, shrink_every=2, feedback=None, device_shift=False):
     """solve -> apply u0 -> x0 <- A x0 + B u0 -> update_bounds ->
     warm start from the shifted previous solution -> every `shrink_every`-th step shrink the
     horizon by one stage (osqp_update_recursive), last step grow back to N0.
     `feedback[t]` (batch x nu), when given, replaces the implementation's own u0 so that
-    every implementation sees identical problem data at every step."""
+    every implementation sees identical problem data at every step.  `device_shift` uses the
+    api's own warm_start_shift() (rldl_batch_warm_start_shift) instead of shifting on the host."""
     nx, nu = mdl.nx, mdl.nu
     a, b = nx + nu, nx + mdl.ny
     N, xcur, out = N0, np.array(x0, float), []
@@ -35,7 +36,10 @@ def receding_horizon(api, mdl, N0, Nmax, x0, T, shrink_every=2, feedback=None):
             break
         u0 = r["x"][:, :nu] if feedback is None else feedback[t]
         xcur = xcur @ mdl.A.T + u0 @ mdl.B.T
-        xs, ys = shift_one_stage(r["x"], r["y"], n, m, a, b)
+        if device_shift:
+            assert api.warm_start_shift() == 0
+        else:
+            xs, ys = shift_one_stage(r["x"], r["y"], n, m, a, b)
         Nnew = N
         if (t + 1) % shrink_every == 0:
             Nnew = N - 1
@@ -46,5 +50,6 @@ def receding_horizon(api, mdl, N0, Nmax, x0, T, shrink_every=2, feedback=None):
             N = Nnew
         q, l, u = mdl.vectors(xcur, N, Nmax)
         assert api.update_bounds(l, u) == 0
-        assert api.warm_start(xs, ys) == 0
+        if not device_shift:
+            assert api.warm_start(xs, ys) == 0
     return out

@@ -375,6 +375,11 @@ c_int Batch::factor(int k0, bool only_flagged) {
 c_int Batch::solve() {
   CK(cudaSetDevice(device));
   CK(cudaEventRecord(ev0, stream));
+  if (z_pending) {
+    CK(launch_warm_start_z(M, D, stream));
+    launches++;
+    z_pending = false;
+  }
   if (use_stream() && records_stale) {  // a generic-kernel adaptive solve re-factorised behind the records
     CK(launch_set_rho_vec(D, D.m, nullptr, stream));
     launches++;
@@ -511,8 +516,19 @@ c_int Batch::warm_start(const c_float *x, const c_float *y) {
   settings.warm_start = 1;  // osqp.c:935
   if (x) CK(cudaMemcpyAsync(D.x, x, (size_t)batch * D.nmax * sizeof(double), cudaMemcpyHostToDevice, stream));
   if (y) CK(cudaMemcpyAsync(D.y, y, (size_t)batch * D.mmax * sizeof(double), cudaMemcpyHostToDevice, stream));
-  if (x) { CK(launch_warm_start_z(M, D, stream)); launches++; }
+  if (x) { CK(launch_warm_start_z(M, D, stream)); launches++; z_pending = false; }
   CK(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+c_int Batch::warm_start_shift() {
+  CK(cudaSetDevice(device));
+  if (generic) return -1;
+  settings.warm_start = 1;  // osqp.c:935
+  CK(launch_shift_rows(D.x, D.nmax, D.n, a, batch, stream));
+  CK(launch_shift_rows(D.y, D.mmax, D.m, b, batch, stream));
+  launches += 2;
+  z_pending = true;  // z = A x at the next solve, with the sizes and bounds current by then
   return 0;
 }
 

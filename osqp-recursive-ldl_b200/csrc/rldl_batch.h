@@ -16,6 +16,7 @@ struct Batch {
   bool streaming = false;  // shapes the streaming kernels cover (rldl_stream.cu)
   bool need_unpacked = false;   // a generic-kernel consumer wants Xinv/Sinv unpacked as well as the records
   bool unpacked_valid = false;  // D.Xinv / D.Sinv match the current factorisation
+  bool z_pending = false;       // warm_start_shift moved x: z = A x is formed at the next solve
   bool records_stale = false;   // the generic adaptive-rho kernel re-factorised without refreshing the records
   int nx = 0, nu = 0, ny = 0, nt = 0, a = 0, b = 0, N = 0, Nmax = 0, batch = 0, nmax = 0, mmax = 0;
   OSQPSettings settings;
@@ -58,6 +59,7 @@ struct Batch {
   c_int partial_update_bounds(c_int start, c_int stop, const c_float *l, const c_float *u);
   c_int update_lin_cost(const c_float *q);
   c_int warm_start(const c_float *x, const c_float *y);
+  c_int warm_start_shift();
   c_int update_horizon(c_int Nnew);
   c_int update_rho(const c_float *rho);
   c_int refactor();

@@ -730,6 +730,7 @@ c_int rldl_batch_partial_update_bounds(RLDLBatch *h, c_int start, c_int stop, co
 }
 c_int rldl_batch_update_lin_cost(RLDLBatch *h, const c_float *q) { HB(h); return h->b->update_lin_cost(q); }
 c_int rldl_batch_warm_start(RLDLBatch *h, const c_float *x, const c_float *y) { HB(h); return h->b->warm_start(x, y); }
+c_int rldl_batch_warm_start_shift(RLDLBatch *h) { HB(h); return h->b->warm_start_shift(); }
 c_int rldl_batch_update_horizon(RLDLBatch *h, c_int N) { HB(h); return h->b->update_horizon(N); }
 c_int rldl_batch_update_rho(RLDLBatch *h, const c_float *rho) { HB(h); return h->b->update_rho(rho); }
 c_int rldl_batch_refactor(RLDLBatch *h) { HB(h); return h->b->refactor(); }

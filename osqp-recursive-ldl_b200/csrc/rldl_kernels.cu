@@ -216,6 +216,25 @@ __global__ void k_check_bounds(const double *l, const double *u, int ld, int m, 
   if (__any_sync(FULL, b) && (threadIdx.x & 31) == 0) atomicOr(bad, 1);
 }
 
+// In-place shift of every instance's row by `sh` entries towards index 0 over [0,len): one warp per
+// instance, 32-entry chunks in ascending order (a chunk is read completely before it is overwritten,
+// and later chunks only read entries that have not been written yet).  Entries [len,ld) are zeroed,
+// as they are in the vectors rldl_batch_get_solution hands to a host-side shift.
+__global__ void k_shift_rows(double *v, int ld, int len, int sh, int batch) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= batch) return;
+  double *row = v + (size_t)warp * ld;
+  for (int base = 0; base < len - sh; base += 32) {
+    const int i = base + lane;
+    double t = 0.0;
+    if (i < len - sh) t = row[i + sh];
+    __syncwarp();
+    if (i < len - sh) row[i] = t;
+    __syncwarp();
+  }
+  for (int i = len + lane; i < ld; i += 32) row[i] = 0.0;  // entries beyond the current horizon start cold
+}
+
 __global__ void k_fill(double *p, double v, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t st = (size_t)gridDim.x * blockDim.x;
@@ -305,6 +324,13 @@ cudaError_t launch_check_bounds(const double *l, const double *u, int ld, int m,
   cudaError_t e = cudaMemsetAsync(bad, 0, sizeof(int), st);
   if (e != cudaSuccess) return e;
   k_check_bounds<<<148 * 8, 256, 0, st>>>(l, u, ld, m, batch, bad);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_shift_rows(double *v, int ld, int len, int sh, int batch, cudaStream_t st) {
+  if (len <= sh || sh <= 0) return cudaSuccess;
+  const int threads = 128, wpb = threads / 32;
+  k_shift_rows<<<(batch + wpb - 1) / wpb, threads, 0, st>>>(v, ld, len, sh, batch);
   return cudaGetLastError();
 }
 

@@ -109,7 +109,7 @@ osqp_setup_recursive osqp_solve_recursive osqp_update_recursive osqp_setup_combi
 osqp_solve_combine_recursive osqp_update_Z_horizon osqp_update_X_horizon
 osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions cleanup_rldl
 rldl_batch_setup rldl_batch_solve rldl_batch_update_bounds rldl_batch_partial_update_bounds
-rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_update_horizon rldl_batch_update_rho
+rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
 rldl_batch_refactor rldl_batch_kkt_solve rldl_batch_get_solution rldl_batch_get_info
 rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel
 rldl_batch_free
@@ -166,6 +166,7 @@ def lib():
         "rldl_batch_partial_update_bounds": [vp, c_int, c_int, vp, vp],
         "rldl_batch_update_lin_cost": [vp, vp],
         "rldl_batch_warm_start": [vp, vp, vp],
+        "rldl_batch_warm_start_shift": [vp],
         "rldl_batch_update_horizon": [vp, c_int],
         "rldl_batch_update_rho": [vp, vp],
         "rldl_batch_refactor": [vp],
@@ -284,6 +285,9 @@ class Batch:
         x = None if x is None else np.ascontiguousarray(x)
         y = None if y is None else np.ascontiguousarray(y)
         return lib().rldl_batch_warm_start(self.h, _p(x), _p(y))
+
+    def warm_start_shift(self):
+        return lib().rldl_batch_warm_start_shift(self.h)
 
     def update_horizon(self, N):
         return lib().rldl_batch_update_horizon(self.h, N)
