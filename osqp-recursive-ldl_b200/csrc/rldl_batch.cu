@@ -264,7 +264,7 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
     D.RS = D.qa + D.PX + D.PS + 3 * D.bb;
     D.rec_stride = (long long)(B->Nmax + 1) * D.RS;
     CK(dalloc(&D.rec, B->streaming ? bs * (size_t)D.rec_stride : 1));
-    CK(dalloc(&D.sched, 2 + 2 * kSchedBuckets));
+    CK(dalloc(&D.sched, kSchedCounters));
     CK(dalloc(&D.sched_slots, B->streaming ? (size_t)kSchedBuckets * bs : 1));
   }
   CK(cudaStreamCreateWithFlags(&B->stream, cudaStreamNonBlocking));
@@ -304,7 +304,7 @@ void Batch::set_sizes() {
 Batch::~Batch() {
   cudaSetDevice(device);
   double *dp[] = {D.q, D.l, D.u, D.rho_vec, D.x, D.z, D.y, D.dx, D.dy, D.Xinv, D.Sinv, D.yk, D.sk,
-                  D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec, d_l_alt, d_u_alt};
+                  D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec, d_l_alt, d_u_alt, d_latT};
   for (double *p : dp) if (p) cudaFree(p);
   if (D.iter) cudaFree(D.iter);
   int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx, D.sched, D.sched_slots};
@@ -392,17 +392,39 @@ c_int Batch::solve() {
     if (streaming && settings.adaptive_rho) records_stale = true;
   }
   if (use_stream()) {
+    // Two kernels share one solve.  The streaming kernel carries the bulk (HBM-bound, thousands of instances
+    // in flight); once at most `lat_below` instances are unfinished it suspends them as they stand and the
+    // latency-mode kernel (one instance per CTA, factor resident in shared memory, ~10x shorter iteration)
+    // finishes them.  Small batches go to the latency-mode kernel directly.
     // Adaptive rho: an instance whose rho changes parks itself (osqp_update_rho, osqp.c:1268-1319, needs a
     // full stage recursion); parked instances are re-typed, re-factorised and re-packed together, then resumed.
-    int resume = 0;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    int lat_below = 1024;
+    if (const char *e = getenv("RLDL_LAT_BELOW")) lat_below = atoi(e);
+    const size_t lat_smem = latency_smem_bytes(M, N);
+    const bool lat_ok = lat_below > 0 && lat_smem != (size_t)-1 && lat_smem <= 227 * 1024;
+    if (lat_ok && !d_latT) CK(cudaMalloc(&d_latT, (size_t)sms * 2 * Nmax * nx * (nx + 2) * sizeof(double)));
+    int unfinished = batch, resume = 0;
+    CK(cudaMemcpyAsync(D.sched + kSchedUnfinished, &unfinished, sizeof(int), cudaMemcpyHostToDevice, stream));
     for (;;) {
-      CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, stream));
-      launches++;
+      const bool run_stream = !lat_ok || unfinished > lat_below;
+      if (run_stream) {
+        CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, lat_ok ? lat_below : 0, stream));
+        launches++;
+      }
+      if (lat_ok) {
+        CK(launch_admm_latency(M, D, S, (int)settings.warm_start, (resume || run_stream) ? 1 : 0, d_latT,
+                               std::min(sms, batch), run_stream ? 0 : 1, stream));
+        launches++;
+      }
       if (!settings.adaptive_rho) break;
-      int parked = 0;
-      CK(cudaMemcpyAsync(&parked, D.sched + 1, sizeof(int), cudaMemcpyDeviceToHost, stream));
+      int cnt[2] = {0, 0};
+      CK(cudaMemcpyAsync(&cnt[0], D.sched + 1, sizeof(int), cudaMemcpyDeviceToHost, stream));
+      CK(cudaMemcpyAsync(&cnt[1], D.sched + kSchedUnfinished, sizeof(int), cudaMemcpyDeviceToHost, stream));
       CK(cudaStreamSynchronize(stream));
-      if (!parked) break;
+      if (!cnt[0]) break;
+      unfinished = cnt[1];
       CK(launch_set_rho_vec(D, D.m, d_changed, stream));
       launches++;
       c_int rc = factor_launch(0, true);

@@ -27,6 +27,7 @@ struct Batch {
   int *d_midx = nullptr;
   int *d_changed = nullptr;
   double *d_stage = nullptr;
+  double *d_latT = nullptr;  // per-CTA T_k blocks of the latency-mode kernel
   double *d_l_alt = nullptr, *d_u_alt = nullptr;  // landing buffers of validated bound updates
   size_t stage_cap = 0;
   double *h_pin = nullptr;

@@ -82,7 +82,14 @@ struct BatchDev {
 };
 
 constexpr int kSchedBuckets = 32;  // priority buckets: floor(2*log2(residual / tolerance)), clamped
+// sched[kSchedUnfinished]: instances of the current solve not yet finished (kept across the launches of
+// one solve: streaming launch, latency-mode launch, adaptive-rho resume rounds); kSchedCounters = array size
+constexpr int kSchedUnfinished = 2 + 2 * kSchedBuckets;
+constexpr int kSchedCounters = kSchedUnfinished + 2;
 
 constexpr int STATUS_FACTOR_ERROR = -7;  // reported as OSQP_NON_CVX
+// device-internal: instance parked by an adaptive-rho update until its factor has been refreshed (never
+// visible after a solve: k_set_rho_vec turns it back into OSQP_UNSOLVED before the resume launch)
+constexpr int kStatusParkedRho = -11;
 
 }  // namespace rldl

@@ -40,6 +40,7 @@ __global__ void k_set_rho_vec(BatchDev B, int m, int *changed) {
   if (lane == 0) {
     B.rho[warp] = rho;
     if (changed) changed[warp] = ch;
+    if (B.status[warp] == kStatusParkedRho) B.status[warp] = -10;  // parked for this refresh: resumable again
   }
 }
 

@@ -26,7 +26,11 @@ void stream_record_dims(int a, int nx, int b, int *qa, int *PX, int *PS, int *bb
 cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,
                                 cudaStream_t st);
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                               int resume, cudaStream_t st);
+                               int resume, int park_below, cudaStream_t st);
+// latency-mode kernel (rldl_latency.cu): one instance per CTA, factor resident in shared memory
+size_t latency_smem_bytes(const ModelDev &M, int N);  // (size_t)-1 if the shape is not in the table
+cudaError_t launch_admm_latency(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
+                                int resume, double *Tg, int ctas, int reset_parked, cudaStream_t st);
 cudaError_t launch_factor_stream(const ModelDev &M, const BatchDev &B, double sigma, int k0,
                                  const int *only_flagged, int write_unpacked, cudaStream_t st);
 }  // namespace rldl

@@ -1,0 +1,714 @@
+// rldl_latency.cu — latency-mode ADMM kernel (sm_100a): one QP instance per CTA.
+//
+// The streaming kernel (rldl_stream.cu) is built for throughput: thousands of instances in
+// flight, one per lane group, each walking its 2(N+1) stage steps strictly in sequence
+// (~1 us per step).  When few instances are left — the tail of a large batch, a small shard on
+// one of 8 GPUs, or a batch of one behind the scalar osqp_solve — that chain is all that
+// matters.  This kernel shortens it by an order of magnitude:
+//
+//  * the whole factor of the instance (its N+1 stage records) is loaded into shared memory
+//    ONCE by bulk async copies (TMA) and reused for every iteration: no HBM traffic per
+//    iteration except the iterates;
+//  * the block substitution (reference lin_sys/direct/qdldl/qdldl_interface.c:559-585 over the
+//    factor of src/recursive_ldl.c:1139-1318) is re-associated so that everything that does not
+//    depend on the neighbouring stage runs for all stages in parallel (one lane group per
+//    stage), and only an nx x nx mat-vec per stage stays on the critical path:
+//        forward :  sp_k = c_k + T_k sp_{k-1},      c_k = Sinv_k (r^d_k - F_k Xinv_k r^v_k)
+//        backward:  vn_k = d_k + T_k' vn_{k+1},     T_k = Sinv_k F_k Xinv_k[:, 0:nx]
+//    (T_k is formed once per instance from the resident factor; the same matrix serves both
+//    sweeps by symmetry).  Phases per iteration:
+//        A  (parallel)  rhs build, a_k = Xinv_k r^v_k, c_k
+//        B  (scan)      sp_k                                   — one group, shuffles only
+//        C  (parallel)  e_k = a_k + Xinv_k (F_k' sp_k - J' sp_{k-1}),  d_k = e_k[0:nx]
+//        D  (scan)      vn_k
+//        E  (parallel)  nu^d_k, v_k = e_k + Xinv_k F_k' Sinv_k vn_{k+1}, ADMM step
+//    (reference src/auxil.c:164-228, src/proj.c:4-14);
+//  * residuals / termination / rho adaptation (src/auxil.c:243-789) by one group every
+//    check_termination iterations, with the same device functions as the other kernels.
+//
+// Instances are claimed from the same device counter and with the same resume semantics as
+// the streaming kernel, so the host can hand the tail of a streaming launch to this kernel.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include "rldl_device_fn.cuh"
+#include "rldl_kernels.h"
+#include "rldl_stream_common.cuh"
+
+namespace rldl {
+
+constexpr int kLatThreads = 512;
+
+template <class SH>
+struct LatLayout {  // shared-memory layout (doubles) of k_admm_cta for horizon N
+  static constexpr int NG = (kLatThreads / 32) * SH::GPW;
+  // T_k ring of the scan phases: NS slots of CH stage blocks; a block is nx rows of TS = nx+2 doubles
+  // (row stride chosen so that the per-lane LDS.128 of a row are bank-conflict free)
+  static constexpr int CH = 5, NS = 3, TS = SH::NX + 2, TBLK = SH::NX * TS;
+  int recs, va, vc, vd, scr, bar, ctl, tring, tbar, qs, red, end;
+  __host__ __device__ explicit LatLayout(int N) {
+    recs = SH::M_END;
+    va = recs + (N + 1) * SH::RS;
+    vc = va + (N + 1) * SH::AE;
+    vd = vc + (N + 1) * SH::NXE;
+    scr = vd + (N + 1) * SH::NXE;
+    bar = scr + NG * SH::SC;
+    ctl = bar + 2;
+    tring = ctl + 4;
+    tbar = tring + NS * CH * TBLK;
+    qs = tbar + NS + (NS & 1);
+    red = qs + 3 * SH::A * SH::A;  // dense cost blocks padded to A x A (residuals)
+    end = red + NG * 10 + (kLatThreads / 32) * 4;  // per-group partial residuals + per-warp certificate partials
+  }
+};
+
+template <class SH>
+__global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDev B, SettingsDev S, int warm_start,
+                                                              int resume, double *Tg) {
+  constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, NT = SH::NT, CW = SH::CW, G = SH::G, NYT = SH::NYT,
+                ROWS = SH::ROWS, RS = SH::RS, BQ = SH::B, AE = SH::AE, NXE = SH::NXE, NG = LatLayout<SH>::NG;
+  extern __shared__ __align__(16) double smem[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int gl = lane & (G - 1), gw = lane / G;
+  const unsigned gm = (G == 32) ? FULL : (((1u << G) - 1u) << (gw * G));
+  const int grp = wid * SH::GPW + gw;
+  const int N = B.N, n = B.n, m = B.m;
+  const LatLayout<SH> L(N);
+
+  // ---- CTA-shared model block (same layout as the streaming kernel) ----
+  double *Fd = smem + SH::M_FD, *FdT = smem + SH::M_FDT, *Cv = smem + SH::M_CV, *Ctv = smem + SH::M_CTV;
+  int *Ci = reinterpret_cast<int *>(smem + SH::M_CI), *Cti = reinterpret_cast<int *>(smem + SH::M_CTI);
+  for (int e = threadIdx.x; e < SH::M_END; e += blockDim.x) smem[e] = 0.0;
+  __syncthreads();
+  for (int t = threadIdx.x; t < 2 * NX; t += blockDim.x) {
+    const int c = t / NX, r = t - c * NX;
+    const Ell &E = M.sc[c].F;
+    for (int e = 0; e < E.width; e++) {
+      const double v = M.val[E.off + r * E.width + e];
+      const int j = M.idx[E.off + r * E.width + e];
+      if (v != 0.0) {
+        Fd[c * A * NX + j * NX + r] = v;
+        FdT[c * A * NX + r * A + j] = v;
+      }
+    }
+  }
+  for (int t = threadIdx.x; t < 3 * ROWS; t += blockDim.x) {
+    const int c = t / ROWS, r = t - c * ROWS;
+    const Ell &E = M.sc[c].C;
+    if (r < E.rows)
+      for (int e = 0; e < E.width && e < CW; e++) {
+        Cv[t * CW + e] = M.val[E.off + r * E.width + e];
+        Ci[t * CW + e] = M.idx[E.off + r * E.width + e];
+      }
+  }
+  for (int t = threadIdx.x; t < 3 * AE; t += blockDim.x) {
+    const int c = t / AE, r = t - c * AE;
+    const Ell &E = M.sc[c].Ct;
+    if (r < E.rows)
+      for (int e = 0; e < E.width && e < CW; e++) {
+        Ctv[t * CW + e] = M.val[E.off + r * E.width + e];
+        Cti[t * CW + e] = M.idx[E.off + r * E.width + e];
+      }
+  }
+  double *Qs = smem + L.qs, *red = smem + L.red;
+  for (int t = threadIdx.x; t < 3 * A * A; t += blockDim.x) {
+    const int c = t / (A * A), e = t - c * A * A, j = e / A, i = e - j * A;
+    const int dimq = (c == 2) ? NX : A;
+    Qs[t] = (i < dimq && j < dimq) ? M.val[M.sc[c].Q + j * dimq + i] : 0.0;
+  }
+  double *recs = smem + L.recs, *va = smem + L.va, *vc = smem + L.vc, *vd = smem + L.vd;
+  double *sc = smem + L.scr + (size_t)grp * SH::SC;
+  uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L.bar);
+  volatile int *ctl = reinterpret_cast<volatile int *>(smem + L.ctl);
+  double *w = sc + SH::O_W, *tv2 = sc + SH::O_TV2, *yvs = sc + SH::O_YV, *td2 = sc + SH::O_TD2;
+  double *vn2 = sc + SH::O_VN2, *vcur = sc + SH::O_VC, *nudv = sc + SH::O_NUD, *gg2 = sc + SH::O_GG2;
+  Scratch rs;  // residual routines (group 0 only) alias that group's scratch
+  rs.v = sc; rs.w = sc + SH::VM; rs.vn = sc + 2 * SH::VM; rs.td = sc + 3 * SH::VM; rs.sp = sc + 4 * SH::VM;
+  rs.g = rs.yv = rs.nud = nullptr;
+  constexpr int CH = LatLayout<SH>::CH, NS = LatLayout<SH>::NS, TS = LatLayout<SH>::TS, TBLK = LatLayout<SH>::TBLK;
+  static_assert(NX % 2 == 0, "latency-mode kernel: nx must be even (16-byte rows of T)");
+  double *tring = smem + L.tring;
+  uint64_t *tbars = reinterpret_cast<uint64_t *>(smem + L.tbar);
+  if (threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    for (int d = 0; d < NS; d++) mbar_init(&tbars[d], 1);
+  }
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncthreads();
+  const uint32_t bar_s = smem_u32(bar), recs_s = smem_u32(recs), tring_s = smem_u32(tring), tbars_s = smem_u32(tbars);
+  long long twait_ = 0;
+  uint32_t phase = 0, tphase = 0;  // tphase: one parity bit per ring slot (group 0 only)
+  auto lds128 = [](uint32_t a) -> double2 {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+    return v;
+  };
+  auto lds64 = [](uint32_t a) -> double {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+  };
+  auto sts64 = [](uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory"); };
+  auto t_wait = [&](int s) {
+    mbar_wait(tbars_s + 8u * s, (tphase >> s) & 1u);
+    tphase ^= 1u << s;
+  };
+
+  int wrapX[SH::WNX], wrapS[SH::WNS];
+#pragma unroll
+  for (int d = 1; d <= A - 1 - A / 2; d++) wrapX[d - 1] = d * A + ((gl < A ? gl : 0) - d + A) % A;
+#pragma unroll
+  for (int d = 1; d <= NX - 1 - NX / 2; d++) wrapS[d - 1] = d * NX + ((gl < NX ? gl : 0) - d + NX) % NX;
+
+  const double sigma = S.sigma, alpha = S.alpha, oma = 1.0 - S.alpha;
+  // T_k for phase B (TB[k][i*TS + j] = T_k(i,j)) and phase D (TD[k][i*TS + j] = T_k(j,i)) in global memory
+  // (2*Nmax*TBLK doubles per CTA, L2-resident), written once per instance by this CTA and streamed back
+  // through the shared-memory ring by bulk async copies, CH stages per copy
+  double *TB = Tg + (size_t)blockIdx.x * 2 * B.Nmax * TBLK, *TD = TB + (size_t)B.Nmax * TBLK;
+  // One scan (group 0): vec[k] += T_k vec[k-1], k = 1..N-1 (fwd, vec = vc: sp_k) or
+  // vec[k] += T_k' vec[k+1], k = N-1..1 (bwd, vec = vd: vn_k).  The previous result is re-read from shared
+  // memory by broadcast LDS.128; one __syncwarp per stage.
+  auto scan = [&](const bool fwd) {
+    const double *Tsrc = fwd ? TB : TD;
+    double *vec = fwd ? vc : vd;
+    const int nblk = N - 1, nchunk = (nblk + CH - 1) / CH;
+    auto issue_chunk = [&](int c) {  // leader: chunk c of the scan order -> ring slot c % NS
+      const int t0 = c * CH, cnt = min(CH, nblk - t0);
+      const int k_lo = fwd ? 1 + t0 : (N - 1 - t0) - (cnt - 1);
+      const int s = c % NS;
+      mbar_expect_tx(tbars_s + 8u * s, (uint32_t)(cnt * TBLK * 8));
+      bulk_g2s(tring_s + 8u * (uint32_t)(s * CH * TBLK), Tsrc + (size_t)k_lo * TBLK, (uint32_t)(cnt * TBLK * 8),
+               tbars_s + 8u * s);
+    };
+    if (gl == 0)
+      for (int c = 0; c < NS && c < nchunk; c++) issue_chunk(c);
+    // 32-bit shared addresses, advanced incrementally: nothing but the mat-vec itself is on the chain
+    const int row = (gl < NX) ? gl : 0;
+    const uint32_t vec_s = smem_u32(vec);
+    uint32_t pk = vec_s + 8u * (uint32_t)((fwd ? 1 : N - 1) * NXE);  // &vec[k][0]
+    const int dstep = fwd ? NXE * 8 : -NXE * 8, tstep = fwd ? TBLK * 8 : -TBLK * 8;
+    int s = 0;
+    for (int c = 0; c < nchunk; c++) {
+#ifdef RLDL_LAT_PROFILE
+      const long long w0_ = clock64();
+#endif
+      t_wait(s);
+#ifdef RLDL_LAT_PROFILE
+      twait_ += clock64() - w0_;
+#endif
+      const int cnt = min(CH, nblk - c * CH);
+      uint32_t ta = tring_s + 8u * (uint32_t)((s * CH + (fwd ? 0 : cnt - 1)) * TBLK + row * TS);
+      for (int r = 0; r < cnt; r++) {
+        double2 tv[NX / 2], vv[NX / 2];
+#pragma unroll
+        for (int j = 0; j < NX / 2; j++) tv[j] = lds128(ta + 16u * j);
+        double cur = 0.0;
+        if (gl < NX) cur = lds64(pk + 8u * gl);
+#pragma unroll
+        for (int j = 0; j < NX / 2; j++) vv[j] = lds128(pk - dstep + 16u * j);
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+        for (int j = 0; j < NX / 2; j++) {
+          acc[(2 * j) & 3] = fma(tv[j].x, vv[j].x, acc[(2 * j) & 3]);
+          acc[(2 * j + 1) & 3] = fma(tv[j].y, vv[j].y, acc[(2 * j + 1) & 3]);
+        }
+        if (gl < NX) sts64(pk + 8u * gl, cur + ((acc[0] + acc[1]) + (acc[2] + acc[3])));
+        __syncwarp(gm);
+        ta += tstep;
+        pk += dstep;
+      }
+      if (gl == 0 && c + NS < nchunk) issue_chunk(c + NS);
+      s = (s + 1 == NS) ? 0 : s + 1;
+    }
+  };
+
+  for (;;) {
+    // ---------------- claim an instance (same counter / resume rules as the streaming kernel) ----------------
+    if (threadIdx.x == 0) {
+      int i = -1;
+      for (;;) {
+        i = atomicAdd(B.sched, 1);
+        if (i >= B.batch) { i = -1; break; }
+        if (B.fact_flag[i]) {  // failed factorisation: report non-convex, like a diverged solve
+          if (!resume || B.status[i] == -10) {
+            B.status[i] = -7; B.iter[i] = 0; B.obj[i] = kOsqpNan;
+            atomicSub(B.sched + kSchedUnfinished, 1);
+          }
+          continue;
+        }
+        if (resume && __ldcg(B.status + i) != -10) continue;
+        break;
+      }
+      ctl[0] = i;
+    }
+    __syncthreads();
+    const int inst = ctl[0];
+    if (inst < 0) break;
+    const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
+    double *x = B.x + vo, *z = B.z + ro, *y = B.y + ro, *dx = B.dx + vo, *dy = B.dy + ro;
+    const double *recb = B.rec + (size_t)inst * B.rec_stride;
+    const double rho_in = __ldcg(B.rho + inst), rho_eq = kRhoEq * rho_in;
+    const double inv_in = 1.0 / rho_in, inv_eq = 1.0 / rho_eq, inv_min = 1.0 / kRhoMin;
+    auto rinv_of = [&](double rv) -> double {
+      return rv == rho_in ? inv_in : (rv == rho_eq ? inv_eq : (rv == kRhoMin ? inv_min : 1.0 / rv));
+    };
+    // ---------------- the whole factor of the instance -> shared memory (TMA bulk copies) ----------------
+    if (threadIdx.x == 0) mbar_expect_tx(bar_s, (uint32_t)((N + 1) * RS * 8));
+    __syncthreads();
+    for (int k = threadIdx.x; k <= N; k += blockDim.x)
+      bulk_g2s(recs_s + 8u * (uint32_t)(k * RS), recb + (size_t)k * RS, RS * 8, bar_s);
+    int iter;
+    const bool fresh = !resume || false;
+    if (fresh) {
+      if (!warm_start) {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) x[i] = 0.0;
+        for (int r = threadIdx.x; r < m; r += blockDim.x) { z[r] = 0.0; y[r] = 0.0; }
+      }
+      if (threadIdx.x == 0) B.status[inst] = -10;
+      iter = 0;
+    } else {
+      iter = (int)__ldcg(B.iter + inst);
+    }
+    mbar_wait(bar_s, phase);
+    phase ^= 1u;
+    __syncthreads();
+    // ---------------- T_k = Sinv_k F_k Xinv_k[:, 0:nx], one group per stage ----------------
+    for (int k = grp; k < N; k += NG) {
+      const double *sl_ = recs + k * RS;
+      const double *Fk = Fd + (k == 0 ? 0 : A * NX);
+      for (int j = 0; j < NX; j++) {
+        if (gl < A) {  // column j of Xinv_k from the diagonal-packed block
+          int d = j - gl;
+          if (d < 0) d += A;
+          yvs[gl] = (d <= A / 2) ? sl_[SH::XOFF + d * A + gl] : sl_[SH::XOFF + (A - d) * A + j];
+        }
+        __syncwarp(gm);
+        if (gl < NX) {
+          const double wv = dense_mv<A, NX>(Fk + gl, yvs);
+          td2[gl] = wv; td2[gl + NX] = wv;
+        }
+        __syncwarp(gm);
+        if (gl < NX) {
+          const double t = dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, td2 + gl, wrapS);
+          TB[(size_t)k * TBLK + gl * TS + j] = t;
+          TD[(size_t)k * TBLK + j * TS + gl] = t;
+        }
+        __syncwarp(gm);
+      }
+    }
+    __threadfence();  // T blocks are read back by bulk async copies (async proxy)
+    asm volatile("fence.proxy.async;" ::: "memory");
+    __syncthreads();
+    // ---------------- ADMM iterations (osqp.c:354-519) ----------------
+#ifdef RLDL_LAT_PROFILE
+    long long pt[7] = {0, 0, 0, 0, 0, 0, 0}, pc = 0;
+#define PT(i) do { const long long now_ = clock64(); pt[i] += now_ - pc; pc = now_; } while (0)
+#else
+#define PT(i)
+#endif
+    for (;;) {
+      iter++;
+#ifdef RLDL_LAT_PROFILE
+      pc = clock64();
+#endif
+      const bool can_check = S.check_termination && (iter % S.check_termination == 0);
+      const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval && (iter % S.adaptive_rho_interval == 0);
+      const bool last = iter == S.max_iter;
+      const bool store_delta = can_check || last;
+      // ===== phase A: rhs, a_k = Xinv_k r^v_k, c_k = Sinv_k (r^d_k - F_k a_k) =====
+      for (int k = grp; k <= N; k += NG) {
+        const bool term = (k == N);
+        const int cls = term ? 2 : (k == 0 ? 0 : 1);
+        const int dim = term ? NX : A, np = term ? NT : NY;
+        const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
+        const double *sl_ = recs + k * RS;
+        const double xv = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
+        double zp[NYT], yp[NYT], zd = 0.0, yd = 0.0;
+#pragma unroll
+        for (int t = 0; t < NYT; t++) {
+          const int rr = gl + G * t;
+          zp[t] = yp[t] = 0.0;
+          if (rr < np) { zp[t] = __ldcg(z + roff + rr); yp[t] = __ldcg(y + roff + rr); }
+        }
+        if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
+        double g = 0.0;
+        if (gl >= ilo && gl < dim) g = sigma * xv - sl_[gl];
+#pragma unroll
+        for (int t = 0; t < NYT; t++) {
+          const int rr = gl + G * t;
+          if (rr < np) w[rr] = sl_[SH::RHO + rr] * zp[t] - yp[t];
+        }
+        __syncwarp(gm);
+        double tt = 0.0;
+        if (gl < dim) tt = g + ell_row<CW>(Ctv + cls * AE * CW, Cti + cls * AE * CW, gl, w);
+        if (gl < A) { tv2[gl] = tt; tv2[gl + A] = tt; }
+        __syncwarp(gm);
+        if (gl < A) {
+          const double av = dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, tv2 + gl, wrapX);
+          va[k * AE + gl] = av;
+          yvs[gl] = av;
+        }
+        __syncwarp(gm);
+        if (!term) {
+          if (gl < NX) {
+            const double ri = rinv_of(sl_[SH::RHO + NY + gl]);
+            const double tdv = (zd - yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
+            td2[gl] = tdv; td2[gl + NX] = tdv;
+          }
+          __syncwarp(gm);
+          if (gl < NX) vc[k * NXE + gl] = dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, td2 + gl, wrapS);
+        }
+        __syncwarp(gm);
+      }
+      __syncthreads();
+      PT(0);
+      // ===== phase B: sp_k = c_k + T_k sp_{k-1}, in place in vc =====
+      if (grp == 0) scan(true);
+      __syncthreads();
+      PT(1);
+      // ===== phase C: e_k = a_k + Xinv_k (F_k' sp_k - J' sp_{k-1}),  d_k = e_k[0:nx] =====
+      for (int k = grp; k <= N; k += NG) {
+        const bool term = (k == N);
+        const double *sl_ = recs + k * RS;
+        if (gl < A) {
+          double gg = 0.0;
+          if (!term) gg = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, vc + k * NXE);
+          if (k > 0 && gl < NX) gg -= vc[(k - 1) * NXE + gl];
+          gg2[gl] = gg; gg2[gl + A] = gg;
+        }
+        __syncwarp(gm);
+        if (gl < A) {
+          const double e = va[k * AE + gl] + dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
+          va[k * AE + gl] = e;
+          if (gl < NX) vd[k * NXE + gl] = e;
+        }
+        __syncwarp(gm);
+      }
+      __syncthreads();
+      PT(2);
+      // ===== phase D: vn_k = d_k + T_k' vn_{k+1}, k = N-1 .. 1, in place in vd (vn_N = d_N; stage 0 has no state) =====
+      if (grp == 0) scan(false);
+      __syncthreads();
+      PT(3);
+      // ===== phase E: v_k = e_k + Xinv_k F_k' (Sinv_k vn_{k+1}), nu^d_k, ADMM step (auxil.c:188-228) =====
+      for (int k = grp; k <= N; k += NG) {
+        const bool term = (k == N);
+        const int cls = term ? 2 : (k == 0 ? 0 : 1);
+        const int dim = term ? NX : A, np = term ? NT : NY;
+        const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
+        const double *sl_ = recs + k * RS;
+        const double xo = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
+        double zp[NYT], yp[NYT], zd = 0.0, yd = 0.0;
+#pragma unroll
+        for (int t = 0; t < NYT; t++) {
+          const int rr = gl + G * t;
+          zp[t] = yp[t] = 0.0;
+          if (rr < np) { zp[t] = __ldcg(z + roff + rr); yp[t] = __ldcg(y + roff + rr); }
+        }
+        if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
+        double vv = 0.0, nud = 0.0;
+        if (term) {
+          if (gl < A) vv = va[k * AE + gl];
+        } else {
+          if (gl < NX) {
+            const double v1 = vd[(k + 1) * NXE + gl];
+            vn2[gl] = v1; vn2[gl + NX] = v1;
+          }
+          __syncwarp(gm);
+          if (gl < NX) {
+            const double s = dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, vn2 + gl, wrapS);
+            nud = -(vc[k * NXE + gl] + s);
+            nudv[gl] = s;
+          }
+          __syncwarp(gm);
+          if (gl < A) {
+            const double ggv = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, nudv);
+            gg2[gl] = ggv; gg2[gl + A] = ggv;
+          }
+          __syncwarp(gm);
+          if (gl < A) vv = va[k * AE + gl] + dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
+        }
+        if (gl < A) vcur[gl] = vv;
+        __syncwarp(gm);
+#pragma unroll
+        for (int t = 0; t < NYT; t++) {
+          const int rr = gl + G * t;
+          if (rr < np) {
+            const int ri = roff + rr;
+            const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
+            const double rho = sl_[SH::RHO + rr], rinv = rinv_of(rho), zo = zp[t], yo = yp[t];
+            const double zh = alpha * zt + oma * zo;
+            const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
+            const double d = rho * (zh - zn);
+            z[ri] = zn; y[ri] = yo + d;
+            if (store_delta) dy[ri] = d;
+          }
+        }
+        if (!term && gl < NX) {
+          const int ri = roff + NY + gl;
+          const double rho = sl_[SH::RHO + NY + gl], rinv = rinv_of(rho);
+          const double zt = (zd - yd * rinv) + nud * rinv;
+          const double zh = alpha * zt + oma * zd;
+          const double zn = fmin(fmax(zh + yd * rinv, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
+          const double d = rho * (zh - zn);
+          z[ri] = zn; y[ri] = yd + d;
+          if (store_delta) dy[ri] = d;
+        }
+        if (gl >= ilo && gl < dim) {
+          const double xn = alpha * vv + oma * xo;
+          x[xoff + gl] = xn;
+          if (store_delta) dx[xoff + gl] = xn - xo;
+        }
+        __syncwarp(gm);
+      }
+      if (!(can_check || can_adapt || last)) {
+        __syncthreads();  // iterates of this iteration visible to every group of the CTA
+        PT(4);
+        continue;
+      }
+      __syncthreads();
+      PT(4);
+      // ---------------- residuals (update_info, auxil.c:567-632), one group per stage ----------------
+      {
+        double pri = 0, nz = 0, nAx = 0, dua = 0, nq = 0, nAty = 0, nPx = 0, oq = 0, oP = 0;
+        double *rv_ = sc, *rw_ = sc + AE, *rtd = rw_ + ROWS, *rvn = rtd + NXE, *rsp = rvn + NXE;
+        for (int k = grp; k <= N; k += NG) {
+          const bool term = (k == N);
+          const int cls = term ? 2 : (k == 0 ? 0 : 1);
+          const int dim = term ? NX : A, np = term ? NT : NY;
+          const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
+          const double *sl_ = recs + k * RS;
+          const double xv = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
+          if (gl < A) rv_[gl] = xv;
+#pragma unroll
+          for (int t = 0; t < NYT; t++) {
+            const int rr = gl + G * t;
+            if (rr < np) rw_[rr] = __ldcg(y + roff + rr);
+          }
+          if (gl < NX) {
+            rtd[gl] = term ? 0.0 : __ldcg(y + roff + NY + gl);
+            rvn[gl] = term ? 0.0 : __ldcg(x + xoff + A + gl);
+            rsp[gl] = (k > 0) ? __ldcg(y + roff - NX + gl) : 0.0;  // dynamics rows of stage k-1
+          }
+          __syncwarp(gm);
+#pragma unroll
+          for (int t = 0; t < NYT; t++) {
+            const int rr = gl + G * t;
+            if (rr < np) {
+              const double ax = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, rv_), zz = __ldcg(z + roff + rr);
+              pri = fmax(pri, fabs(ax - zz)); nz = fmax(nz, fabs(zz)); nAx = fmax(nAx, fabs(ax));
+            }
+          }
+          if (!term && gl < NX) {
+            const double ax = dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, rv_) - rvn[gl], zz = __ldcg(z + roff + NY + gl);
+            pri = fmax(pri, fabs(ax - zz)); nz = fmax(nz, fabs(zz)); nAx = fmax(nAx, fabs(ax));
+          }
+          if (gl >= ilo && gl < dim) {
+            const double px = dense_mv<A, A>(Qs + cls * A * A + gl, rv_);
+            double aty = ell_row<CW>(Ctv + cls * AE * CW, Cti + cls * AE * CW, gl, rw_);
+            if (!term) aty += dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, rtd);
+            if (k > 0 && gl < NX) aty -= rsp[gl];
+            const double qv = sl_[gl];
+            dua = fmax(dua, fabs((qv + px) + aty)); nq = fmax(nq, fabs(qv));
+            nAty = fmax(nAty, fabs(aty)); nPx = fmax(nPx, fabs(px));
+            oq = fma(qv, xv, oq); oP = fma(xv, px, oP);
+          }
+          __syncwarp(gm);
+        }
+        pri = grp_max<G>(pri, gm); nz = grp_max<G>(nz, gm); nAx = grp_max<G>(nAx, gm); dua = grp_max<G>(dua, gm);
+        nq = grp_max<G>(nq, gm); nAty = grp_max<G>(nAty, gm); nPx = grp_max<G>(nPx, gm);
+        oq = grp_sum<G>(oq, gm); oP = grp_sum<G>(oP, gm);
+        if (gl == 0) {
+          double *o = red + grp * 10;
+          o[0] = pri; o[1] = nz; o[2] = nAx; o[3] = dua; o[4] = nq; o[5] = nAty; o[6] = nPx; o[7] = oq; o[8] = oP;
+        }
+      }
+      // cheap parts of the infeasibility certificates (auxil.c:364-515) over the flat vectors, whole CTA:
+      // projected delta_y with its norm and support-function value; norm of delta_x and q'delta_x
+      if (store_delta) {
+        const double *lg = B.l + ro, *ug = B.u + ro, *qg = B.q + vo;
+        double ny_ = 0.0, lhs_ = 0.0, nx_ = 0.0, qdx_ = 0.0;
+        for (int r = threadIdx.x; r < m; r += blockDim.x) {
+          double d = __ldcg(dy + r);
+          const double lv = __ldcg(lg + r), uv = __ldcg(ug + r);
+          if (uv > kInfBound) d = (lv < -kInfBound) ? 0.0 : fmin(d, 0.0);
+          else if (lv < -kInfBound) d = fmax(d, 0.0);
+          dy[r] = d;
+          ny_ = fmax(ny_, fabs(d));
+          lhs_ += uv * fmax(d, 0.0) + lv * fmin(d, 0.0);
+        }
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+          const double d = __ldcg(dx + i);
+          nx_ = fmax(nx_, fabs(d));
+          qdx_ = fma(__ldcg(qg + i), d, qdx_);
+        }
+        ny_ = grp_max<32>(ny_, FULL); nx_ = grp_max<32>(nx_, FULL);
+        lhs_ = grp_sum<32>(lhs_, FULL); qdx_ = grp_sum<32>(qdx_, FULL);
+        if (lane == 0) {
+          double *o = red + NG * 10 + wid * 4;
+          o[0] = ny_; o[1] = lhs_; o[2] = nx_; o[3] = qdx_;
+        }
+      }
+      __syncthreads();
+      // ---------------- epilogue by group 0: termination, rho adaptation ----------------
+      if (grp == 0) {
+        bool done = false, rho_changed = false;
+        int status = -10;
+        double obj = 0.0, rho_new = rho_in;
+        Resid R = {0, 0, 0, 0, 0, 0, 0, 0};
+        {
+          double a[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+          for (int g2 = gl; g2 < NG; g2 += G) {
+#pragma unroll
+            for (int e = 0; e < 7; e++) a[e] = fmax(a[e], red[g2 * 10 + e]);
+            a[7] += red[g2 * 10 + 7]; a[8] += red[g2 * 10 + 8];
+          }
+#pragma unroll
+          for (int e = 0; e < 7; e++) a[e] = grp_max<G>(a[e], gm);
+          a[7] = grp_sum<G>(a[7], gm); a[8] = grp_sum<G>(a[8], gm);
+          R.pri = a[0]; R.nz = a[1]; R.nAx = a[2]; R.dua = a[3]; R.nq = a[4]; R.nAty = a[5]; R.nPx = a[6];
+          R.obj = 0.5 * a[8] + a[7];
+        }
+        double cny = 0.0, clhs = 0.0, cnx = 0.0, cqdx = 0.0;
+        if (store_delta) {
+          for (int w2 = gl; w2 < kLatThreads / 32; w2 += G) {
+            const double *o = red + NG * 10 + w2 * 4;
+            cny = fmax(cny, o[0]); clhs += o[1]; cnx = fmax(cnx, o[2]); cqdx += o[3];
+          }
+          cny = grp_max<G>(cny, gm); cnx = grp_max<G>(cnx, gm);
+          clhs = grp_sum<G>(clhs, gm); cqdx = grp_sum<G>(cqdx, gm);
+        }
+        // check_termination (auxil.c:684-789) with the certificates pre-filtered by the CTA-wide partials: the
+        // full routines (a stage sweep each) only run when the cheap necessary conditions hold
+        auto check_term = [&](int approximate) -> int {
+          if (R.pri > kInfty || R.dua > kInfty) { status = -7; obj = kOsqpNan; return 1; }
+          double ea = S.eps_abs, er = S.eps_rel, epi = S.eps_prim_inf, edi = S.eps_dual_inf;
+          if (approximate) { ea *= 10; er *= 10; epi *= 10; edi *= 10; }
+          int prim_ok = 0, dual_ok = 0, prim_inf = 0, dual_inf = 0;
+          if (m == 0) prim_ok = 1;
+          else if (R.pri < ea + er * fmax(R.nz, R.nAx)) prim_ok = 1;
+          else if (cny > epi && clhs < -epi * cny) prim_inf = primal_infeasible<G>(M, B, inst, gl, gm, rs, epi, m);
+          if (R.dua < ea + er * fmax(fmax(R.nq, R.nAty), R.nPx)) dual_ok = 1;
+          else if (cnx > edi && cqdx < -edi * cnx) dual_inf = dual_infeasible<G>(M, B, inst, gl, gm, rs, edi, n);
+          if (prim_ok && dual_ok) { status = approximate ? 2 : 1; return 1; }
+          if (prim_inf) { status = approximate ? 3 : -3; obj = kInfty; return 1; }
+          if (dual_inf) { status = approximate ? 4 : -4; obj = -kInfty; return 1; }
+          return 0;
+        };
+        if (can_check) {
+          obj = R.obj;
+          if (check_term(0)) done = true;
+        }
+        if (!done && can_adapt) {
+          if (!can_check) { obj = R.obj; }
+          const double rn = rho_estimate(R, rho_in);
+          if (rn > rho_in * S.adaptive_rho_tolerance || rn < rho_in / S.adaptive_rho_tolerance) {
+            rho_changed = true;
+            rho_new = fmin(fmax(rn, kRhoMin), kRhoMax);
+          }
+        }
+        if (!done && last) {
+          if (!can_check) {
+            obj = R.obj;
+            check_term(0);
+          }
+          if (status == -10) {
+            if (!check_term(1)) status = -2;
+          }
+          done = true;
+        }
+        if (rho_changed && gl == 0) {
+          B.rho[inst] = rho_new;
+          B.rho_updates[inst] += 1;
+          atomicAdd(B.sched + 1, 1);
+        }
+        if (done) {
+          const bool has_sol = !(status == -3 || status == 3 || status == -4 || status == 4 || status == -7);
+          if (has_sol) obj = R.obj;
+          const double rho_est = rho_estimate(R, rho_new);
+          if (!has_sol) {  // store_solution (auxil.c:527-563)
+            if (status == -3 || status == 3) {
+              double nrm = 0.0;
+              for (int r = gl; r < m; r += G) nrm = fmax(nrm, fabs(dy[r]));
+              nrm = grp_max<G>(nrm, gm);
+              for (int r = gl; r < m; r += G) dy[r] *= 1.0 / nrm;
+            }
+            if (status == -4 || status == 4) {
+              double nrm = 0.0;
+              for (int i = gl; i < n; i += G) nrm = fmax(nrm, fabs(dx[i]));
+              nrm = grp_max<G>(nrm, gm);
+              for (int i = gl; i < n; i += G) dx[i] *= 1.0 / nrm;
+            }
+            for (int i = gl; i < n; i += G) x[i] = 0.0;
+            for (int r = gl; r < m; r += G) { z[r] = 0.0; y[r] = 0.0; }
+          }
+          if (gl == 0) {
+            B.iter[inst] = iter;
+            B.status[inst] = status;
+            B.obj[inst] = obj;
+            B.pri[inst] = R.pri;
+            B.dua[inst] = R.dua;
+            B.rho_est[inst] = rho_est;
+            atomicSub(B.sched + kSchedUnfinished, 1);
+          }
+        } else if (rho_changed) {
+          // parked for the batched re-factorisation, resumed afterwards
+          if (gl == 0) { B.iter[inst] = iter; B.status[inst] = kStatusParkedRho; }
+        }
+        if (gl == 0) ctl[1] = (done || rho_changed) ? 1 : 0;
+      }
+      __syncthreads();
+      PT(5);
+      if (ctl[1]) break;
+    }
+#ifdef RLDL_LAT_PROFILE
+    if (threadIdx.x == 0 && blockIdx.x == 0)
+      printf("lat profile inst %d iters %d: cycles/iter A %lld B %lld C %lld D %lld E %lld epi %lld  (T waits in B+D %lld)\n", inst, iter,
+             pt[0] / iter, pt[1] / iter, pt[2] / iter, pt[3] / iter, pt[4] / iter, pt[5] / iter, twait_ / iter);
+#endif
+    __syncthreads();  // ctl is rewritten by the next claim
+  }
+}
+
+// ------------------------------- launcher --------------------------------
+template <class SH>
+static size_t latency_smem_t(int N) {
+  return (size_t)LatLayout<SH>(N).end * sizeof(double);
+}
+
+template <class SH>
+static cudaError_t launch_latency_t(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
+                                    int resume, double *Tg, int ctas, int reset_parked, cudaStream_t st) {
+  const size_t shm = latency_smem_t<SH>(B.N);
+  auto kern = k_admm_cta<SH>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm);
+  if (e != cudaSuccess) return e;
+  // fresh counter; the parked-for-rho counter only if no streaming launch of this round has counted into it
+  e = cudaMemsetAsync(B.sched, 0, (reset_parked ? 2 : 1) * sizeof(int), st);
+  if (e != cudaSuccess) return e;
+  kern<<<(unsigned)ctas, kLatThreads, shm, st>>>(M, B, S, warm_start, resume, Tg);
+  return cudaGetLastError();
+}
+
+size_t latency_smem_bytes(const ModelDev &M, int N) {
+  const int cw = max_c_width(M);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_) \
+  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_) return latency_smem_t<Shape<a_, nx_, ny_, nt_, cw_>>(N);
+  RLDL_SHAPES(RLDL_X)
+#undef RLDL_X
+  return (size_t)-1;
+}
+
+cudaError_t launch_admm_latency(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
+                                int resume, double *Tg, int ctas, int reset_parked, cudaStream_t st) {
+  const int cw = max_c_width(M);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_)                                          \
+  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_)      \
+    return launch_latency_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, S, warm_start, resume, Tg, ctas, reset_parked, st);
+  RLDL_SHAPES(RLDL_X)
+#undef RLDL_X
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace rldl

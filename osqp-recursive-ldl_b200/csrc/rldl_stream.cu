@@ -32,40 +32,9 @@
 #include <stdlib.h>
 #include "rldl_device_fn.cuh"
 #include "rldl_kernels.h"
+#include "rldl_stream_common.cuh"
 
 namespace rldl {
-
-// ------------------------------ PTX helpers ------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// 1-D bulk async copy global -> shared (TMA engine); completes on `bar`.
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-               "l"(src), "r"(bytes), "r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "RLDL_WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra RLDL_DONE_%=;\n"
-      "bra RLDL_WAIT_%=;\n"
-      "RLDL_DONE_%=:\n"
-      "}" ::"r"(bar),
-      "r"(parity)
-      : "memory");
-}
-
-__host__ __device__ inline int even_up(int v) { return (v + 1) & ~1; }
-// doubles of the diagonal-packed form of a symmetric n x n matrix
-__host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
 
 // ---------------------------------------------------------------------------
 // Record packing: (Xinv, Sinv, q, l, u, rho_vec) -> rec, stages k0..N of every instance.
@@ -154,83 +123,6 @@ void stream_record_dims(int a, int nx, int b, int *qa, int *PX, int *PS, int *bb
 }
 
 // ---------------------------------------------------------------------------
-// Compile-time shape of one specialisation
-// ---------------------------------------------------------------------------
-template <int A_, int NX_, int NY_, int NT_, int CW_>
-struct Shape {
-  static constexpr int A = A_, NX = NX_, NY = NY_, NT = NT_, CW = CW_;
-  static constexpr int B = NX + NY;
-  static constexpr int G = A <= 8 ? 8 : (A <= 16 ? 16 : 32);
-  static constexpr int GPW = 32 / G;
-  static constexpr int RMAX = NY > NT ? NY : NT;
-  static constexpr int NYT = (RMAX + G - 1) / G;
-  static constexpr int ROWS = NYT * G;
-  static constexpr int QA = (A + 1) & ~1, PX = ((A / 2 + 1) * A + 1) & ~1, PS = ((NX / 2 + 1) * NX + 1) & ~1,
-                       BB = (B + 1) & ~1;
-  static constexpr int RS = QA + PX + PS + 3 * BB;
-  static constexpr int XOFF = QA, SOFF = QA + PX, RHO = QA + PX + PS, LO = RHO + BB, UP = LO + BB;
-  static constexpr uint32_t FWD_BYTES = 8u * (QA + PX + PS + BB), BWD_BYTES = 8u * (PX + PS + 3 * BB);
-  // per-group scratch (doubles, every block even-sized)
-  static constexpr int AE = (A + 1) & ~1, NXE = (NX + 1) & ~1;
-  // the vectors of the forward sweep (w, tv2, yv, td2, sp) and of the backward sweep (vn2, vc, nud, gg2)
-  // are never live together, so the two sets share one region (4 CTAs/SM need <= 56 KB per CTA)
-  static constexpr int O_W = 0, O_TV2 = O_W + ROWS, O_YV = O_TV2 + 2 * AE, O_TD2 = O_YV + AE, O_SP = O_TD2 + 2 * NXE,
-                       SC_FWD = O_SP + NXE;
-  static constexpr int O_VN2 = 0, O_VC = O_VN2 + 2 * NXE, O_NUD = O_VC + AE, O_GG2 = O_NUD + NXE, SC_BWD = O_GG2 + 2 * AE;
-  static constexpr int SC_SWEEP = SC_FWD > SC_BWD ? SC_FWD : SC_BWD;
-  static constexpr int VM = (A > RMAX ? A : RMAX);
-  // the residual routines (5 vectors of VM doubles) alias the sweep scratch between iterations
-  static constexpr int SC = SC_SWEEP > 5 * VM ? SC_SWEEP : 5 * VM;
-  // CTA-shared model block (doubles)
-  static constexpr int M_FD = 0, M_FDT = M_FD + 2 * A * NX, M_CV = M_FDT + 2 * A * NX, M_CTV = M_CV + 3 * ROWS * CW,
-                       M_CI = M_CTV + 3 * AE * CW,                       // ints from here: 3*ROWS*CW
-                       M_CTI = M_CI + (3 * ROWS * CW + 1) / 2,            // ints: 3*AE*CW
-                       M_END = (M_CTI + (3 * AE * CW + 1) / 2 + 1) & ~1;
-  static constexpr int WNX = (A - 1 - A / 2) > 0 ? (A - 1 - A / 2) : 1;
-  static constexpr int WNS = (NX - 1 - NX / 2) > 0 ? (NX - 1 - NX / 2) : 1;
-  __host__ __device__ static int group_doubles(int D) { return ((D * RS + D + SC) + 1) & ~1; }
-};
-
-// y_i = sum_j M(i,j) v_j from the diagonal-packed form.  Dpi = DP + i, v2i = v2 + i (v doubled),
-// wrap[d-1] = d*N + (i-d) mod N.
-template <int N, int WN>
-__device__ __forceinline__ double dmv(const double *__restrict__ Dp, const double *__restrict__ Dpi,
-                                      const double *__restrict__ v2i, const int (&wrap)[WN]) {
-  double acc[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-  for (int d = 0; d <= N / 2; d++) acc[d & 3] = fma(Dpi[d * N], v2i[d], acc[d & 3]);
-#pragma unroll
-  for (int d = 1; d <= N - 1 - N / 2; d++)
-    acc[(N / 2 + d) & 3] = fma(Dp[wrap[d - 1]], v2i[N - d], acc[(N / 2 + d) & 3]);
-  return (acc[0] + acc[1]) + (acc[2] + acc[3]);
-}
-
-// sum_j Mcol[j*LD] * v[j], j < NJ  (Mcol already offset by the lane's row)
-template <int NJ, int LD>
-__device__ __forceinline__ double dense_mv(const double *__restrict__ Mcol, const double *__restrict__ v) {
-  double acc[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-  for (int j = 0; j < NJ; j++) acc[j & 3] = fma(Mcol[j * LD], v[j], acc[j & 3]);
-  return (acc[0] + acc[1]) + (acc[2] + acc[3]);
-}
-
-template <int CW>
-__device__ __forceinline__ double ell_row(const double *__restrict__ val, const int *__restrict__ idx, int row,
-                                          const double *__restrict__ v) {
-  double s = 0.0;
-#pragma unroll
-  for (int e = 0; e < CW; e++) s = fma(val[row * CW + e], v[idx[row * CW + e]], s);
-  return s;
-}
-
-
-template <int NYT>
-struct MutVec {  // the mutable per-stage values a lane owns (iterates and forward intermediates)
-  double x, zd, yd, yk, sk;
-  double zp[NYT], yp[NYT];
-};
-
-// ---------------------------------------------------------------------------
 // Device work scheduler.  Iteration counts inside a batch are heavy-tailed (C5: mean 330,
 // max 4000), and an instance is a strictly sequential chain, so the order in which instances
 // are started decides how long the kernel runs half-empty at the end.  Instances are therefore
@@ -284,7 +176,7 @@ __device__ __forceinline__ int sched_best(const BatchDev &B, int gl, unsigned gm
 // ---------------------------------------------------------------------------
 template <class SH>
 __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, SettingsDev S, int warm_start, int D,
-                                                        int resume, int s0) {
+                                                        int resume, int s0, int park_below) {
   constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, NT = SH::NT, CW = SH::CW, G = SH::G, NYT = SH::NYT,
                 ROWS = SH::ROWS, RS = SH::RS, BQ = SH::B;
   extern __shared__ __align__(16) double smem[];
@@ -405,8 +297,17 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   };
   // claim an instance: fresh ones first, then the most urgent suspended one, provided its
   // bucket is above `above`.  Returns the instance (group-uniform) or -1; *fresh tells which.
+  auto tail_reached = [&]() -> bool {  // few enough instances left: they go to the latency-mode kernel
+    int t = 0;
+    if (park_below > 0) {
+      if (gl == 0) t = ld_volatile(B.sched + kSchedUnfinished) <= park_below;
+      t = __shfl_sync(gm, t, 0, G);
+    }
+    return t != 0;
+  };
   auto acquire = [&](int above, bool *fresh) -> int {
     for (;;) {
+      if (tail_reached()) return -1;
       int i = -1;
       if (gl == 0 && ld_volatile(B.sched) < B.batch) {
         i = atomicAdd(B.sched, 1);
@@ -416,9 +317,12 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       if (i >= 0) {
         bool skip = false;
         if (B.fact_flag[i]) {  // failed factorisation: report non-convex, like a diverged solve
-          if (gl == 0) { B.status[i] = -7; B.iter[i] = 0; B.obj[i] = kOsqpNan; }
+          if (gl == 0 && (!resume || __ldcg(B.status + i) == -10)) {
+            B.status[i] = -7; B.iter[i] = 0; B.obj[i] = kOsqpNan;
+            atomicSub(B.sched + kSchedUnfinished, 1);
+          }
           skip = true;
-        } else if (resume && B.status[i] != -10) {
+        } else if (resume && __ldcg(B.status + i) != -10) {
           skip = true;  // finished in an earlier launch of this solve
         }
         if (skip) continue;
@@ -677,14 +581,21 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           B.pri[inst] = R.pri;
           B.dua[inst] = R.dua;
           B.rho_est[inst] = rho_est;
+          atomicSub(B.sched + kSchedUnfinished, 1);
         }
         drain();
         have = start_next();
       } else if (rho_changed) {
-        // parked: the host re-types rho_vec, re-factorises and re-packs this instance, then resumes it
-        if (gl == 0) B.iter[inst] = iter;
+        // parked: the host re-types rho_vec, re-factorises and re-packs this instance, then resumes it;
+        // until then no kernel of this solve may pick it up (k_set_rho_vec turns the mark back into UNSOLVED)
+        if (gl == 0) { B.iter[inst] = iter; B.status[inst] = kStatusParkedRho; }
         drain();
         have = start_next();
+      } else if (can_check && tail_reached()) {
+        // suspended as it stands (status stays OSQP_UNSOLVED): the latency-mode kernel resumes it
+        if (gl == 0) B.iter[inst] = iter;
+        drain();
+        have = false;
       } else {
         bool yield = false;
         int myb = 0;
@@ -719,7 +630,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
 // ------------------------------- launcher --------------------------------
 template <class SH>
 static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                   int resume, cudaStream_t st) {
+                                   int resume, int park_below, cudaStream_t st) {
   const int threads = 128, groups = (threads / 32) * SH::GPW;
   int D = 2;  // ring depth: two stage steps of look-ahead cover the HBM latency
   if (const char *e = getenv("RLDL_RING_DEPTH")) D = atoi(e) > 1 ? atoi(e) : 2;
@@ -748,11 +659,10 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   // scheduler state: counters to 0, every ring slot to -1 (empty)
   e = cudaMemsetAsync(B.sched, 0, (2 + 2 * kSchedBuckets) * sizeof(int), st);
   if (e != cudaSuccess) return e;
-  if (!resume) {  // the rings are empty again at the end of every launch
-    e = cudaMemsetAsync(B.sched_slots, 0xff, (size_t)kSchedBuckets * B.batch * sizeof(int), st);
-    if (e != cudaSuccess) return e;
-  }
-  kern<<<(unsigned)grid, threads, shm, st>>>(M, B, S, warm_start, D, resume, s0);
+  // (instances suspended for the latency-mode kernel may be left in the rings of an earlier launch)
+  e = cudaMemsetAsync(B.sched_slots, 0xff, (size_t)kSchedBuckets * B.batch * sizeof(int), st);
+  if (e != cudaSuccess) return e;
+  kern<<<(unsigned)grid, threads, shm, st>>>(M, B, S, warm_start, D, resume, s0, park_below);
   return cudaGetLastError();
 }
 
@@ -995,21 +905,6 @@ static cudaError_t launch_factor_stream_t(const ModelDev &M, const BatchDev &B, 
   return cudaGetLastError();
 }
 
-// The specialisation table: (nx+nu, nx, ny, nt, ELL width of C) of the BASELINE.json shapes.
-#define RLDL_SHAPES(X) \
-  X(6, 4, 6, 4, 1)     \
-  X(16, 12, 16, 12, 1) \
-  X(11, 8, 11, 8, 1)
-
-static int max_c_width(const ModelDev &M) {
-  int wdt = 0;
-  for (int c = 0; c < 3; c++) {
-    if (M.sc[c].C.width > wdt) wdt = M.sc[c].C.width;
-    if (M.sc[c].Ct.width > wdt) wdt = M.sc[c].Ct.width;
-  }
-  return wdt;
-}
-
 bool stream_supported(const ModelDev &M, int N) {
   if (N < 1) return false;
   const int cw = max_c_width(M);
@@ -1021,11 +916,11 @@ bool stream_supported(const ModelDev &M, int N) {
 }
 
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                               int resume, cudaStream_t st) {
+                               int resume, int park_below, cudaStream_t st) {
   const int cw = max_c_width(M);
 #define RLDL_X(a_, nx_, ny_, nt_, cw_)                                          \
   if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_)      \
-    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, S, warm_start, resume, st);
+    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, S, warm_start, resume, park_below, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;

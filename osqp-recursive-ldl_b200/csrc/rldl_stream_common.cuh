@@ -1,0 +1,138 @@
+// rldl_stream_common.cuh — pieces shared by the shape-specialised kernels (rldl_stream.cu: the
+// HBM-streaming ADMM kernel and the stage recursion; rldl_latency.cu: the CTA-per-instance
+// latency-mode ADMM kernel): PTX helpers for mbarrier / bulk copies, the compile-time Shape with
+// the stage-record layout, and the small mat-vec primitives on diagonal-packed symmetric blocks.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "rldl_device_fn.cuh"
+
+namespace rldl {
+
+// ------------------------------ PTX helpers ------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// 1-D bulk async copy global -> shared (TMA engine); completes on `bar`.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "RLDL_WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra RLDL_DONE_%=;\n"
+      "bra RLDL_WAIT_%=;\n"
+      "RLDL_DONE_%=:\n"
+      "}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+
+
+__host__ __device__ inline int even_up(int v) { return (v + 1) & ~1; }
+// doubles of the diagonal-packed form of a symmetric n x n matrix
+__host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
+
+// ---------------------------------------------------------------------------
+// Compile-time shape of one specialisation
+// ---------------------------------------------------------------------------
+template <int A_, int NX_, int NY_, int NT_, int CW_>
+struct Shape {
+  static constexpr int A = A_, NX = NX_, NY = NY_, NT = NT_, CW = CW_;
+  static constexpr int B = NX + NY;
+  static constexpr int G = A <= 8 ? 8 : (A <= 16 ? 16 : 32);
+  static constexpr int GPW = 32 / G;
+  static constexpr int RMAX = NY > NT ? NY : NT;
+  static constexpr int NYT = (RMAX + G - 1) / G;
+  static constexpr int ROWS = NYT * G;
+  static constexpr int QA = (A + 1) & ~1, PX = ((A / 2 + 1) * A + 1) & ~1, PS = ((NX / 2 + 1) * NX + 1) & ~1,
+                       BB = (B + 1) & ~1;
+  static constexpr int RS = QA + PX + PS + 3 * BB;
+  static constexpr int XOFF = QA, SOFF = QA + PX, RHO = QA + PX + PS, LO = RHO + BB, UP = LO + BB;
+  static constexpr uint32_t FWD_BYTES = 8u * (QA + PX + PS + BB), BWD_BYTES = 8u * (PX + PS + 3 * BB);
+  // per-group scratch (doubles, every block even-sized)
+  static constexpr int AE = (A + 1) & ~1, NXE = (NX + 1) & ~1;
+  // the vectors of the forward sweep (w, tv2, yv, td2, sp) and of the backward sweep (vn2, vc, nud, gg2)
+  // are never live together, so the two sets share one region (4 CTAs/SM need <= 56 KB per CTA)
+  static constexpr int O_W = 0, O_TV2 = O_W + ROWS, O_YV = O_TV2 + 2 * AE, O_TD2 = O_YV + AE, O_SP = O_TD2 + 2 * NXE,
+                       SC_FWD = O_SP + NXE;
+  static constexpr int O_VN2 = 0, O_VC = O_VN2 + 2 * NXE, O_NUD = O_VC + AE, O_GG2 = O_NUD + NXE, SC_BWD = O_GG2 + 2 * AE;
+  static constexpr int SC_SWEEP = SC_FWD > SC_BWD ? SC_FWD : SC_BWD;
+  static constexpr int VM = (A > RMAX ? A : RMAX);
+  // the residual routines (5 vectors of VM doubles) alias the sweep scratch between iterations
+  static constexpr int SC = SC_SWEEP > 5 * VM ? SC_SWEEP : 5 * VM;
+  // CTA-shared model block (doubles)
+  static constexpr int M_FD = 0, M_FDT = M_FD + 2 * A * NX, M_CV = M_FDT + 2 * A * NX, M_CTV = M_CV + 3 * ROWS * CW,
+                       M_CI = M_CTV + 3 * AE * CW,                       // ints from here: 3*ROWS*CW
+                       M_CTI = M_CI + (3 * ROWS * CW + 1) / 2,            // ints: 3*AE*CW
+                       M_END = (M_CTI + (3 * AE * CW + 1) / 2 + 1) & ~1;
+  static constexpr int WNX = (A - 1 - A / 2) > 0 ? (A - 1 - A / 2) : 1;
+  static constexpr int WNS = (NX - 1 - NX / 2) > 0 ? (NX - 1 - NX / 2) : 1;
+  __host__ __device__ static int group_doubles(int D) { return ((D * RS + D + SC) + 1) & ~1; }
+};
+
+// y_i = sum_j M(i,j) v_j from the diagonal-packed form.  Dpi = DP + i, v2i = v2 + i (v doubled),
+// wrap[d-1] = d*N + (i-d) mod N.
+template <int N, int WN>
+__device__ __forceinline__ double dmv(const double *__restrict__ Dp, const double *__restrict__ Dpi,
+                                      const double *__restrict__ v2i, const int (&wrap)[WN]) {
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+  for (int d = 0; d <= N / 2; d++) acc[d & 3] = fma(Dpi[d * N], v2i[d], acc[d & 3]);
+#pragma unroll
+  for (int d = 1; d <= N - 1 - N / 2; d++)
+    acc[(N / 2 + d) & 3] = fma(Dp[wrap[d - 1]], v2i[N - d], acc[(N / 2 + d) & 3]);
+  return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
+// sum_j Mcol[j*LD] * v[j], j < NJ  (Mcol already offset by the lane's row)
+template <int NJ, int LD>
+__device__ __forceinline__ double dense_mv(const double *__restrict__ Mcol, const double *__restrict__ v) {
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+  for (int j = 0; j < NJ; j++) acc[j & 3] = fma(Mcol[j * LD], v[j], acc[j & 3]);
+  return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
+template <int CW>
+__device__ __forceinline__ double ell_row(const double *__restrict__ val, const int *__restrict__ idx, int row,
+                                          const double *__restrict__ v) {
+  double s = 0.0;
+#pragma unroll
+  for (int e = 0; e < CW; e++) s = fma(val[row * CW + e], v[idx[row * CW + e]], s);
+  return s;
+}
+
+
+template <int NYT>
+struct MutVec {  // the mutable per-stage values a lane owns (iterates and forward intermediates)
+  double x, zd, yd, yk, sk;
+  double zp[NYT], yp[NYT];
+};
+
+
+// The specialisation table: (nx+nu, nx, ny, nt, ELL width of C) of the BASELINE.json shapes.
+#define RLDL_SHAPES(X) \
+  X(6, 4, 6, 4, 1)     \
+  X(16, 12, 16, 12, 1) \
+  X(11, 8, 11, 8, 1)
+
+inline int max_c_width(const ModelDev &M) {
+  int wdt = 0;
+  for (int c = 0; c < 3; c++) {
+    if (M.sc[c].C.width > wdt) wdt = M.sc[c].C.width;
+    if (M.sc[c].Ct.width > wdt) wdt = M.sc[c].Ct.width;
+  }
+  return wdt;
+}
+
+}  // namespace rldl

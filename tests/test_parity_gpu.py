@@ -58,7 +58,8 @@ def test_scheduler_does_not_change_results(monkeypatch):
     oversubscribe the groups and force preemptions, results are bitwise those of first-come order."""
     mdl, N, x0, q, l, u = problem("C1", 40000)
     outs = []
-    for s0 in ("0", "25"):
+    monkeypatch.setenv("RLDL_LAT_BELOW", "0")  # streaming kernel only: which instances the latency-mode
+    for s0 in ("0", "25"):                      # kernel finishes is timing dependent (rounding-level differences)
         monkeypatch.setenv("RLDL_SCHED_S0", s0)
         gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
         assert gb.solve() == 0
@@ -69,10 +70,14 @@ def test_scheduler_does_not_change_results(monkeypatch):
     assert outs[0]["iter"].max() > outs[0]["iter"].min()  # the batch really is imbalanced
 
 
+@pytest.mark.parametrize("below", ["0", "16", "100000"])
 @pytest.mark.parametrize("name,batch", [("C4", 48), ("C1", 64)])
-def test_adaptive_rho_streaming_matches_generic_kernel(name, batch):
-    """Adaptive rho: the streaming kernel parks an instance, the host re-factorises the parked ones in one
-    batched launch and resumes them; the generic kernel re-factorises in place.  Same iteration."""
+def test_adaptive_rho_streaming_matches_generic_kernel(name, batch, below, monkeypatch):
+    """Adaptive rho: the streaming / latency-mode kernels park an instance, the host re-factorises the parked
+    ones in one batched launch and resumes them; the generic kernel re-factorises in place.  Same iteration,
+    whether the streaming kernel runs alone (0), hands its tail to the latency-mode kernel (16) or the
+    latency-mode kernel runs alone (100000)."""
+    monkeypatch.setenv("RLDL_LAT_BELOW", below)
     mdl, N, x0, q, l, u = problem(name, batch)
     rng = np.random.default_rng(5)
     rho = rng.choice([1e-3, 0.1, 10.0], size=batch)
@@ -108,3 +113,22 @@ def test_batch_update_bounds_rejects_l_above_u_and_keeps_problem():
     assert (out["iter"] == ref["iter"]).all() and np.array_equal(out["x"], ref["x"])
     assert gb.update_bounds(l, u) == 0
     gb.free()
+
+
+@pytest.mark.parametrize("name,batch", [("C1", 300), ("C3", 200), ("C4", 160)])
+@pytest.mark.parametrize("mode", ["latency_only", "handoff"])
+def test_latency_mode_kernel_matches_streaming_kernel(name, batch, mode, monkeypatch):
+    """The CTA-per-instance latency-mode kernel (re-associated block substitution, factor resident in shared
+    memory) alone, and as the finisher of a streaming launch that suspends its last instances, against the
+    streaming kernel alone: same status / iterations, x, y, obj within 1e-6."""
+    mdl, N, x0, q, l, u = problem(name, batch)
+    outs = []
+    for below in ("0", "100000" if mode == "latency_only" else str(batch // 3)):
+        monkeypatch.setenv("RLDL_LAT_BELOW", below)
+        gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+        assert gb.solve() == 0
+        outs.append(gb.get())
+        n, m, _, _ = gb.dims()
+        gb.free()
+    bad = compare(outs[1], outs[0], n, m)
+    assert not bad, bad[:5]
