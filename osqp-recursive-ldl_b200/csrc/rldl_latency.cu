@@ -55,7 +55,7 @@ struct LatLayout {  // shared-memory layout (doubles) of k_admm_cta for horizon 
     scr = vd + (N + 1) * SH::NXE;
     bar = scr + NG * SH::SC;
     ctl = bar + 2;
-    tring = ctl + 4;
+    tring = ctl + 4;  // ctl: 4 ints (instance, leave flag, forward / backward scan progress) padded to 16 bytes
     tbar = tring + NS * CH * TBLK;
     qs = tbar + NS + (NS & 1);
     red = qs + 3 * SH::A * SH::A;  // dense cost blocks padded to A x A (residuals)
@@ -121,6 +121,13 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
   double *sc = smem + L.scr + (size_t)grp * SH::SC;
   uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L.bar);
   volatile int *ctl = reinterpret_cast<volatile int *>(smem + L.ctl);
+  volatile int *prog_f = ctl + 2, *prog_b = ctl + 3;  // progress of the forward / backward scan (see scan())
+  auto wait_prog = [&](volatile int *p, int need) {
+    while (*p < need) __nanosleep(64);  // back off: the scan warp shares its scheduler with pollers
+    __threadfence_block();
+  };
+  // groups 2.. work behind the scans (group 1 shares warp 0 with the scanning group and stays out of its way)
+  constexpr int NGW = NG - 2;
   double *w = sc + SH::O_W, *tv2 = sc + SH::O_TV2, *yvs = sc + SH::O_YV, *td2 = sc + SH::O_TD2;
   double *vn2 = sc + SH::O_VN2, *vcur = sc + SH::O_VC, *nudv = sc + SH::O_NUD, *gg2 = sc + SH::O_GG2;
   Scratch rs;  // residual routines (group 0 only) alias that group's scratch
@@ -131,6 +138,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
   double *tring = smem + L.tring;
   uint64_t *tbars = reinterpret_cast<uint64_t *>(smem + L.tbar);
   if (threadIdx.x == 0) {
+    ctl[2] = 0; ctl[3] = 0;
     mbar_init(bar, 1);
     for (int d = 0; d < NS; d++) mbar_init(&tbars[d], 1);
   }
@@ -183,6 +191,15 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     };
     if (gl == 0)
       for (int c = 0; c < NS && c < nchunk; c++) issue_chunk(c);
+    // progress counter of this scan: number of final vectors (the first one is final before the scan starts);
+    // the other direction's counter is idle during this phase and is reset here for its next use
+    volatile int *prog = fwd ? prog_f : prog_b;
+    int done_ = 1;
+    if (gl == 0) {
+      *(fwd ? prog_b : prog_f) = 0;
+      __threadfence_block();
+      *prog = 1;
+    }
     // 32-bit shared addresses, advanced incrementally: nothing but the mat-vec itself is on the chain
     const int row = (gl < NX) ? gl : 0;
     const uint32_t vec_s = smem_u32(vec);
@@ -200,6 +217,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       const int cnt = min(CH, nblk - c * CH);
       uint32_t ta = tring_s + 8u * (uint32_t)((s * CH + (fwd ? 0 : cnt - 1)) * TBLK + row * TS);
       for (int r = 0; r < cnt; r++) {
+        // (loading the next stage's T rows ahead of the STS below was measured slower: the loads sit in the
+        // in-order LSU queue in front of the store the next stage is waiting for)
         double2 tv[NX / 2], vv[NX / 2];
 #pragma unroll
         for (int j = 0; j < NX / 2; j++) tv[j] = lds128(ta + 16u * j);
@@ -215,6 +234,9 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         }
         if (gl < NX) sts64(pk + 8u * gl, cur + ((acc[0] + acc[1]) + (acc[2] + acc[3])));
         __syncwarp(gm);
+        // publish (after the __syncwarp: the stores of one warp reach shared memory in program order);
+        // the groups working behind the scan poll this counter
+        if (gl == 0) *prog = ++done_;
         ta += tstep;
         pk += dstep;
       }
@@ -300,6 +322,63 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     __threadfence();  // T blocks are read back by bulk async copies (async proxy)
     asm volatile("fence.proxy.async;" ::: "memory");
     __syncthreads();
+    // ===== phase A for one stage: rhs, a_k = Xinv_k r^v_k, c_k = Sinv_k (r^d_k - F_k a_k), from the iterates of
+    // the stage held by the lanes that own them (loaded from HBM for the first iteration of an instance, handed
+    // over in registers by phase E afterwards) =====
+    auto stage_A = [&](int k, double xv, const double (&zp)[NYT], const double (&yp)[NYT], double zd, double yd) {
+      const bool term = (k == N);
+      const int cls = term ? 2 : (k == 0 ? 0 : 1);
+      const int dim = term ? NX : A, np = term ? NT : NY;
+      const int ilo = (k == 0) ? NX : 0;
+      const double *sl_ = recs + k * RS;
+      double g = 0.0;
+      if (gl >= ilo && gl < dim) g = sigma * xv - sl_[gl];
+#pragma unroll
+      for (int t = 0; t < NYT; t++) {
+        const int rr = gl + G * t;
+        if (rr < np) w[rr] = sl_[SH::RHO + rr] * zp[t] - yp[t];
+      }
+      __syncwarp(gm);
+      double tt = 0.0;
+      if (gl < dim) tt = g + ell_row<CW>(Ctv + cls * AE * CW, Cti + cls * AE * CW, gl, w);
+      if (gl < A) { tv2[gl] = tt; tv2[gl + A] = tt; }
+      __syncwarp(gm);
+      if (gl < A) {
+        const double av = dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, tv2 + gl, wrapX);
+        va[k * AE + gl] = av;
+        yvs[gl] = av;
+      }
+      __syncwarp(gm);
+      if (!term) {
+        if (gl < NX) {
+          const double ri = rinv_of(sl_[SH::RHO + NY + gl]);
+          const double tdv = (zd - yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
+          td2[gl] = tdv; td2[gl + NX] = tdv;
+        }
+        __syncwarp(gm);
+        if (gl < NX) vc[k * NXE + gl] = dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, td2 + gl, wrapS);
+      }
+      __syncwarp(gm);
+    };
+    // first iteration: phase A from the iterates in HBM, by the groups that will own the stages in phase E
+    if (grp >= 2) {
+      for (int k = grp - 2; k <= N; k += NGW) {
+        const bool term = (k == N);
+        const int dim = term ? NX : A, np = term ? NT : NY;
+        const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
+        const double xv = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
+        double zp[NYT], yp[NYT], zd = 0.0, yd = 0.0;
+#pragma unroll
+        for (int t = 0; t < NYT; t++) {
+          const int rr = gl + G * t;
+          zp[t] = yp[t] = 0.0;
+          if (rr < np) { zp[t] = __ldcg(z + roff + rr); yp[t] = __ldcg(y + roff + rr); }
+        }
+        if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
+        stage_A(k, xv, zp, yp, zd, yd);
+      }
+    }
+    __syncthreads();
     // ---------------- ADMM iterations (osqp.c:354-519) ----------------
 #ifdef RLDL_LAT_PROFILE
     long long pt[7] = {0, 0, 0, 0, 0, 0, 0}, pc = 0;
@@ -316,83 +395,40 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval && (iter % S.adaptive_rho_interval == 0);
       const bool last = iter == S.max_iter;
       const bool store_delta = can_check || last;
-      // ===== phase A: rhs, a_k = Xinv_k r^v_k, c_k = Sinv_k (r^d_k - F_k a_k) =====
-      for (int k = grp; k <= N; k += NG) {
-        const bool term = (k == N);
-        const int cls = term ? 2 : (k == 0 ? 0 : 1);
-        const int dim = term ? NX : A, np = term ? NT : NY;
-        const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
-        const double *sl_ = recs + k * RS;
-        const double xv = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
-        double zp[NYT], yp[NYT], zd = 0.0, yd = 0.0;
-#pragma unroll
-        for (int t = 0; t < NYT; t++) {
-          const int rr = gl + G * t;
-          zp[t] = yp[t] = 0.0;
-          if (rr < np) { zp[t] = __ldcg(z + roff + rr); yp[t] = __ldcg(y + roff + rr); }
-        }
-        if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
-        double g = 0.0;
-        if (gl >= ilo && gl < dim) g = sigma * xv - sl_[gl];
-#pragma unroll
-        for (int t = 0; t < NYT; t++) {
-          const int rr = gl + G * t;
-          if (rr < np) w[rr] = sl_[SH::RHO + rr] * zp[t] - yp[t];
-        }
-        __syncwarp(gm);
-        double tt = 0.0;
-        if (gl < dim) tt = g + ell_row<CW>(Ctv + cls * AE * CW, Cti + cls * AE * CW, gl, w);
-        if (gl < A) { tv2[gl] = tt; tv2[gl + A] = tt; }
-        __syncwarp(gm);
-        if (gl < A) {
-          const double av = dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, tv2 + gl, wrapX);
-          va[k * AE + gl] = av;
-          yvs[gl] = av;
-        }
-        __syncwarp(gm);
-        if (!term) {
-          if (gl < NX) {
-            const double ri = rinv_of(sl_[SH::RHO + NY + gl]);
-            const double tdv = (zd - yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
-            td2[gl] = tdv; td2[gl + NX] = tdv;
+      // ===== phases B and C, pipelined.  B (group 0): sp_k = c_k + T_k sp_{k-1}, in place in vc.
+      //       C (groups 2..): e_k = a_k + Xinv_k (F_k' sp_k - J' sp_{k-1}), d_k = e_k[0:nx], as soon as the scan
+      //       has published sp_k =====
+      if (grp == 0) {
+        scan(true);
+      } else if (grp >= 2) {
+        for (int k = grp - 2; k <= N; k += NGW) {
+          const bool term = (k == N);
+          const double *sl_ = recs + k * RS;
+          wait_prog(prog_f, (term ? N - 1 : k) + 1);
+          if (gl < A) {
+            double gg = 0.0;
+            if (!term) gg = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, vc + k * NXE);
+            if (k > 0 && gl < NX) gg -= vc[(k - 1) * NXE + gl];
+            gg2[gl] = gg; gg2[gl + A] = gg;
           }
           __syncwarp(gm);
-          if (gl < NX) vc[k * NXE + gl] = dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, td2 + gl, wrapS);
+          if (gl < A) {
+            const double e = va[k * AE + gl] + dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
+            va[k * AE + gl] = e;
+            if (gl < NX) vd[k * NXE + gl] = e;
+          }
+          __syncwarp(gm);
         }
-        __syncwarp(gm);
-      }
-      __syncthreads();
-      PT(0);
-      // ===== phase B: sp_k = c_k + T_k sp_{k-1}, in place in vc =====
-      if (grp == 0) scan(true);
-      __syncthreads();
-      PT(1);
-      // ===== phase C: e_k = a_k + Xinv_k (F_k' sp_k - J' sp_{k-1}),  d_k = e_k[0:nx] =====
-      for (int k = grp; k <= N; k += NG) {
-        const bool term = (k == N);
-        const double *sl_ = recs + k * RS;
-        if (gl < A) {
-          double gg = 0.0;
-          if (!term) gg = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, vc + k * NXE);
-          if (k > 0 && gl < NX) gg -= vc[(k - 1) * NXE + gl];
-          gg2[gl] = gg; gg2[gl + A] = gg;
-        }
-        __syncwarp(gm);
-        if (gl < A) {
-          const double e = va[k * AE + gl] + dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
-          va[k * AE + gl] = e;
-          if (gl < NX) vd[k * NXE + gl] = e;
-        }
-        __syncwarp(gm);
       }
       __syncthreads();
       PT(2);
-      // ===== phase D: vn_k = d_k + T_k' vn_{k+1}, k = N-1 .. 1, in place in vd (vn_N = d_N; stage 0 has no state) =====
+      // ===== phases D and E, pipelined.  D (group 0): vn_k = d_k + T_k' vn_{k+1}, k = N-1 .. 1, in place in vd
+      //       (vn_N = d_N; stage 0 has no state) =====
+      // (phase E below runs behind this scan: groups 2.. take their stages in descending order and start on
+      // stage k once vn_{k+1} is published)
       if (grp == 0) scan(false);
-      __syncthreads();
-      PT(3);
       // ===== phase E: v_k = e_k + Xinv_k F_k' (Sinv_k vn_{k+1}), nu^d_k, ADMM step (auxil.c:188-228) =====
-      for (int k = grp; k <= N; k += NG) {
+      for (int k = (grp >= 2 && grp - 2 <= N) ? (grp - 2) + ((N - (grp - 2)) / NGW) * NGW : -1; k >= 0; k -= NGW) {
         const bool term = (k == N);
         const int cls = term ? 2 : (k == 0 ? 0 : 1);
         const int dim = term ? NX : A, np = term ? NT : NY;
@@ -408,6 +444,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         }
         if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
         double vv = 0.0, nud = 0.0;
+        if (!term) wait_prog(prog_b, N - k);  // vn_{k+1} published (the loads above are already in flight)
         if (term) {
           if (gl < A) vv = va[k * AE + gl];
         } else {
@@ -442,6 +479,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
             const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
             z[ri] = zn; y[ri] = yo + d;
+            zp[t] = zn; yp[t] = yo + d;  // handed to phase A of the next iteration
             if (store_delta) dy[ri] = d;
           }
         }
@@ -454,13 +492,19 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
           const double d = rho * (zh - zn);
           z[ri] = zn; y[ri] = yd + d;
           if (store_delta) dy[ri] = d;
+          zd = zn; yd = yd + d;
         }
+        double xnew = 0.0;
         if (gl >= ilo && gl < dim) {
           const double xn = alpha * vv + oma * xo;
+          xnew = xn;
           x[xoff + gl] = xn;
           if (store_delta) dx[xoff + gl] = xn - xo;
         }
         __syncwarp(gm);
+        // phase A of the next iteration for this stage, straight from the registers (its inputs are stage-local;
+        // va[k] / vc[k] have no reader left in this iteration)
+        stage_A(k, xnew, zp, yp, zd, yd);
       }
       if (!(can_check || can_adapt || last)) {
         __syncthreads();  // iterates of this iteration visible to every group of the CTA
