@@ -261,7 +261,7 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   B->streaming = !generic && stream_supported(B->M, B->N);
   {
     stream_record_dims(B->a, B->nx, B->b, &D.qa, &D.PX, &D.PS, &D.bb);
-    D.RS = D.qa + D.PX + D.PS + 3 * D.bb;
+    D.RS = D.qa + D.PX + D.PS + kClsWords + 2 * D.bb;
     D.rec_stride = (long long)(B->Nmax + 1) * D.RS;
     CK(dalloc(&D.rec, B->streaming ? bs * (size_t)D.rec_stride : 1));
     CK(dalloc(&D.sched, kSchedCounters));
@@ -668,7 +668,7 @@ double Batch::admm_bytes_per_iteration() const {
   if (use_stream()) {
     // streaming kernel: every stage record is streamed once forward ([q|Xinv|Sinv|rho]) and once
     // backward ([Xinv|Sinv|rho|l|u]); the iterates x,z,y are counted first-read + last-write only
-    const double fwd = D.qa + D.PX + D.PS + D.bb, bwd = D.PX + D.PS + 3.0 * D.bb;
+    const double fwd = D.qa + D.PX + D.PS + kClsWords, bwd = D.PX + D.PS + kClsWords + 2.0 * D.bb;
     return 8.0 * ((N + 1) * (fwd + bwd) + 2.0 * (D.n + 2.0 * D.m));
   }
   // generic kernel: the full (unpacked) pivot inverses streamed once forward and once backward,

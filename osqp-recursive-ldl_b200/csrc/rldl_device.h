@@ -67,7 +67,7 @@ struct BatchDev {
   int *rho_updates;
   int *fact_flag;          // 0 ok, >0 = 1 + stage of the first non-positive pivot
   // Streaming layout (rldl_stream.cu): one record per (instance, stage), RS doubles:
-  //   [ q_k (qa) | Xinv_k packed (PX) | Sinv_k packed (PS) | rho_k (bb) | l_k (bb) | u_k (bb) ]
+  //   [ q_k (qa) | Xinv_k packed (PX) | Sinv_k packed (PS) | row classes (kClsWords) | l_k (bb) | u_k (bb) ]
   // packed = lower triangle, column-major, of the a x a / nx x nx symmetric pivot inverse;
   // every part is padded to an even number of doubles (16-byte bulk-copy granularity).
   double *rec;
@@ -81,6 +81,7 @@ struct BatchDev {
   int *sched_slots;
 };
 
+constexpr int kClsWords = 2;  // 64-bit words of 2-bit row classes per stage record (up to 64 rows per stage)
 constexpr int kSchedBuckets = 32;  // priority buckets: floor(2*log2(residual / tolerance)), clamped
 // sched[kSchedUnfinished]: instances of the current solve not yet finished (kept across the launches of
 // one solve: streaming launch, latency-mode launch, adaptive-rho resume rounds); kSchedCounters = array size

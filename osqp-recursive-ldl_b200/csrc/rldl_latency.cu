@@ -272,9 +272,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     const double *recb = B.rec + (size_t)inst * B.rec_stride;
     const double rho_in = __ldcg(B.rho + inst), rho_eq = kRhoEq * rho_in;
     const double inv_in = 1.0 / rho_in, inv_eq = 1.0 / rho_eq, inv_min = 1.0 / kRhoMin;
-    auto rinv_of = [&](double rv) -> double {
-      return rv == rho_in ? inv_in : (rv == rho_eq ? inv_eq : (rv == kRhoMin ? inv_min : 1.0 / rv));
-    };
+    auto rho_of = [&](int c) -> double { return c == 0 ? rho_in : (c == 1 ? rho_eq : kRhoMin); };
+    auto rinv_of = [&](int c) -> double { return c == 0 ? inv_in : (c == 1 ? inv_eq : inv_min); };
     // ---------------- the whole factor of the instance -> shared memory (TMA bulk copies) ----------------
     if (threadIdx.x == 0) mbar_expect_tx(bar_s, (uint32_t)((N + 1) * RS * 8));
     __syncthreads();
@@ -336,7 +335,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
 #pragma unroll
       for (int t = 0; t < NYT; t++) {
         const int rr = gl + G * t;
-        if (rr < np) w[rr] = sl_[SH::RHO + rr] * zp[t] - yp[t];
+        if (rr < np) w[rr] = rho_of(row_class(sl_ + SH::CLS, rr)) * zp[t] - yp[t];
       }
       __syncwarp(gm);
       double tt = 0.0;
@@ -351,7 +350,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       __syncwarp(gm);
       if (!term) {
         if (gl < NX) {
-          const double ri = rinv_of(sl_[SH::RHO + NY + gl]);
+          const double ri = rinv_of(row_class(sl_ + SH::CLS, NY + gl));
           const double tdv = (zd - yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
           td2[gl] = tdv; td2[gl + NX] = tdv;
         }
@@ -474,7 +473,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
           if (rr < np) {
             const int ri = roff + rr;
             const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
-            const double rho = sl_[SH::RHO + rr], rinv = rinv_of(rho), zo = zp[t], yo = yp[t];
+            const int rc = row_class(sl_ + SH::CLS, rr);
+            const double rho = rho_of(rc), rinv = rinv_of(rc), zo = zp[t], yo = yp[t];
             const double zh = alpha * zt + oma * zo;
             const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
@@ -485,7 +485,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         }
         if (!term && gl < NX) {
           const int ri = roff + NY + gl;
-          const double rho = sl_[SH::RHO + NY + gl], rinv = rinv_of(rho);
+          const int rc = row_class(sl_ + SH::CLS, NY + gl);
+          const double rho = rho_of(rc), rinv = rinv_of(rc);
           const double zt = (zd - yd * rinv) + nud * rinv;
           const double zh = alpha * zt + oma * zd;
           const double zn = fmin(fmax(zh + yd * rinv, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);

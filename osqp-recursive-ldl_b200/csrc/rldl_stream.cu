@@ -5,7 +5,7 @@
 // (reference src/osqp.c:354-627) inside one launch.  Per ADMM iteration an instance walks
 // its N+1 stages forward and backward (the block substitution of SURVEY §8a "block form");
 // each stage step needs that stage's record
-//     [ q_k | Xinv_k | Sinv_k | rho_k | l_k | u_k ]
+//     [ q_k | Xinv_k | Sinv_k | row classes | l_k | u_k ]
 // which is immutable during a solve and is streamed HBM -> shared memory by the TMA engine
 // (cp.async.bulk + mbarrier complete_tx, SASS UBLKCP) into a per-group ring, D stage steps
 // ahead of the arithmetic, so the dependent chain of small FP64 mat-vecs only ever touches
@@ -94,12 +94,24 @@ __global__ void k_pack_records(ModelDev M, BatchDev B, int k0, int parts /*bit0 
     }
     o -= B.PS;
     if (!(parts & 2)) continue;
-    const int which = o / B.bb, r = o - which * B.bb;
     const int rows = term ? nt : b;
-    double v = (which == 0) ? 1.0 : 0.0;
+    if (o < kClsWords) {  // 2-bit classes of rows 32*o .. 32*o+31: 0 inequality, 1 equality, 2 loose
+      const double rho_in = B.rho[inst];
+      unsigned long long wv = 0ull;
+      for (int r = 32 * o; r < 32 * o + 32 && r < rows; r++) {
+        const double rv = B.rho_vec[ro + (size_t)k * b + r];
+        const unsigned long long cl = (rv == kRhoMin) ? 2ull : (rv == rho_in ? 0ull : 1ull);
+        wv |= cl << (2 * (r & 31));
+      }
+      *dst = __longlong_as_double((long long)wv);
+      continue;
+    }
+    o -= kClsWords;
+    const int which = o / B.bb, r = o - which * B.bb;
+    double v = 0.0;
     if (r < rows) {
       const size_t ri = ro + (size_t)k * b + r;
-      v = which == 0 ? B.rho_vec[ri] : (which == 1 ? B.l[ri] : B.u[ri]);
+      v = which == 0 ? B.l[ri] : B.u[ri];
     }
     *dst = v;
   }
@@ -260,9 +272,9 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   double rho_in = 0.0, rho_eq = 0.0, inv_in = 0.0, inv_eq = 0.0, inv_min = 0.0;
   MutVec<NYT> cur;
 
-  auto rinv_of = [&](double rv) -> double {  // reciprocal of a rho_vec entry (one of three classes)
-    return rv == rho_in ? inv_in : (rv == rho_eq ? inv_eq : (rv == kRhoMin ? inv_min : 1.0 / rv));
-  };
+  // step size of a row and its reciprocal from the row's class (0 inequality, 1 equality, 2 loose)
+  auto rho_of = [&](int c) -> double { return c == 0 ? rho_in : (c == 1 ? rho_eq : kRhoMin); };
+  auto rinv_of = [&](int c) -> double { return c == 0 ? inv_in : (c == 1 ? inv_eq : inv_min); };
   // leader only: issue the packet at position ipos into ring slot `s`, advance ipos
   auto issue = [&](int s) {
     const bool fwd = ipos <= N;
@@ -417,7 +429,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
 #pragma unroll
         for (int t = 0; t < NYT; t++) {
           const int rr = gl + G * t;
-          if (rr < np) w[rr] = sl_[SH::RHO + rr] * cur.zp[t] - cur.yp[t];
+          if (rr < np) w[rr] = rho_of(row_class(sl_ + SH::CLS, rr)) * cur.zp[t] - cur.yp[t];
         }
         __syncwarp(gm);
         double tt = 0.0;
@@ -437,7 +449,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         __syncwarp(gm);
         if (!term) {
           if (gl < NX) {
-            const double ri = rinv_of(sl_[SH::RHO + NY + gl]);
+            const double ri = rinv_of(row_class(sl_ + SH::CLS, NY + gl));
             const double tdv = (cur.zd - cur.yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
             td2[gl] = tdv; td2[gl + NX] = tdv;
           }
@@ -487,7 +499,8 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           if (rr < np) {
             const int ri = roff + rr;
             const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
-            const double rho = sl_[SH::RHO + rr], rinv = rinv_of(rho), zo = cur.zp[t], yo = cur.yp[t];
+            const int rc = row_class(sl_ + SH::CLS, rr);
+            const double rho = rho_of(rc), rinv = rinv_of(rc), zo = cur.zp[t], yo = cur.yp[t];
             const double zh = alpha * zt + oma * zo;
             const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
@@ -498,7 +511,8 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         }
         if (!term && gl < NX) {
           const int ri = roff + NY + gl;
-          const double rho = sl_[SH::RHO + NY + gl], rinv = rinv_of(rho);
+          const int rc = row_class(sl_ + SH::CLS, NY + gl);
+          const double rho = rho_of(rc), rinv = rinv_of(rc);
           const double zo = cur.zd, yo = cur.yd;
           const double zt = (zo - yo * rinv) + nud * rinv;
           const double zh = alpha * zt + oma * zo;
@@ -648,9 +662,10 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, shm);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
-  // 3 CTAs/SM already saturate HBM (measured 5.1 TB/s algorithmic); a 4th only lengthens every instance's
-  // iteration (bandwidth is shared equally) and with it the critical path of the longest instance
-  int cap = 3;
+  // 3 CTAs/SM nearly saturate the memory system; a 4th adds 2.5 % of bulk throughput but lengthens every
+  // instance's iteration (the machine is shared equally) and with it the chain of the longest instance — a net
+  // loss (1 316 vs 1 273 ms at C5) unless the latency-mode kernel takes the tail over (1 147 vs 1 174 ms)
+  int cap = park_below > 0 ? 4 : 3;
   if (const char *e = getenv("RLDL_CTAS_PER_SM")) cap = atoi(e) > 0 ? atoi(e) : cap;
   if (per_sm > cap) per_sm = cap;
   long long grid = (long long)sms * per_sm;

@@ -39,6 +39,14 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 
 
 __host__ __device__ inline int even_up(int v) { return (v + 1) & ~1; }
+// The per-row step size of an instance takes one of three values (constraint typing, reference
+// src/auxil.c:79-101): rho (inequality), 1e3*rho (equality), 1e-6 (loose).  The stage records carry the
+// class of every row in 2 bits (kClsWords 64-bit words per stage) instead of the value: 26 fewer doubles
+// per stage and sweep direction at the C5 shape.
+__device__ __forceinline__ int row_class(const double *cls, int row) {
+  const unsigned long long wv = reinterpret_cast<const unsigned long long *>(cls)[row >> 5];
+  return (int)((wv >> (2 * (row & 31))) & 3ull);
+}
 // doubles of the diagonal-packed form of a symmetric n x n matrix
 __host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
 
@@ -56,9 +64,11 @@ struct Shape {
   static constexpr int ROWS = NYT * G;
   static constexpr int QA = (A + 1) & ~1, PX = ((A / 2 + 1) * A + 1) & ~1, PS = ((NX / 2 + 1) * NX + 1) & ~1,
                        BB = (B + 1) & ~1;
-  static constexpr int RS = QA + PX + PS + 3 * BB;
-  static constexpr int XOFF = QA, SOFF = QA + PX, RHO = QA + PX + PS, LO = RHO + BB, UP = LO + BB;
-  static constexpr uint32_t FWD_BYTES = 8u * (QA + PX + PS + BB), BWD_BYTES = 8u * (PX + PS + 3 * BB);
+  // stage record: [ q | Xinv (diagonal-packed) | Sinv (diagonal-packed) | row classes (2 bits per row) | l | u ]
+  static_assert(B <= 32 * kClsWords, "row classes of a stage must fit the class words of the record");
+  static constexpr int RS = QA + PX + PS + kClsWords + 2 * BB;
+  static constexpr int XOFF = QA, SOFF = QA + PX, CLS = QA + PX + PS, LO = CLS + kClsWords, UP = LO + BB;
+  static constexpr uint32_t FWD_BYTES = 8u * (QA + PX + PS + kClsWords), BWD_BYTES = 8u * (PX + PS + kClsWords + 2 * BB);
   // per-group scratch (doubles, every block even-sized)
   static constexpr int AE = (A + 1) & ~1, NXE = (NX + 1) & ~1;
   // the vectors of the forward sweep (w, tv2, yv, td2, sp) and of the backward sweep (vn2, vc, nud, gg2)
