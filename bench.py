@@ -296,14 +296,14 @@ def main_b200(args):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = iter_sum * admm_bytes / (s_ms * 1e-3) / 1e9
     # DRAM traffic of the same kernel from the committed ncu --set full capture
-    # (profiles/r01_stream_v4_ncu_full_c5_batch16384.txt: dram read 1.508 TB + write 0.217 TB for
-    # 1.595 TB algorithmic at batch 16384), scaled by the algorithmic bytes of this launch
-    traffic_ratio = (1.508469e12 + 217.423811e9) / 1595449656000.0
-    roof = {"bound": "hbm", "kernel": "k_admm_stream (fused KKT solve + ADMM step + termination, whole solve loop)",
+    # (profiles/r01_stream_v5_ncu_full_uniform_c5_batch16384.txt: dram read 432.75 GB + write 66.61 GB for
+    # 1.6384 M instance-iterations x 275 040 algorithmic bytes), scaled by the algorithmic bytes of this launch
+    traffic_ratio = (432.746847e9 + 66.611270e9) / (16384 * 100 * 275040.0)
+    roof = {"bound": "hbm", "kernel": "k_admm_stream (fused KKT solve + ADMM step + termination, whole solve loop; its tail is finished by k_admm_cta inside the same timed region)",
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
             "traffic": traffic_ratio * iter_sum * admm_bytes,
-            "traffic_source": "ncu dram__bytes_read+write of this kernel at batch 16384 (x%.3f of algorithmic), scaled" % traffic_ratio,
+            "traffic_source": "ncu dram__bytes_read+write of this kernel at batch 16384, uniform 100 iterations (x%.3f of algorithmic), scaled" % traffic_ratio,
             "launch_ms": s_ms, "algorithmic_bytes_per_launch": iter_sum * admm_bytes,
             "factor_kernel": {"kernel": "k_factor_stream (stage recursion, FP64-latency bound: ~10 flop/B)",
                               "launch_ms": f_ms, "achieved": factor_bytes / (f_ms * 1e-3) / 1e9,
