@@ -399,6 +399,12 @@ class OracleBatch:
             s.update_bounds(self.l[k], self.u[k])
         return 0
 
+    def partial_update_bounds(self, start, stop, l, u):
+        """osqp_partial_update_bounds (src/recursive_ldl.c:119): rows [start, stop) only."""
+        ln, un = self.l.copy(), self.u.copy()
+        ln[:, start:stop], un[:, start:stop] = l, u
+        return self.update_bounds(ln, un)
+
     def update_lin_cost(self, q):
         self.q = np.array(q, float)
         for k, s in enumerate(self.sv):

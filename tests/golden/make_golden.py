@@ -70,6 +70,45 @@ def infeasible():
     save("infeasible_C1", batch=4, seed=1234, status=r["status"], iter=r["iter"], obj=r["obj"])
 
 
+def updates(name, batch):
+    """Vector-update entry points between solves (osqp_update_lin_cost, osqp_partial_update_bounds,
+    osqp_warm_start, osqp_warm_start_x, osqp_update_lower/upper_bound through update_bounds) on the
+    recursive path, and osqp_update_rho on the stock path (the recursive path segfaults there, F1)."""
+    cfg = mpc.CONFIGS[name]
+    mdl, N = mpc.make_model(cfg), cfg["N"]
+    x0 = mpc.sample_x0(mdl, batch, 99)
+    q, l, u = mdl.vectors(x0, N, N + 1)
+    rng = np.random.default_rng(5)
+    n, m = N * (mdl.nx + mdl.nu), l.shape[1]
+    q2 = q.copy(); q2[:, :n] += 0.05 * rng.standard_normal((batch, n))
+    x0b = mpc.sample_x0(mdl, batch, 100)
+    _, l2, u2 = mdl.vectors(x0b, N, N + 1)
+    s, e = mdl.ny, mdl.ny + mdl.nx                    # the stage-0 dynamics rows carry x0
+    xw = 0.1 * rng.standard_normal((batch, q.shape[1])); yw = 0.1 * rng.standard_normal((batch, l.shape[1]))
+    lt, ut = l2.copy(), u2.copy()
+    tight = slice(0, mdl.ny)                          # tighten the stage-0 path rows
+    lt[:, tight] *= 0.5; ut[:, tight] *= 0.5
+    ops = [("solve",), ("get",),
+           ("update_lin_cost", q2), ("partial_update_bounds", s, e, l2[:, s:e].copy(), u2[:, s:e].copy()),
+           ("solve",), ("get",),
+           ("warm_start", xw, yw), ("solve",), ("get",),
+           ("update_bounds", lt, ut), ("warm_start", xw, None), ("solve",), ("get",), ("dims",)]
+    res = ref_run(mdl, N, N + 1, q, l, u, ops, warm_start=1)
+    n, m = res[-2]
+    kw = dict(batch=batch, seed=99, n=n, m=m, q2=q2, l2=l2, u2=u2, s=s, e=e, xw=xw, yw=yw, lt=lt, ut=ut)
+    for t, i in enumerate((1, 5, 8, 12)):
+        for key in ("status", "iter", "obj"):
+            kw[f"{key}_{t}"] = res[i][key]
+        kw[f"x_{t}"], kw[f"y_{t}"] = res[i]["x"][:, :n], res[i]["y"][:, :m]
+    # stock path: per-instance osqp_update_rho between two cold solves
+    rho2 = np.where(np.arange(batch) % 2 == 0, 0.02, 1.5)
+    rr = ref_run(mdl, N, N, q[:, :n], l[:, :m], u[:, :m], [("solve",), ("update_rho", rho2), ("solve",), ("get",)],
+                 path="stock", warm_start=0)[3]
+    kw.update(rho2=rho2, status_rho=rr["status"], iter_rho=rr["iter"], obj_rho=rr["obj"],
+              x_rho=rr["x"][:, :n], y_rho=rr["y"][:, :m])
+    save(f"updates_{name}", **kw)
+
+
 if __name__ == "__main__":
     cold("C1", 16)
     cold("C3", 6)
@@ -78,3 +117,4 @@ if __name__ == "__main__":
     receding("C1", 6, 7, 2)
     receding("C3", 3, 6, 2)
     infeasible()
+    updates("C1", 6)

@@ -72,6 +72,20 @@ def test_oracle_receding_horizon_matches_golden():
         assert rel_err(s["x"], g[f"x_{t}"]) < REL_TOL and rel_err(s["y"], g[f"y_{t}"]) < REL_TOL
 
 
+def test_oracle_update_entry_points_match_golden():
+    """update_lin_cost / partial_update_bounds / warm_start(x, y) / update_bounds + warm_start_x between
+    warm-started solves, and per-instance update_rho on the dense path (fixture: make_golden.updates)."""
+    import updates_script as US
+    g = gold("updates_C1")
+    mdl, N, q, l, u = US.inputs(g)
+    take = 3
+    US.replay(O.OracleBatch(mdl, N, N + 1, q[:take], l[:take], u[:take], settings_dict(warm_start=1)), g, take)
+    n, m = int(g["n"]), int(g["m"])
+    ob = O.OracleBatch(mdl, N, N, q[:take, :n], l[:take, :m], u[:take, :m], settings_dict(), path="stock")
+    ob.solve(); ob.update_rho(g["rho2"][:take]); ob.solve()
+    US.check(ob.get(), g, "rho", n, m, take)
+
+
 def test_oracle_primal_infeasible_matches_golden():
     g = gold("infeasible_C1")
     mdl, N, x0, q, l, u = problem("C1", 4)
