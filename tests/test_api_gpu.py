@@ -140,9 +140,10 @@ def test_scalar_update_entry_points_match_golden():
     assert not compare(ws.out(), gb.get(), n, m)
     gb.free()
     # one-sided updates that cross the other bound are refused and leave the problem untouched (osqp.c:835-925)
-    bad = lt.copy(); bad[0] = ut[0] + 1.0
+    r = int(np.flatnonzero((np.abs(lt[:m]) < 1e20) & (np.abs(ut[:m]) < 1e20))[0])
+    bad = lt.copy(); bad[r] = ut[r] + 1.0
     assert L.osqp_update_lower_bound(w, bad.ctypes.data) == 1
-    bad = ut.copy(); bad[0] = lt[0] - 1.0
+    bad = ut.copy(); bad[r] = lt[r] - 1.0
     assert L.osqp_update_upper_bound(w, bad.ctypes.data) == 1
     assert ws.solve() == 0 and ws.info.status_val == 1
     ws.free()
@@ -184,9 +185,10 @@ def test_update_P_A_on_recursive_workspace_matches_fresh_setup():
     fresh = Scalar(m1, N, Nmax, q[0], l[0], u[0], gpu_settings())
     assert fresh.solve() == 0
     assert not compare(a.out(), fresh.out(), n, m)
-    # (3) too many values: refused (osqp.c:1033, 1111)
-    assert L.osqp_update_P(a.w, Px1.ctypes.data, None, len(Px1) + 1) == 1
-    assert L.osqp_update_A(a.w, Ax1.ctypes.data, None, len(Ax1) + 1) == 1
+    # (3) an index list longer than the matrix: refused (osqp.c:1020-1031, 1098-1109)
+    longP, longA = np.zeros(len(Px1) + 1, np.int64), np.zeros(len(Ax1) + 1, np.int64)
+    assert L.osqp_update_P(a.w, np.zeros(len(longP)).ctypes.data, longP.ctypes.data, len(longP)) == 1
+    assert L.osqp_update_A(a.w, np.zeros(len(longA)).ctypes.data, longA.ctypes.data, len(longA)) == 1
     # (4) one entry of one interior stage changed: the stages no longer share blocks -> refused
     one = np.array([Ax1[len(Ax1) // 2] + 0.25]); at = np.array([len(Ax1) // 2], np.int64)
     assert L.osqp_update_A(a.w, one.ctypes.data, at.ctypes.data, 1) == 1
