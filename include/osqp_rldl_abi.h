@@ -403,7 +403,8 @@ void  rldl_batch_last_times(const RLDLBatch *b, double *factor_ms, double *solve
 void  rldl_batch_counters(const RLDLBatch *b, double *admm_bytes, double *factor_bytes, c_int *launches);
 /* ADMM kernel selection: 0 = automatic (the TMA-streaming kernel when the stage shapes allow
  * it, nx+nu <= 32, and adaptive_rho is off), 1 = always the generic runtime-shape kernel.
- * Both compute the same iteration; the switch exists for cross-checking and profiling. */
+ * Both compute the same iteration; the switch exists for cross-checking and profiling.
+ * which = 2 changes nothing and returns 0 iff the handle's stage shape has specialised kernels. */
 c_int rldl_batch_select_kernel(RLDLBatch *b, c_int which);
 /* the CUDA stream (cudaStream_t) every launch and copy of this handle is issued on, so a
  * caller can bracket calls with its own events on the launching stream */

@@ -762,6 +762,7 @@ void rldl_batch_counters(const RLDLBatch *h, double *admm_bytes, double *factor_
 }
 c_int rldl_batch_select_kernel(RLDLBatch *h, c_int which) {
   HB(h);
+  if (which == 2) return h->b->streaming ? 0 : 1;  // query: is this shape in the specialisation table?
   if (which < 0 || which > 1) return 1;
   h->b->kernel_choice = (int)which;
   return 0;

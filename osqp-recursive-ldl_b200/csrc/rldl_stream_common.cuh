@@ -130,11 +130,19 @@ struct MutVec {  // the mutable per-stage values a lane owns (iterates and forwa
 };
 
 
-// The specialisation table: (nx+nu, nx, ny, nt, ELL width of C) of the BASELINE.json shapes.
+// The specialisation table: (nx+nu, nx, ny, nt, ELL width of C).  First the BASELINE.json shapes, then
+// other box-constrained MPC shapes (nx,nu) = (2,1) (4,1) (6,2) (6,3) (8,4) (16,4): odd and even block sizes
+// in every lane-group width.  Any other shape runs on the runtime-shape kernels of rldl_kernels.cu.
 #define RLDL_SHAPES(X) \
   X(6, 4, 6, 4, 1)     \
   X(16, 12, 16, 12, 1) \
-  X(11, 8, 11, 8, 1)
+  X(11, 8, 11, 8, 1)   \
+  X(3, 2, 3, 2, 1)     \
+  X(5, 4, 5, 4, 1)     \
+  X(8, 6, 8, 6, 1)     \
+  X(9, 6, 9, 6, 1)     \
+  X(12, 8, 12, 8, 1)   \
+  X(20, 16, 20, 16, 1)
 
 inline int max_c_width(const ModelDev &M) {
   int wdt = 0;

@@ -132,3 +132,31 @@ def test_latency_mode_kernel_matches_streaming_kernel(name, batch, mode, monkeyp
         gb.free()
     bad = compare(outs[1], outs[0], n, m)
     assert not bad, bad[:5]
+
+
+@pytest.mark.parametrize("nx,nu", [(2, 1), (4, 1), (6, 2), (6, 3), (8, 4), (16, 4)])
+def test_other_specialised_shapes_match_reference(nx, nu, monkeypatch):
+    """The shape table of rldl_stream_common.cuh beyond the BASELINE shapes (odd and even block sizes in each
+    lane-group width): the recursion kernel (one KKT solve), the streaming kernel alone and the latency-mode
+    kernel alone, each against the unmodified reference."""
+    from rldl_b200 import mpc
+    N, batch = 9, 24
+    mdl = mpc.random_model(nx, nu, seed=100 + nx * 10 + nu)
+    x0 = mpc.sample_x0(mdl, batch, 77)
+    q, l, u = mdl.vectors(x0, N, N + 1)
+    rng = np.random.default_rng(3)
+    res = ref_run(mdl, N, N + 1, q, l, u, [("solve",), ("get",), ("dims",)])
+    ref, (n, m) = res[1], res[2]
+    rhs = rng.standard_normal((batch, n + m))
+    kk = ref_run(mdl, N, N + 1, q, l, u, [("kkt_solve", k, rhs[k]) for k in range(3)])
+    for below in ("0", "100000"):
+        monkeypatch.setenv("RLDL_LAT_BELOW", below)
+        gb = R.Batch(mdl, N, N + 1, q, l, u, gpu_settings())
+        assert gb.select_kernel(2) == 0          # the shape-specialised kernels serve this shape
+        got = gb.kkt_solve(rhs)
+        for k in range(3):
+            assert rel_err(got[k], kk[k]) < 1e-9, (nx, nu, k)
+        assert gb.solve() == 0
+        bad = compare(gb.get(), ref, n, m)
+        assert not bad, (nx, nu, below, bad[:5])
+        gb.free()
