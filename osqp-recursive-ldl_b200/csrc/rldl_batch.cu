@@ -67,6 +67,15 @@ struct ModelBuilder {
   }
 };
 
+template <class T>
+static cudaError_t dalloc(T **p, size_t count) {
+  *p = nullptr;
+  if (!count) count = 1;
+  cudaError_t e = cudaMalloc((void **)p, count * sizeof(T));
+  if (e == cudaSuccess) e = cudaMemset(*p, 0, count * sizeof(T));
+  return e;
+}
+
 static bool check_dims(const csc *M, c_int m, c_int n) { return M && M->m == m && M->n == n && M->p; }
 
 c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc *A0, const csc *Ai,
@@ -75,6 +84,7 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
   ModelDev &Md = M;
   Md.nx = nx; Md.nu = nu; Md.ny = ny; Md.nt = nt; Md.a = a; Md.b = b;
   memset(Md.sc, 0, sizeof(Md.sc));
+  Md.bd = 0;
   if (!generic) {
     if (!check_dims(Q0, nu, nu) || !check_dims(Qi, a, a) || !check_dims(QN, nx, nx) ||
         !check_dims(A0, b, nu) || !check_dims(Ai, b, a) || !check_dims(AN, nt, nx) ||
@@ -112,6 +122,10 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
     {
       std::vector<double> Q = csc_dense(Qi, a, a, true), A = csc_dense(Ai, b, a, false);
       std::vector<double> C(A.begin(), A.begin() + (size_t)ny * a), F(A.begin() + (size_t)ny * a, A.end());
+      Md.bd = 1;  // state-input cross terms of the cost? (stage 0 and the terminal stage have none by construction)
+      for (int i = 0; i < nx; i++)
+        for (int j = nx; j < a; j++)
+          if (Q[(size_t)i * a + j] != 0.0 || Q[(size_t)j * a + i] != 0.0) Md.bd = 0;
       StageClass &s = Md.sc[1];
       s.Q = mb.add_dense(Q);
       s.C = mb.add_ell(C, ny, a, false); s.Ct = mb.add_ell(C, ny, a, true);
@@ -137,6 +151,33 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
   CK(cudaMemcpy(d_mval, mb.val.data(), mb.val.size() * sizeof(double), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(d_midx, mb.idx.data(), mb.idx.size() * sizeof(int), cudaMemcpyHostToDevice));
   Md.val = d_mval; Md.idx = d_midx; Md.nval = (int)mb.val.size();
+  if (D.rec) return configure_stream();  // a P / A update may change which specialisation serves the model
+  return 0;
+}
+
+// Which kernels serve the model, and the stage-record layout that goes with them.
+c_int Batch::configure_stream() {
+  streaming = !generic && stream_supported(M, N);
+  stream_record_dims(M, &D.qa, &D.PX, &D.PS, &D.bb, &D.bd, &D.PXX);
+  D.RS = D.qa + D.PX + D.PS + kClsWords + 2 * D.bb;
+  D.rec_stride = (long long)(Nmax + 1) * D.RS;
+  const size_t bs = (size_t)batch;
+  const size_t want = streaming ? bs * (size_t)D.rec_stride : 1;
+  if (want > rec_cap) {
+    if (D.rec) cudaFree(D.rec);
+    D.rec = nullptr; rec_cap = 0;
+    CK(dalloc(&D.rec, want));
+    rec_cap = want;
+  }
+  if (streaming && !slots_full) {
+    if (D.sched_slots) cudaFree(D.sched_slots);
+    D.sched_slots = nullptr;
+    CK(dalloc(&D.sched_slots, (size_t)kSchedBuckets * bs));
+    slots_full = true;
+  } else if (!D.sched_slots) {
+    CK(dalloc(&D.sched_slots, 1));
+  }
+  unpacked_valid = false;
   return 0;
 }
 
@@ -197,15 +238,6 @@ void Batch::push_settings() {
 }
 
 // ------------------------------ lifetime ------------------------------
-template <class T>
-static cudaError_t dalloc(T **p, size_t count) {
-  *p = nullptr;
-  if (!count) count = 1;
-  cudaError_t e = cudaMalloc((void **)p, count * sizeof(T));
-  if (e == cudaSuccess) e = cudaMemset(*p, 0, count * sizeof(T));
-  return e;
-}
-
 c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, const csc *A0,
                     const csc *Ai, const csc *Aij, const csc *AN, const OSQPSettings *st, c_int Nmax,
                     c_int N, c_int nx, c_int nu, c_int ny, c_int nt, c_int batch, const c_float *q,
@@ -258,15 +290,9 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(dalloc(&D.obj, bs)); CK(dalloc(&D.pri, bs)); CK(dalloc(&D.dua, bs)); CK(dalloc(&D.rho_est, bs));
   CK(dalloc(&D.rho_updates, bs)); CK(dalloc(&D.fact_flag, bs));
   CK(dalloc(&B->d_changed, bs));
-  B->streaming = !generic && stream_supported(B->M, B->N);
-  {
-    stream_record_dims(B->a, B->nx, B->b, &D.qa, &D.PX, &D.PS, &D.bb);
-    D.RS = D.qa + D.PX + D.PS + kClsWords + 2 * D.bb;
-    D.rec_stride = (long long)(B->Nmax + 1) * D.RS;
-    CK(dalloc(&D.rec, B->streaming ? bs * (size_t)D.rec_stride : 1));
-    CK(dalloc(&D.sched, kSchedCounters));
-    CK(dalloc(&D.sched_slots, B->streaming ? (size_t)kSchedBuckets * bs : 1));
-  }
+  CK(dalloc(&D.sched, kSchedCounters));
+  rc = B->configure_stream();
+  if (rc) { delete B; return rc; }
   CK(cudaStreamCreateWithFlags(&B->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&B->ev0)); CK(cudaEventCreate(&B->ev1));
   B->set_sizes();

@@ -43,6 +43,9 @@ struct Batch {
                       const c_float *l, const c_float *u, const c_float *rho, bool generic);
   ~Batch();
 
+  c_int configure_stream();
+  size_t rec_cap = 0;       // doubles allocated for D.rec
+  bool slots_full = false;  // D.sched_slots sized for the scheduler
   c_int upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc *A0, const csc *Ai,
                      const csc *Aij, const csc *AN);
   void push_settings();

@@ -41,6 +41,7 @@ struct ModelDev {
   const double *val;
   const int *idx;
   int nval;  // entries in val[] / idx[] (the ELL part is copied to shared memory by the streaming kernels)
+  int bd;    // 1: no state-input cross terms in the cost and one-variable path rows => block-diagonal pivots
 };
 
 struct SettingsDev {
@@ -70,8 +71,10 @@ struct BatchDev {
   //   [ q_k (qa) | Xinv_k packed (PX) | Sinv_k packed (PS) | row classes (kClsWords) | l_k (bb) | u_k (bb) ]
   // packed = lower triangle, column-major, of the a x a / nx x nx symmetric pivot inverse;
   // every part is padded to an even number of doubles (16-byte bulk-copy granularity).
+  // bd = 1 (block-diagonal pivots): the Xinv part holds the nx x nx block (PXX doubles) and then the nu x nu block.
   double *rec;
   int qa, PX, PS, bb, RS;
+  int bd, PXX;
   long long rec_stride;    // (Nmax+1)*RS doubles per instance
   // Device work scheduler of the persistent ADMM kernel (rldl_stream.cu):
   //   sched[0] fresh-instance counter, sched[1] instances parked for a rho refactorisation,

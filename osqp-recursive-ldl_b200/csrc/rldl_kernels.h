@@ -22,7 +22,7 @@ cudaError_t launch_scatter_rows(double *dst, int ld, const double *src, int len,
                                 cudaStream_t st);
 // streaming path (rldl_stream.cu)
 bool stream_supported(const ModelDev &M, int N);
-void stream_record_dims(int a, int nx, int b, int *qa, int *PX, int *PS, int *bb);
+void stream_record_dims(const ModelDev &M, int *qa, int *PX, int *PS, int *bb, int *bd, int *PXX);
 cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,
                                 cudaStream_t st);
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,

@@ -163,11 +163,9 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     tphase ^= 1u << s;
   };
 
-  int wrapX[SH::WNX], wrapS[SH::WNS];
-#pragma unroll
-  for (int d = 1; d <= A - 1 - A / 2; d++) wrapX[d - 1] = d * A + ((gl < A ? gl : 0) - d + A) % A;
-#pragma unroll
-  for (int d = 1; d <= NX - 1 - NX / 2; d++) wrapS[d - 1] = d * NX + ((gl < NX ? gl : 0) - d + NX) % NX;
+  Wraps<SH> wr;
+  wr.init(gl);
+  const int (&wrapS)[SH::WNS] = wr.S;
 
   const double sigma = S.sigma, alpha = S.alpha, oma = 1.0 - S.alpha;
   // T_k for phase B (TB[k][i*TS + j] = T_k(i,j)) and phase D (TD[k][i*TS + j] = T_k(j,i)) in global memory
@@ -299,11 +297,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       const double *sl_ = recs + k * RS;
       const double *Fk = Fd + (k == 0 ? 0 : A * NX);
       for (int j = 0; j < NX; j++) {
-        if (gl < A) {  // column j of Xinv_k from the diagonal-packed block
-          int d = j - gl;
-          if (d < 0) d += A;
-          yvs[gl] = (d <= A / 2) ? sl_[SH::XOFF + d * A + gl] : sl_[SH::XOFF + (A - d) * A + j];
-        }
+        if (gl < A) yvs[gl] = xinv_state_col<SH>(sl_, gl, j);  // column j of Xinv_k
         __syncwarp(gm);
         if (gl < NX) {
           const double wv = dense_mv<A, NX>(Fk + gl, yvs);
@@ -340,10 +334,10 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       __syncwarp(gm);
       double tt = 0.0;
       if (gl < dim) tt = g + ell_row<CW>(Ctv + cls * AE * CW, Cti + cls * AE * CW, gl, w);
-      if (gl < A) { tv2[gl] = tt; tv2[gl + A] = tt; }
+      if (gl < A) v2_store<SH>(tv2, gl, tt);
       __syncwarp(gm);
       if (gl < A) {
-        const double av = dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, tv2 + gl, wrapX);
+        const double av = xinv_mv<SH>(sl_, gl, tv2, wr);
         va[k * AE + gl] = av;
         yvs[gl] = av;
       }
@@ -408,11 +402,11 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
             double gg = 0.0;
             if (!term) gg = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, vc + k * NXE);
             if (k > 0 && gl < NX) gg -= vc[(k - 1) * NXE + gl];
-            gg2[gl] = gg; gg2[gl + A] = gg;
+            v2_store<SH>(gg2, gl, gg);
           }
           __syncwarp(gm);
           if (gl < A) {
-            const double e = va[k * AE + gl] + dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
+            const double e = va[k * AE + gl] + xinv_mv<SH>(sl_, gl, gg2, wr);
             va[k * AE + gl] = e;
             if (gl < NX) vd[k * NXE + gl] = e;
           }
@@ -460,10 +454,10 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
           __syncwarp(gm);
           if (gl < A) {
             const double ggv = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, nudv);
-            gg2[gl] = ggv; gg2[gl + A] = ggv;
+            v2_store<SH>(gg2, gl, ggv);
           }
           __syncwarp(gm);
-          if (gl < A) vv = va[k * AE + gl] + dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
+          if (gl < A) vv = va[k * AE + gl] + xinv_mv<SH>(sl_, gl, gg2, wr);
         }
         if (gl < A) vcur[gl] = vv;
         __syncwarp(gm);
@@ -738,8 +732,8 @@ static cudaError_t launch_latency_t(const ModelDev &M, const BatchDev &B, const 
 
 size_t latency_smem_bytes(const ModelDev &M, int N) {
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_) \
-  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_) return latency_smem_t<Shape<a_, nx_, ny_, nt_, cw_>>(N);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_) \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_)) return latency_smem_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(N);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return (size_t)-1;
@@ -748,9 +742,9 @@ size_t latency_smem_bytes(const ModelDev &M, int N) {
 cudaError_t launch_admm_latency(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                                 int resume, double *Tg, int ctas, int reset_parked, cudaStream_t st) {
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_)                                          \
-  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_)      \
-    return launch_latency_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, S, warm_start, resume, Tg, ctas, reset_parked, st);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                    \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))         \
+    return launch_latency_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, Tg, ctas, reset_parked, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;

@@ -67,10 +67,32 @@ __global__ void k_pack_records(ModelDev M, BatchDev B, int k0, int parts /*bit0 
     if (o < B.PX) {  // Xinv_k, a x a diagonal-packed (terminal: [Xinv_N 0; 0 I])
       if (!(parts & 1)) continue;
       double v = 0.0;
-      if (o < dp_size(a)) {
-        const int d = o / a, i = o - d * a;
-        int j = i + d;
-        if (j >= a) j -= a;
+      int i = -1, j = -1;  // the entry of the a x a block this element holds
+      if (!B.bd) {
+        if (o < dp_size(a)) {
+          const int d = o / a;
+          i = o - d * a;
+          j = i + d;
+          if (j >= a) j -= a;
+        }
+      } else if (o < B.PXX) {  // block-diagonal pivots: the nx x nx block, then the nu x nu block
+        if (o < dp_size(nx)) {
+          const int d = o / nx;
+          i = o - d * nx;
+          j = i + d;
+          if (j >= nx) j -= nx;
+        }
+      } else {
+        const int nu = a - nx, ou = o - B.PXX;
+        if (ou < dp_size(nu)) {
+          const int d = ou / nu;
+          i = ou - d * nu;
+          j = i + d;
+          if (j >= nu) j -= nu;
+          i += nx; j += nx;
+        }
+      }
+      if (i >= 0) {
         const double *Xk = B.Xinv + (size_t)inst * B.xstride + (size_t)k * a * a;
         if (!term) v = (i >= j) ? Xk[j * a + i] : Xk[i * a + j];  // lower triangle of the stored inverse
         else v = (i < nx && j < nx) ? ((i >= j) ? Xk[j * nx + i] : Xk[i * nx + j]) : (i == j ? 1.0 : 0.0);
@@ -127,11 +149,22 @@ cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, in
   return cudaGetLastError();
 }
 
-void stream_record_dims(int a, int nx, int b, int *qa, int *PX, int *PS, int *bb) {
-  *qa = even_up(a);
-  *PX = even_up(dp_size(a));
-  *PS = even_up(dp_size(nx));
-  *bb = even_up(b);
+// Record layout of the specialisation that serves M (the first table entry that does; the full a x a layout
+// when none does and the records are unused).
+void stream_record_dims(const ModelDev &M, int *qa, int *PX, int *PS, int *bb, int *bd, int *PXX) {
+  const int cw = max_c_width(M);
+  int use_bd = 0;
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_) \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_)) { use_bd = bd_; goto found; }
+  RLDL_SHAPES(RLDL_X)
+#undef RLDL_X
+found:
+  *bd = use_bd;
+  *qa = even_up(M.a);
+  *PXX = even_up(dp_size(M.nx));
+  *PX = use_bd ? *PXX + even_up(dp_size(M.a - M.nx)) : even_up(dp_size(M.a));
+  *PS = even_up(dp_size(M.nx));
+  *bb = even_up(M.b);
 }
 
 // ---------------------------------------------------------------------------
@@ -251,11 +284,9 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
 
   // lane constants of the diagonal-packed mat-vecs
-  int wrapX[SH::WNX], wrapS[SH::WNS];
-#pragma unroll
-  for (int d = 1; d <= A - 1 - A / 2; d++) wrapX[d - 1] = d * A + ((gl < A ? gl : 0) - d + A) % A;
-#pragma unroll
-  for (int d = 1; d <= NX - 1 - NX / 2; d++) wrapS[d - 1] = d * NX + ((gl < NX ? gl : 0) - d + NX) % NX;
+  Wraps<SH> wr;
+  wr.init(gl);
+  const int (&wrapS)[SH::WNS] = wr.S;
 
   const int npos = 2 * (N + 1);
   const double sigma = S.sigma, alpha = S.alpha, oma = 1.0 - S.alpha;
@@ -437,11 +468,11 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           tt = g + ell_row<CW>(Ctv + cls * SH::AE * CW, Cti + cls * SH::AE * CW, gl, w);
           if (k > 0 && gl < NX) tt -= sp[gl];
         }
-        if (gl < A) { tv2[gl] = tt; tv2[gl + A] = tt; }
+        if (gl < A) v2_store<SH>(tv2, gl, tt);
         __syncwarp(gm);
         double yvv = 0.0;
         if (gl < A) {
-          yvv = dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, tv2 + gl, wrapX);
+          yvv = xinv_mv<SH>(sl_, gl, tv2, wr);
           yvs[gl] = yvv;
           if (gl < dim) ykg[k * A + gl] = yvv;
         }
@@ -484,10 +515,10 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           __syncwarp(gm);
           if (gl < A) {
             const double ggv = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, nudv);
-            gg2[gl] = ggv; gg2[gl + A] = ggv;
+            v2_store<SH>(gg2, gl, ggv);
           }
           __syncwarp(gm);
-          if (gl < A) vv = cur.yk - dmv<A, SH::WNX>(sl_ + SH::XOFF, sl_ + SH::XOFF + gl, gg2 + gl, wrapX);
+          if (gl < A) vv = cur.yk - xinv_mv<SH>(sl_, gl, gg2, wr);
         }
         if (gl < A) vcur[gl] = vv;
         if (gl < NX) { vn2[gl] = vv; vn2[gl + NX] = vv; }
@@ -819,7 +850,25 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
         for (int j = 0; j < A; j++) tb[j * A + gl] = Xr[j];  // symmetric: column-major == row-major
       }
       __syncwarp(gm);
-      if (gl < A) {
+      if constexpr (SH::BD) {  // the nx x nx block, then the nu x nu block (the cross blocks are exactly zero)
+        constexpr int NU = SH::NU;
+        if (gl < NX) {
+#pragma unroll
+          for (int d = 0; d <= NX / 2; d++) {
+            int j = gl + d;
+            if (j >= NX) j -= NX;
+            rk[SH::XOFF + d * NX + gl] = tb[j * A + gl];
+          }
+        } else if (gl < A) {
+          const int i = gl - NX;
+#pragma unroll
+          for (int d = 0; d <= NU / 2; d++) {
+            int j = i + d;
+            if (j >= NU) j -= NU;
+            rk[SH::UOFF + d * NU + i] = tb[(NX + j) * A + gl];
+          }
+        }
+      } else if (gl < A) {
 #pragma unroll
         for (int d = 0; d <= A / 2; d++) {
           int j = gl + d;
@@ -923,8 +972,8 @@ static cudaError_t launch_factor_stream_t(const ModelDev &M, const BatchDev &B, 
 bool stream_supported(const ModelDev &M, int N) {
   if (N < 1) return false;
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_) \
-  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_) return true;
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_) \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_)) return true;
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return false;
@@ -933,9 +982,9 @@ bool stream_supported(const ModelDev &M, int N) {
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                                int resume, int park_below, cudaStream_t st) {
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_)                                          \
-  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_)      \
-    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, S, warm_start, resume, park_below, st);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                                          \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))      \
+    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, park_below, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;
@@ -944,9 +993,9 @@ cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const Setti
 cudaError_t launch_factor_stream(const ModelDev &M, const BatchDev &B, double sigma, int k0,
                                  const int *only_flagged, int write_unpacked, cudaStream_t st) {
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_)                                          \
-  if (M.a == a_ && M.nx == nx_ && M.ny == ny_ && M.nt == nt_ && cw <= cw_)      \
-    return launch_factor_stream_t<Shape<a_, nx_, ny_, nt_, cw_>>(M, B, sigma, k0, only_flagged, write_unpacked, st);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                                          \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))      \
+    return launch_factor_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, sigma, k0, only_flagged, write_unpacked, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;

@@ -53,21 +53,29 @@ __host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
 // ---------------------------------------------------------------------------
 // Compile-time shape of one specialisation
 // ---------------------------------------------------------------------------
-template <int A_, int NX_, int NY_, int NT_, int CW_>
+// BD = 1: the cost has no state-input cross terms (and the path rows touch one variable each, CW = 1), so every
+// pivot block X_k = Q_k + sigma I + C' rho C + [Sinv_{k-1} 0; 0 0] is block diagonal, and so is its inverse: the
+// record then carries the nx x nx and the nu x nu diagonal block instead of the a x a block (C5: 96 instead of
+// 144 doubles per stage and sweep direction).
+template <int A_, int NX_, int NY_, int NT_, int CW_, int BD_ = 0>
 struct Shape {
-  static constexpr int A = A_, NX = NX_, NY = NY_, NT = NT_, CW = CW_;
+  static constexpr int A = A_, NX = NX_, NY = NY_, NT = NT_, CW = CW_, BD = BD_;
+  static constexpr int NU = A - NX;
   static constexpr int B = NX + NY;
   static constexpr int G = A <= 8 ? 8 : (A <= 16 ? 16 : 32);
   static constexpr int GPW = 32 / G;
   static constexpr int RMAX = NY > NT ? NY : NT;
   static constexpr int NYT = (RMAX + G - 1) / G;
   static constexpr int ROWS = NYT * G;
-  static constexpr int QA = (A + 1) & ~1, PX = ((A / 2 + 1) * A + 1) & ~1, PS = ((NX / 2 + 1) * NX + 1) & ~1,
-                       BB = (B + 1) & ~1;
-  // stage record: [ q | Xinv (diagonal-packed) | Sinv (diagonal-packed) | row classes (2 bits per row) | l | u ]
+  static constexpr int PXX = ((NX / 2 + 1) * NX + 1) & ~1, PUU = ((NU / 2 + 1) * NU + 1) & ~1;
+  static constexpr int QA = (A + 1) & ~1, PX = BD ? PXX + PUU : (((A / 2 + 1) * A + 1) & ~1),
+                       PS = ((NX / 2 + 1) * NX + 1) & ~1, BB = (B + 1) & ~1;
+  // stage record: [ q | Xinv (diagonal-packed; BD: its xx block, then its uu block) | Sinv (diagonal-packed) |
+  //                 row classes (2 bits per row) | l | u ]
   static_assert(B <= 32 * kClsWords, "row classes of a stage must fit the class words of the record");
   static constexpr int RS = QA + PX + PS + kClsWords + 2 * BB;
-  static constexpr int XOFF = QA, SOFF = QA + PX, CLS = QA + PX + PS, LO = CLS + kClsWords, UP = LO + BB;
+  static constexpr int XOFF = QA, UOFF = QA + PXX, SOFF = QA + PX, CLS = QA + PX + PS, LO = CLS + kClsWords,
+                       UP = LO + BB;
   static constexpr uint32_t FWD_BYTES = 8u * (QA + PX + PS + kClsWords), BWD_BYTES = 8u * (PX + PS + kClsWords + 2 * BB);
   // per-group scratch (doubles, every block even-sized)
   static constexpr int AE = (A + 1) & ~1, NXE = (NX + 1) & ~1;
@@ -87,6 +95,8 @@ struct Shape {
                        M_END = (M_CTI + (3 * AE * CW + 1) / 2 + 1) & ~1;
   static constexpr int WNX = (A - 1 - A / 2) > 0 ? (A - 1 - A / 2) : 1;
   static constexpr int WNS = (NX - 1 - NX / 2) > 0 ? (NX - 1 - NX / 2) : 1;
+  static constexpr int WNU = (NU - 1 - NU / 2) > 0 ? (NU - 1 - NU / 2) : 1;
+  static_assert(NU >= 1, "a stage has at least one input");
   __host__ __device__ static int group_doubles(int D) { return ((D * RS + D + SC) + 1) & ~1; }
 };
 
@@ -102,6 +112,67 @@ __device__ __forceinline__ double dmv(const double *__restrict__ Dp, const doubl
   for (int d = 1; d <= N - 1 - N / 2; d++)
     acc[(N / 2 + d) & 3] = fma(Dp[wrap[d - 1]], v2i[N - d], acc[(N / 2 + d) & 3]);
   return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
+// The doubled operand of an Xinv product: v2[i .. i+n) = v[(i+d) mod n] for the block lane gl belongs to.
+template <class SH>
+__device__ __forceinline__ void v2_store(double *v2, int gl, double v) {
+  if constexpr (SH::BD) {
+    if (gl < SH::NX) {
+      v2[gl] = v; v2[gl + SH::NX] = v;
+    } else {
+      v2[2 * SH::NX + (gl - SH::NX)] = v; v2[2 * SH::NX + SH::NU + (gl - SH::NX)] = v;
+    }
+  } else {
+    v2[gl] = v; v2[gl + SH::A] = v;
+  }
+}
+
+// wrap-around offsets of lane gl for dmv: of the a x a block, of an nx x nx block, of the nu x nu block
+template <class SH>
+struct Wraps {
+  int X[SH::WNX], S[SH::WNS], U[SH::WNU];
+  __device__ __forceinline__ void init(int gl) {
+    constexpr int A = SH::A, NX = SH::NX, NU = SH::NU;
+#pragma unroll
+    for (int d = 1; d <= A - 1 - A / 2; d++) X[d - 1] = d * A + ((gl < A ? gl : 0) - d + A) % A;
+#pragma unroll
+    for (int d = 1; d <= NX - 1 - NX / 2; d++) S[d - 1] = d * NX + ((gl < NX ? gl : 0) - d + NX) % NX;
+    const int iu = (gl >= NX && gl < A) ? gl - NX : 0;
+#pragma unroll
+    for (int d = 1; d <= NU - 1 - NU / 2; d++) U[d - 1] = d * NU + (iu - d + NU) % NU;
+  }
+};
+
+// (Xinv_k v)_gl for gl < A, v doubled in v2 by v2_store; rec = the stage record.
+// BD: two passes (state lanes, then input lanes).  Running the input lanes predicated inside the state block's
+// loop saves a quarter of the instructions of this product but measured 3 % slower (longer dependent chains per
+// lane at the same shared-memory wavefront count).
+template <class SH>
+__device__ __forceinline__ double xinv_mv(const double *__restrict__ rec, int gl, const double *__restrict__ v2,
+                                          const Wraps<SH> &wr) {
+  if constexpr (SH::BD) {
+    if (gl < SH::NX) return dmv<SH::NX, SH::WNS>(rec + SH::XOFF, rec + SH::XOFF + gl, v2 + gl, wr.S);
+    const int i = gl - SH::NX;
+    return dmv<SH::NU, SH::WNU>(rec + SH::UOFF, rec + SH::UOFF + i, v2 + 2 * SH::NX + i, wr.U);
+  } else {
+    return dmv<SH::A, SH::WNX>(rec + SH::XOFF, rec + SH::XOFF + gl, v2 + gl, wr.X);
+  }
+}
+
+// entry (i, j) of the symmetric n x n block stored diagonal-packed at dp
+template <int N>
+__device__ __forceinline__ double dp_at(const double *__restrict__ dp, int i, int j) {
+  int d = j - i;
+  if (d < 0) d += N;
+  return (d <= N / 2) ? dp[d * N + i] : dp[(N - d) * N + j];
+}
+
+// Xinv_k(i, j), i < A, j < NX (the state columns)
+template <class SH>
+__device__ __forceinline__ double xinv_state_col(const double *__restrict__ rec, int i, int j) {
+  if constexpr (SH::BD) return i < SH::NX ? dp_at<SH::NX>(rec + SH::XOFF, i, j) : 0.0;
+  else return dp_at<SH::A>(rec + SH::XOFF, i, j);
 }
 
 // sum_j Mcol[j*LD] * v[j], j < NJ  (Mcol already offset by the lane's row)
@@ -133,16 +204,25 @@ struct MutVec {  // the mutable per-stage values a lane owns (iterates and forwa
 // The specialisation table: (nx+nu, nx, ny, nt, ELL width of C).  First the BASELINE.json shapes, then
 // other box-constrained MPC shapes (nx,nu) = (2,1) (4,1) (6,2) (6,3) (8,4) (16,4): odd and even block sizes
 // in every lane-group width.  Any other shape runs on the runtime-shape kernels of rldl_kernels.cu.
-#define RLDL_SHAPES(X) \
-  X(6, 4, 6, 4, 1)     \
-  X(16, 12, 16, 12, 1) \
-  X(11, 8, 11, 8, 1)   \
-  X(3, 2, 3, 2, 1)     \
-  X(5, 4, 5, 4, 1)     \
-  X(8, 6, 8, 6, 1)     \
-  X(9, 6, 9, 6, 1)     \
-  X(12, 8, 12, 8, 1)   \
-  X(20, 16, 20, 16, 1)
+// Last column: 1 = the block-diagonal-pivot variant (chosen first when the model qualifies, ModelDev::bd).
+#define RLDL_SHAPES(X)    \
+  X(6, 4, 6, 4, 1, 1)     \
+  X(16, 12, 16, 12, 1, 1) \
+  X(11, 8, 11, 8, 1, 1)   \
+  X(6, 4, 6, 4, 1, 0)     \
+  X(16, 12, 16, 12, 1, 0) \
+  X(11, 8, 11, 8, 1, 0)   \
+  X(3, 2, 3, 2, 1, 0)     \
+  X(5, 4, 5, 4, 1, 0)     \
+  X(8, 6, 8, 6, 1, 0)     \
+  X(9, 6, 9, 6, 1, 0)     \
+  X(12, 8, 12, 8, 1, 0)   \
+  X(20, 16, 20, 16, 1, 0)
+
+// does table entry (a, nx, ny, nt, cw, bd) serve this model?
+inline bool shape_serves(const ModelDev &M, int cw_model, int a, int nx, int ny, int nt, int cw, int bd) {
+  return M.a == a && M.nx == nx && M.ny == ny && M.nt == nt && cw_model <= cw && (bd == 0 || M.bd != 0);
+}
 
 inline int max_c_width(const ModelDev &M) {
   int wdt = 0;
