@@ -296,16 +296,21 @@ def main_b200(args):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = iter_sum * admm_bytes / (s_ms * 1e-3) / 1e9
     # DRAM traffic of the same kernel from the committed ncu --set full capture
-    # (profiles/r01_stream_v5_ncu_full_uniform_c5_batch16384.txt: dram read 432.75 GB + write 66.61 GB for
-    # 1.6384 M instance-iterations x 275 040 algorithmic bytes), scaled by the algorithmic bytes of this launch
-    traffic_ratio = (432.746847e9 + 66.611270e9) / (16384 * 100 * 275040.0)
+    # (profiles/r01_stream_v7_ncu_full_uniform_c5_batch16384.txt: dram read 372.42 GB + write 66.51 GB for
+    # 1.6384 M instance-iterations x 235 872 algorithmic bytes with the block-diagonal pivot records;
+    # r01_stream_v5_...: 432.75 + 66.61 GB x 275 040 bytes with the full a x a block), scaled by the algorithmic
+    # bytes of this launch
+    if abs(admm_bytes - 235872.0) < 1.0:
+        traffic_ratio = (372.419525e9 + 66.513596e9) / (16384 * 100 * 235872.0)
+    else:
+        traffic_ratio = (432.746847e9 + 66.611270e9) / (16384 * 100 * 275040.0)
     roof = {"bound": "hbm", "kernel": "k_admm_stream (fused KKT solve + ADMM step + termination, whole solve loop; its tail is finished by k_admm_cta inside the same timed region)",
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
             "traffic": traffic_ratio * iter_sum * admm_bytes,
             "traffic_source": "ncu dram__bytes_read+write of this kernel at batch 16384, uniform 100 iterations (x%.3f of algorithmic), scaled" % traffic_ratio,
             "launch_ms": s_ms, "algorithmic_bytes_per_launch": iter_sum * admm_bytes,
-            "factor_kernel": {"kernel": "k_factor_stream (stage recursion, FP64-latency bound: ~10 flop/B)",
+            "factor_kernel": {"kernel": "k_factor_stream (stage recursion, ~10 flop/B: shared-memory data pipe 70 %, FP64 pipe 27 %, profiles/r01_factor_v6_ncu_full_c5_batch16384.txt)",
                               "launch_ms": f_ms, "achieved": factor_bytes / (f_ms * 1e-3) / 1e9,
                               "frac": factor_bytes / (f_ms * 1e-3) / 1e9 / peak}}
     mean_iter = allsum(iter_sum) / total
