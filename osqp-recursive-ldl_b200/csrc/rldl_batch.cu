@@ -430,7 +430,7 @@ c_int Batch::solve() {
     if (const char *e = getenv("RLDL_LAT_BELOW")) lat_below = atoi(e);
     const size_t lat_smem = latency_smem_bytes(M, N);
     const bool lat_ok = lat_below > 0 && lat_smem != (size_t)-1 && lat_smem <= 227 * 1024;
-    if (lat_ok && !d_latT) CK(cudaMalloc(&d_latT, (size_t)sms * 2 * Nmax * nx * (nx + 2) * sizeof(double)));
+    if (lat_ok && !d_latT) CK(cudaMalloc(&d_latT, (size_t)sms * latency_t_blocks(Nmax) * nx * (nx + 2) * sizeof(double)));
     int unfinished = batch, resume = 0;
     CK(cudaMemcpyAsync(D.sched + kSchedUnfinished, &unfinished, sizeof(int), cudaMemcpyHostToDevice, stream));
     for (;;) {

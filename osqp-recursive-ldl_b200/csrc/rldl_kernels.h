@@ -28,6 +28,7 @@ cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, in
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                                int resume, int park_below, cudaStream_t st);
 // latency-mode kernel (rldl_latency.cu): one instance per CTA, factor resident in shared memory
+int latency_t_blocks(int Nmax);  // nx x (nx+2) blocks of global scratch per CTA of the latency-mode kernel
 size_t latency_smem_bytes(const ModelDev &M, int N);  // (size_t)-1 if the shape is not in the table
 cudaError_t launch_admm_latency(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                                 int resume, double *Tg, int ctas, int reset_parked, cudaStream_t st);

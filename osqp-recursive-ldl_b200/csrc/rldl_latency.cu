@@ -40,6 +40,9 @@ namespace rldl {
 
 constexpr int kLatThreads = 512;
 
+// nx x (nx+2) blocks of global scratch per CTA: T_k and T_k' per stage, chain blocks and their transposes
+__host__ __device__ inline int lat_t_blocks(int Nmax) { return 2 * Nmax + 2 * (Nmax / 2 + 2); }
+
 template <class SH>
 struct LatLayout {  // shared-memory layout (doubles) of k_admm_cta for horizon N
   static constexpr int NG = (kLatThreads / 32) * SH::GPW;
@@ -171,39 +174,58 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
   // T_k for phase B (TB[k][i*TS + j] = T_k(i,j)) and phase D (TD[k][i*TS + j] = T_k(j,i)) in global memory
   // (2*Nmax*TBLK doubles per CTA, L2-resident), written once per instance by this CTA and streamed back
   // through the shared-memory ring by bulk async copies, CH stages per copy
-  double *TB = Tg + (size_t)blockIdx.x * 2 * B.Nmax * TBLK, *TD = TB + (size_t)B.Nmax * TBLK;
-  // One scan (group 0): vec[k] += T_k vec[k-1], k = 1..N-1 (fwd, vec = vc: sp_k) or
-  // vec[k] += T_k' vec[k+1], k = N-1..1 (bwd, vec = vd: vn_k).  The previous result is re-read from shared
-  // memory by broadcast LDS.128; one __syncwarp per stage.
+  double *TB = Tg + (size_t)blockIdx.x * lat_t_blocks(B.Nmax) * TBLK, *TD = TB + (size_t)B.Nmax * TBLK;
+  // Blocked scans: the stages 1..N-1 of the two recurrences are taken in pairs (2j-1, 2j), j = 1..J, plus a
+  // leftover stage N-1 when N-1 is odd.  The sequential chain runs over the pairs only,
+  //     sp_2j     = (c_2j     + T_2j c_2j-1)      + (T_2j T_2j-1)  sp_2j-2
+  //     vn_2j-1   = (d_2j-1   + T_2j-1' d_2j)     + (T_2j T_2j-1)' vn_2j+1
+  // (NC = J + leftover steps instead of N-1), and the stage in the middle of every pair is filled in by the group
+  // that owns the pair (sp_2j-1 = c_2j-1 + T_2j-1 sp_2j-2, vn_2j = d_2j + T_2j' vn_2j+1), off the chain.
+  // CB[p] / CD[p], p = 1..NC: the chain blocks (P_p = T_2p T_2p-1, or T_N-1 for the leftover) and their transposes.
+  double *CB = TD + (size_t)B.Nmax * TBLK, *CD = CB + (size_t)(B.Nmax / 2 + 2) * TBLK;
+  const int J = (N - 1) / 2, LEFT = (N - 1) & 1, NC = J + LEFT, NI = J + 2;
+  // row gl of an nx x nx block in global memory (L2) times a vector in shared memory
+  auto tmv = [&](const double *blk, const double *v) -> double {
+    const double2 *r = reinterpret_cast<const double2 *>(blk + (gl < NX ? gl : 0) * TS);
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int j = 0; j < NX / 2; j++) {
+      const double2 t = __ldcg(r + j);
+      acc[(2 * j) & 3] = fma(t.x, v[2 * j], acc[(2 * j) & 3]);
+      acc[(2 * j + 1) & 3] = fma(t.y, v[2 * j + 1], acc[(2 * j + 1) & 3]);
+    }
+    return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+  };
+  // One scan (group 0) over the chain: step p = 1..NC (fwd, vec = vc) writes sp_2p from sp_2p-2 (leftover:
+  // sp_N-1 from sp_N-2); step p = NC..1 (bwd, vec = vd) writes vn_2p-1 from vn_2p+1 (leftover, first: vn_N-1 from
+  // vn_N).  The source vector is re-read from shared memory by broadcast LDS.128; one __syncwarp per step.
   auto scan = [&](const bool fwd) {
-    const double *Tsrc = fwd ? TB : TD;
+    const double *Tsrc = fwd ? CB : CD;
     double *vec = fwd ? vc : vd;
-    const int nblk = N - 1, nchunk = (nblk + CH - 1) / CH;
+    const int nblk = NC, nchunk = (nblk + CH - 1) / CH;
     auto issue_chunk = [&](int c) {  // leader: chunk c of the scan order -> ring slot c % NS
       const int t0 = c * CH, cnt = min(CH, nblk - t0);
-      const int k_lo = fwd ? 1 + t0 : (N - 1 - t0) - (cnt - 1);
+      const int p_lo = fwd ? 1 + t0 : (NC - t0) - (cnt - 1);
       const int s = c % NS;
       mbar_expect_tx(tbars_s + 8u * s, (uint32_t)(cnt * TBLK * 8));
-      bulk_g2s(tring_s + 8u * (uint32_t)(s * CH * TBLK), Tsrc + (size_t)k_lo * TBLK, (uint32_t)(cnt * TBLK * 8),
+      bulk_g2s(tring_s + 8u * (uint32_t)(s * CH * TBLK), Tsrc + (size_t)p_lo * TBLK, (uint32_t)(cnt * TBLK * 8),
                tbars_s + 8u * s);
     };
     if (gl == 0)
       for (int c = 0; c < NS && c < nchunk; c++) issue_chunk(c);
-    // progress counter of this scan: number of final vectors (the first one is final before the scan starts);
-    // the other direction's counter is idle during this phase and is reset here for its next use
+    // progress counter of this scan: number of chain steps done; the other direction's counter is idle during
+    // this phase and is reset here for its next use
     volatile int *prog = fwd ? prog_f : prog_b;
-    int done_ = 1;
+    int done_ = 0;
     if (gl == 0) {
       *(fwd ? prog_b : prog_f) = 0;
       __threadfence_block();
-      *prog = 1;
     }
-    // 32-bit shared addresses, advanced incrementally: nothing but the mat-vec itself is on the chain
+    // 32-bit shared addresses: nothing but the mat-vec itself is on the chain
     const int row = (gl < NX) ? gl : 0;
     const uint32_t vec_s = smem_u32(vec);
-    uint32_t pk = vec_s + 8u * (uint32_t)((fwd ? 1 : N - 1) * NXE);  // &vec[k][0]
-    const int dstep = fwd ? NXE * 8 : -NXE * 8, tstep = fwd ? TBLK * 8 : -TBLK * 8;
-    int s = 0;
+    const int tstep = fwd ? TBLK * 8 : -TBLK * 8;
+    int s = 0, t = 0;
     for (int c = 0; c < nchunk; c++) {
 #ifdef RLDL_LAT_PROFILE
       const long long w0_ = clock64();
@@ -214,34 +236,42 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
 #endif
       const int cnt = min(CH, nblk - c * CH);
       uint32_t ta = tring_s + 8u * (uint32_t)((s * CH + (fwd ? 0 : cnt - 1)) * TBLK + row * TS);
-      for (int r = 0; r < cnt; r++) {
-        // (loading the next stage's T rows ahead of the STS below was measured slower: the loads sit in the
-        // in-order LSU queue in front of the store the next stage is waiting for)
+      for (int r = 0; r < cnt; r++, t++) {
+        const int p = fwd ? t + 1 : NC - t;
+        const bool pair = p <= J;
+        const int dst = pair ? (fwd ? 2 * p : 2 * p - 1) : N - 1;
+        const int src = pair ? (fwd ? 2 * p - 2 : 2 * p + 1) : (fwd ? N - 2 : N);
+        const uint32_t pd = vec_s + 8u * (uint32_t)(dst * NXE), ps = vec_s + 8u * (uint32_t)(src * NXE);
+        // (loading the next step's T rows ahead of the STS below was measured slower: the loads sit in the
+        // in-order LSU queue in front of the store the next step is waiting for)
         double2 tv[NX / 2], vv[NX / 2];
 #pragma unroll
         for (int j = 0; j < NX / 2; j++) tv[j] = lds128(ta + 16u * j);
         double cur = 0.0;
-        if (gl < NX) cur = lds64(pk + 8u * gl);
+        if (gl < NX) cur = lds64(pd + 8u * gl);
 #pragma unroll
-        for (int j = 0; j < NX / 2; j++) vv[j] = lds128(pk - dstep + 16u * j);
+        for (int j = 0; j < NX / 2; j++) vv[j] = lds128(ps + 16u * j);
         double acc[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
         for (int j = 0; j < NX / 2; j++) {
           acc[(2 * j) & 3] = fma(tv[j].x, vv[j].x, acc[(2 * j) & 3]);
           acc[(2 * j + 1) & 3] = fma(tv[j].y, vv[j].y, acc[(2 * j + 1) & 3]);
         }
-        if (gl < NX) sts64(pk + 8u * gl, cur + ((acc[0] + acc[1]) + (acc[2] + acc[3])));
+        if (gl < NX) sts64(pd + 8u * gl, cur + ((acc[0] + acc[1]) + (acc[2] + acc[3])));
         __syncwarp(gm);
         // publish (after the __syncwarp: the stores of one warp reach shared memory in program order);
         // the groups working behind the scan poll this counter
         if (gl == 0) *prog = ++done_;
         ta += tstep;
-        pk += dstep;
       }
       if (gl == 0 && c + NS < nchunk) issue_chunk(c + NS);
       s = (s + 1 == NS) ? 0 : s + 1;
     }
   };
+  // work items of the groups behind the scans: item 0 = stage 0, item j = 1..J = the pair (2j-1, 2j),
+  // item J+1 = the leftover stage (if any) and the terminal stage
+  auto item_lo = [&](int it) -> int { return it == 0 ? 0 : (it <= J ? 2 * it - 1 : 2 * J + 1); };
+  auto item_hi = [&](int it) -> int { return it == 0 ? 0 : (it <= J ? 2 * it : N); };
 
   for (;;) {
     // ---------------- claim an instance (same counter / resume rules as the streaming kernel) ----------------
@@ -312,7 +342,34 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         __syncwarp(gm);
       }
     }
-    __threadfence();  // T blocks are read back by bulk async copies (async proxy)
+    __threadfence();
+    __syncthreads();
+    // ---------------- chain blocks: P_p = T_2p T_2p-1 (and the leftover T_N-1), one group per block ----------------
+    for (int p = 1 + grp; p <= NC; p += NG) {
+      const bool pair = p <= J;
+      const double *T2 = TB + (size_t)(pair ? 2 * p : N - 1) * TBLK;  // rows of the left factor
+      const double *T1t = TD + (size_t)(pair ? 2 * p - 1 : 0) * TBLK;  // rows of T_2p-1' = columns of T_2p-1
+      if (gl < NX) {
+        double rowv[NX];
+#pragma unroll
+        for (int mm = 0; mm < NX; mm++) rowv[mm] = __ldcg(T2 + gl * TS + mm);
+#pragma unroll 1
+        for (int c = 0; c < NX; c++) {
+          double v = 0.0;
+          if (pair) {
+#pragma unroll
+            for (int mm = 0; mm < NX; mm++) v = fma(rowv[mm], __ldcg(T1t + c * TS + mm), v);
+          } else {
+#pragma unroll
+            for (int mm = 0; mm < NX; mm++)
+              if (mm == c) v = rowv[mm];
+          }
+          CB[(size_t)p * TBLK + gl * TS + c] = v;
+          CD[(size_t)p * TBLK + c * TS + gl] = v;
+        }
+      }
+    }
+    __threadfence();  // the chain blocks are read back by bulk async copies (async proxy)
     asm volatile("fence.proxy.async;" ::: "memory");
     __syncthreads();
     // ===== phase A for one stage: rhs, a_k = Xinv_k r^v_k, c_k = Sinv_k (r^d_k - F_k a_k), from the iterates of
@@ -353,22 +410,32 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       }
       __syncwarp(gm);
     };
-    // first iteration: phase A from the iterates in HBM, by the groups that will own the stages in phase E
+    // forward pre-step of a pair: c_2j += T_2j c_2j-1 (the chain then needs sp_2j-2 only)
+    auto pre_fwd = [&](int it) {
+      if (it >= 1 && it <= J) {
+        if (gl < NX) vc[2 * it * NXE + gl] += tmv(TB + (size_t)(2 * it) * TBLK, vc + (2 * it - 1) * NXE);
+        __syncwarp(gm);
+      }
+    };
+    // first iteration: phase A from the iterates in HBM, by the groups that will own the items in phase E
     if (grp >= 2) {
-      for (int k = grp - 2; k <= N; k += NGW) {
-        const bool term = (k == N);
-        const int dim = term ? NX : A, np = term ? NT : NY;
-        const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
-        const double xv = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
-        double zp[NYT], yp[NYT], zd = 0.0, yd = 0.0;
+      for (int it = grp - 2; it < NI; it += NGW) {
+        for (int k = item_lo(it); k <= item_hi(it); k++) {
+          const bool term = (k == N);
+          const int dim = term ? NX : A, np = term ? NT : NY;
+          const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
+          const double xv = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
+          double zp[NYT], yp[NYT], zd = 0.0, yd = 0.0;
 #pragma unroll
-        for (int t = 0; t < NYT; t++) {
-          const int rr = gl + G * t;
-          zp[t] = yp[t] = 0.0;
-          if (rr < np) { zp[t] = __ldcg(z + roff + rr); yp[t] = __ldcg(y + roff + rr); }
+          for (int t = 0; t < NYT; t++) {
+            const int rr = gl + G * t;
+            zp[t] = yp[t] = 0.0;
+            if (rr < np) { zp[t] = __ldcg(z + roff + rr); yp[t] = __ldcg(y + roff + rr); }
+          }
+          if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
+          stage_A(k, xv, zp, yp, zd, yd);
         }
-        if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
-        stage_A(k, xv, zp, yp, zd, yd);
+        pre_fwd(it);
       }
     }
     __syncthreads();
@@ -393,24 +460,36 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       //       has published sp_k =====
       if (grp == 0) {
         scan(true);
+        PT(1);
       } else if (grp >= 2) {
-        for (int k = grp - 2; k <= N; k += NGW) {
-          const bool term = (k == N);
-          const double *sl_ = recs + k * RS;
-          wait_prog(prog_f, (term ? N - 1 : k) + 1);
-          if (gl < A) {
-            double gg = 0.0;
-            if (!term) gg = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, vc + k * NXE);
-            if (k > 0 && gl < NX) gg -= vc[(k - 1) * NXE + gl];
-            v2_store<SH>(gg2, gl, gg);
+        for (int it = grp - 2; it < NI; it += NGW) {
+          // chain steps this item waits for: pair j: sp_2j (step j); last item: the whole chain
+          wait_prog(prog_f, it == 0 ? 0 : (it <= J ? it : NC));
+          if (it >= 1 && it <= J) {  // fill the middle stage: sp_2j-1 = c_2j-1 + T_2j-1 sp_2j-2
+            if (gl < NX) vc[(2 * it - 1) * NXE + gl] += tmv(TB + (size_t)(2 * it - 1) * TBLK, vc + (2 * it - 2) * NXE);
+            __syncwarp(gm);
           }
-          __syncwarp(gm);
-          if (gl < A) {
-            const double e = va[k * AE + gl] + xinv_mv<SH>(sl_, gl, gg2, wr);
-            va[k * AE + gl] = e;
-            if (gl < NX) vd[k * NXE + gl] = e;
+          for (int k = item_lo(it); k <= item_hi(it); k++) {
+            const bool term = (k == N);
+            const double *sl_ = recs + k * RS;
+            if (gl < A) {
+              double gg = 0.0;
+              if (!term) gg = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, vc + k * NXE);
+              if (k > 0 && gl < NX) gg -= vc[(k - 1) * NXE + gl];
+              v2_store<SH>(gg2, gl, gg);
+            }
+            __syncwarp(gm);
+            if (gl < A) {
+              const double e = va[k * AE + gl] + xinv_mv<SH>(sl_, gl, gg2, wr);
+              va[k * AE + gl] = e;
+              if (gl < NX) vd[k * NXE + gl] = e;
+            }
+            __syncwarp(gm);
           }
-          __syncwarp(gm);
+          if (it >= 1 && it <= J) {  // backward pre-step: d_2j-1 += T_2j-1' d_2j
+            if (gl < NX) vd[(2 * it - 1) * NXE + gl] += tmv(TD + (size_t)(2 * it - 1) * TBLK, vd + 2 * it * NXE);
+            __syncwarp(gm);
+          }
         }
       }
       __syncthreads();
@@ -419,9 +498,19 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       //       (vn_N = d_N; stage 0 has no state) =====
       // (phase E below runs behind this scan: groups 2.. take their stages in descending order and start on
       // stage k once vn_{k+1} is published)
-      if (grp == 0) scan(false);
+      if (grp == 0) {
+        scan(false);
+        PT(3);
+      }
       // ===== phase E: v_k = e_k + Xinv_k F_k' (Sinv_k vn_{k+1}), nu^d_k, ADMM step (auxil.c:188-228) =====
-      for (int k = (grp >= 2 && grp - 2 <= N) ? (grp - 2) + ((N - (grp - 2)) / NGW) * NGW : -1; k >= 0; k -= NGW) {
+      for (int it = (grp >= 2 && grp - 2 < NI) ? (grp - 2) + ((NI - 1 - (grp - 2)) / NGW) * NGW : -1; it >= 0; it -= NGW) {
+       // chain steps this item waits for: pair j: vn_2j+1 (LEFT + J - j steps); stage 0: the whole chain (vn_1)
+       wait_prog(prog_b, it == 0 ? NC : (it <= J ? LEFT + J - it : 0));
+       if (it >= 1 && it <= J) {  // fill the middle stage: vn_2j = d_2j + T_2j' vn_2j+1
+         if (gl < NX) vd[2 * it * NXE + gl] += tmv(TD + (size_t)(2 * it) * TBLK, vd + (2 * it + 1) * NXE);
+         __syncwarp(gm);
+       }
+       for (int k = item_hi(it); k >= item_lo(it); k--) {
         const bool term = (k == N);
         const int cls = term ? 2 : (k == 0 ? 0 : 1);
         const int dim = term ? NX : A, np = term ? NT : NY;
@@ -437,7 +526,6 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         }
         if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
         double vv = 0.0, nud = 0.0;
-        if (!term) wait_prog(prog_b, N - k);  // vn_{k+1} published (the loads above are already in flight)
         if (term) {
           if (gl < A) vv = va[k * AE + gl];
         } else {
@@ -500,6 +588,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         // phase A of the next iteration for this stage, straight from the registers (its inputs are stage-local;
         // va[k] / vc[k] have no reader left in this iteration)
         stage_A(k, xnew, zp, yp, zd, yd);
+       }
+       pre_fwd(it);
       }
       if (!(can_check || can_adapt || last)) {
         __syncthreads();  // iterates of this iteration visible to every group of the CTA
@@ -729,6 +819,8 @@ static cudaError_t launch_latency_t(const ModelDev &M, const BatchDev &B, const 
   kern<<<(unsigned)ctas, kLatThreads, shm, st>>>(M, B, S, warm_start, resume, Tg);
   return cudaGetLastError();
 }
+
+int latency_t_blocks(int Nmax) { return lat_t_blocks(Nmax); }
 
 size_t latency_smem_bytes(const ModelDev &M, int N) {
   const int cw = max_c_width(M);

@@ -94,8 +94,12 @@ def test_adaptive_rho_streaming_matches_generic_kernel(name, batch, below, monke
     assert (outs[0]["rho_updates"] == outs[1]["rho_updates"]).all()
     bad = compare(outs[0], outs[1], n, m)
     assert not bad, bad[:5]
-    # rho_estimate is a ratio of converged (1e-6-sized) residuals: only its magnitude is comparable
-    assert np.allclose(outs[0]["rho_estimate"], outs[1]["rho_estimate"], rtol=0.5)
+    # rho_estimate is a ratio of converged residuals: only its magnitude is comparable, and only where the
+    # residuals are above the cancellation noise of their own evaluation (a residual of 1e-10 on O(1) data
+    # differs by a factor between two summation orders)
+    live = np.minimum(np.minimum(outs[0]["pri_res"], outs[0]["dua_res"]),
+                      np.minimum(outs[1]["pri_res"], outs[1]["dua_res"])) > 1e-8
+    assert np.allclose(outs[0]["rho_estimate"][live], outs[1]["rho_estimate"][live], rtol=0.5)
 
 
 def test_batch_update_bounds_rejects_l_above_u_and_keeps_problem():
