@@ -1,0 +1,138 @@
+"""Edge cases of the hot path through the C ABI, each against the unmodified reference
+(oracle/_ref) on identical inputs: shortest horizons, Nmax > N, a batch of one, iteration limits
+that do not fall on a termination check, no termination checks at all, non-default ADMM
+parameters, and batches whose instances have DIFFERENT constraint types per row (loose /
+equality / inequality, src/auxil.c:79-101), on every ADMM kernel.
+
+Oracle choice: the reference's recursive path where it is sound, its stock path on the assembled
+P/A otherwise (the two agree to 1e-13 on the same mathematics; F3/F4 and the
+N = Nmax = 1 failure found here make the recursive path unusable for those inputs).
+"""
+import numpy as np
+import pytest
+
+import rldl_b200 as R
+from rldl_b200 import mpc
+from common import gpu_settings, ref_run, compare
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu(mdl, N, Nmax, q, l, u, kernel=None, rho=None, **kw):
+    gb = R.Batch(mdl, N, Nmax, q, l, u, gpu_settings(**kw), rho=rho)
+    if kernel is not None:
+        assert gb.select_kernel(kernel) == 0
+    assert gb.solve() == 0
+    out = gb.get()
+    n, m, _, _ = gb.dims()
+    gb.free()
+    return out, n, m
+
+
+def _c1(batch, N, Nmax=None, seed=1234):
+    mdl = mpc.make_model(mpc.CONFIGS["C1"])
+    q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch, seed), N, Nmax)
+    return mdl, q, l, u
+
+
+@pytest.mark.parametrize("N,Nmax,path", [(1, 1, "stock"), (1, 2, "recursive"), (2, 2, "recursive"),
+                                         (7, 20, "recursive"), (20, 21, "recursive")])
+def test_short_horizons_and_nmax_above_n(N, Nmax, path):
+    """N = 1 is a stage-0 block followed directly by the terminal block; Nmax > N leaves unused tail
+    storage that must not leak into the solve.  (The reference's recursive path itself fails at
+    N = Nmax = 1 — it runs to max_iter where its stock path needs 50 iterations — so that case is
+    checked against the stock path.)"""
+    mdl, q, l, u = _c1(6, N, Nmax)
+    if path == "stock":
+        qs, ls, us = mdl.vectors(mpc.sample_x0(mdl, 6), N, N)
+        ref = ref_run(mdl, N, N, qs, ls, us, [("solve",), ("get",)], path="stock")[1]
+    else:
+        ref = ref_run(mdl, N, Nmax, q, l, u, [("solve",), ("get",)])[1]
+    for kernel in (None, 0, 1):
+        out, n, m = _gpu(mdl, N, Nmax, q, l, u, kernel)
+        assert (n, m) == (N * 6, N * 10 + 4)
+        bad = compare(out, ref, n, m)
+        assert not bad, (kernel, bad[:3])
+
+
+def test_batch_of_one():
+    mdl, q, l, u = _c1(1, 20)
+    ref = ref_run(mdl, 20, 20, q, l, u, [("solve",), ("get",)])[1]
+    out, n, m = _gpu(mdl, 20, 20, q, l, u)
+    assert not compare(out, ref, n, m)
+
+
+@pytest.mark.parametrize("kw", [dict(max_iter=60), dict(max_iter=25), dict(max_iter=1),
+                                dict(check_termination=0, max_iter=100),
+                                dict(check_termination=7, max_iter=500),
+                                dict(alpha=1.0, sigma=1e-3, rho=1.0),
+                                dict(eps_abs=1e-3, eps_rel=1e-3, alpha=1.8),
+                                dict(eps_abs=1e-9, eps_rel=0.0, max_iter=110)],
+                         ids=["max_iter_60", "max_iter_25", "max_iter_1", "no_checks", "check_every_7",
+                              "alpha1_sigma_rho", "loose_eps", "tight_eps_hits_limit"])
+@pytest.mark.parametrize("kernel", [None, 0, 1], ids=["latency", "stream", "generic"])
+def test_iteration_limits_and_parameters(kw, kernel):
+    """Termination bookkeeping of src/osqp.c:354-627: the last iteration is checked even when it is
+    not a multiple of check_termination, 'solved inaccurate' (status 2) is decided once after
+    max_iter with 10x tolerances, check_termination = 0 disables the checks inside the loop."""
+    mdl, q, l, u = _c1(24, 20)
+    kw = dict(kw)
+    rho = kw.pop("rho", None)                     # the step size goes in per instance (rldl_batch_setup's rho array)
+    rho = None if rho is None else np.full(24, rho)
+    ref = ref_run(mdl, 20, 20, q, l, u, [("solve",), ("get",)], rho=rho, **kw)[1]
+    out, n, m = _gpu(mdl, 20, 20, q, l, u, kernel, rho=rho, **kw)
+    bad = compare(out, ref, n, m)
+    assert not bad, bad[:3]
+
+
+@pytest.mark.parametrize("name,batch", [("C1", 48), ("C3", 24), ("C4", 12)])
+@pytest.mark.parametrize("kernel", [None, 0, 1], ids=["latency", "stream", "generic"])
+def test_per_instance_constraint_types_and_costs(name, batch, kernel):
+    """Every instance gets its own mix of loose rows (|bound| >= 1e26 -> rho 1e-6), equality rows
+    (u - l < 1e-4 -> 1e3 rho) and inequality rows, asymmetric bounds and a random linear cost, so the
+    2-bit row classes of the stage records differ between instances.  Oracle = stock path (the
+    recursive path reads the terminal rho from stage N-1's rows)."""
+    cfg = mpc.CONFIGS[name]
+    mdl = mpc.make_model(cfg)
+    N, nx, nu = cfg["N"], mdl.nx, mdl.nu
+    a, b = nx + nu, 2 * nx + nu
+    q, l, u = mdl.vectors(0.3 * mpc.sample_x0(mdl, batch), N)
+    rng = np.random.default_rng(99)
+    q += 0.05 * rng.standard_normal(q.shape)
+    for k in range(1, N):
+        r = k * b
+        loose = rng.random((batch, nx)) < 0.3                      # state rows: some unbounded
+        l[:, r:r + nx][loose] = -1e30
+        u[:, r:r + nx][loose] = 1e30
+        onesided = rng.random((batch, nx)) < 0.2                   # some one-sided
+        u[:, r:r + nx][onesided & ~loose] = 1e30
+        eq = rng.random((batch, nu)) < 0.15                        # input rows: some pinned (equality)
+        mid = 0.2 * (l[:, r + nx:r + a] + u[:, r + nx:r + a]) + 0.05 * (u[:, r + nx:r + a] - l[:, r + nx:r + a])
+        l[:, r + nx:r + a][eq] = mid[eq]
+        u[:, r + nx:r + a][eq] = mid[eq]
+        shrink = rng.random((batch, nu)) < 0.3                     # some asymmetric
+        u[:, r + nx:r + a][shrink & ~eq] *= 0.5
+    ref = ref_run(mdl, N, N, q, l, u, [("solve",), ("get",)], path="stock")[1]
+    assert (ref["status"] == 1).mean() > 0.5                       # the case is not degenerate
+    out, n, m = _gpu(mdl, N, N, q, l, u, kernel)
+    bad = compare(out, ref, n, m)
+    assert not bad, bad[:3]
+
+
+def test_update_settings_between_solves():
+    """Settings changed between solves (the osqp_update_* setters, include/osqp.h:258-419) take effect
+    on the next solve: tolerances, max_iter, alpha, check_termination."""
+    mdl, q, l, u = _c1(16, 20)
+    kw1 = dict(eps_abs=1e-3, eps_rel=1e-3)
+    kw2 = dict(eps_abs=1e-7, eps_rel=1e-7, alpha=1.4, check_termination=10, max_iter=900)
+    r1 = ref_run(mdl, 20, 20, q, l, u, [("solve",), ("get",)], **kw1)[1]
+    r2 = ref_run(mdl, 20, 20, q, l, u, [("solve",), ("get",)], **kw2)[1]
+    gb = R.Batch(mdl, 20, 20, q, l, u, gpu_settings(**kw1))
+    n, m, _, _ = gb.dims()
+    assert gb.solve() == 0
+    assert not compare(gb.get(), r1, n, m)
+    assert gb.update_settings(gpu_settings(**kw2)) == 0
+    assert gb.solve() == 0                                          # warm_start = 0: cold again
+    bad = compare(gb.get(), r2, n, m)
+    gb.free()
+    assert not bad, bad[:3]

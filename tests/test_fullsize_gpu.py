@@ -1,0 +1,155 @@
+"""GPU parity at BASELINE.json's FULL batch sizes (C2 1 024, C3 4 096, C4 2 048, C5 65 536).
+
+The reference needs minutes for batches of this size, so every instance is checked through
+size-independent properties of an OSQP solve, evaluated on the host with the assembled global
+P and A (mpc.assemble mirrors reference src/recursive_ldl.c:1873), and a seeded SAMPLE of the
+batch is compared with the unmodified reference (oracle/_ref) per instance.
+
+Properties (all follow from the iteration of src/auxil.c:188-228, 243-362, 684-789):
+  P1 status / iter bookkeeping: status in {solved, solved inaccurate, max_iter}, the last two only at
+     iter == max_iter; iter a multiple of check_termination.
+  P2 reported obj_val == 1/2 x'Px + q'x and dua_res == ||Px + q + A'y||_inf of the returned (x, y).
+  P3 solved  =>  dua_res <= eps_abs + eps_rel max(||Px||,||A'y||,||q||)  and
+                 dist(Ax, [l,u]) <= pri_res <= eps_abs + eps_rel ||Ax||_inf (+ slack for ||z||).
+  P4 y = rho (w - clip(w)):  y_i > 0 (above rounding noise) only on rows with |Ax_i - u_i| <= pri_res, y_i < 0 only with
+     |Ax_i - l_i| <= pri_res (z sits exactly on the bound there and |Ax - z| <= pri_res).
+  P5 sub-batch invariance: a slice of the batch solved on its own gives the same results.
+"""
+import numpy as np
+import pytest
+
+import rldl_b200 as R
+from rldl_b200 import mpc
+from common import gpu_settings, settings_dict, ref_run, compare, REL_TOL
+
+pytestmark = pytest.mark.gpu
+
+EPS = 1e-5  # eps_abs = eps_rel of the common settings
+
+
+def _check_properties(mdl, N, q, l, u, out, chunk=8192, check=25):
+    P, A = mdl.assemble(N)
+    Pf = (P + P.T).tocsc()
+    Pf.setdiag(P.diagonal())
+    n, m = A.shape[1], A.shape[0]
+    B = q.shape[0]
+    st, it = out["status"], out["iter"]
+    assert np.isin(st, (1, 2, -2)).all(), np.unique(st)                                # P1
+    assert (it[st != 1] == 4000).all()                       # 'inaccurate' / 'max iter' are only decided at max_iter
+    assert (it % check == 0).all() and (it > 0).all()
+    for s in range(0, B, chunk):
+        e = min(B, s + chunk)
+        x, y = out["x"][s:e, :n], out["y"][s:e, :m]
+        qq, ll, uu = q[s:e, :n], l[s:e, :m], u[s:e, :m]
+        Px = (Pf @ x.T).T
+        Ax = (A @ x.T).T
+        Aty = (A.T @ y.T).T
+        obj = 0.5 * np.einsum("ij,ij->i", x, Px) + np.einsum("ij,ij->i", qq, x)
+        dres = np.abs(Px + qq + Aty).max(axis=1)
+        ok = st[s:e] == 1
+        # P2 (the returned x, y are the iterates the residuals were computed from)
+        assert np.allclose(obj, out["obj"][s:e], rtol=1e-9, atol=1e-9), np.abs(obj - out["obj"][s:e]).max()
+        assert np.allclose(dres, out["dua_res"][s:e], rtol=1e-6, atol=1e-11), np.abs(dres - out["dua_res"][s:e]).max()
+        # P3
+        nrm = lambda v: np.abs(v).max(axis=1)
+        eps_d = EPS + EPS * np.maximum(np.maximum(nrm(Px), nrm(Aty)), nrm(qq))
+        assert (dres[ok] < eps_d[ok]).all()
+        pres = out["pri_res"][s:e]
+        dist = np.maximum(np.maximum(ll - Ax, Ax - uu), 0.0).max(axis=1)
+        assert (dist <= pres * (1 + 1e-9) + 1e-12).all(), (dist - pres).max()
+        bnd = np.maximum(nrm(Ax), 1.0) + pres                                           # ||z|| <= ||Ax|| + pri_res
+        assert (pres[ok] < EPS + EPS * bnd[ok]).all()
+        # P4
+        tol = (pres * (1 + 1e-9) + 1e-12)[:, None]
+        noise = 1e-12 * (1.0 + np.abs(y).max(axis=1))[:, None]      # y_i of an inactive row is rounding noise, not 0
+        pos, neg = y > noise, y < -noise
+        assert (np.abs(Ax - uu)[pos] <= np.broadcast_to(tol, y.shape)[pos]).all()
+        assert (np.abs(Ax - ll)[neg] <= np.broadcast_to(tol, y.shape)[neg]).all()
+    return int((st == 1).sum())
+
+
+def _sample_vs_reference(mdl, N, q, l, u, out, n, m, count, seed, **kw):
+    idx = np.sort(np.random.default_rng(seed).choice(q.shape[0], count, replace=False))
+    ref = ref_run(mdl, N, N, q[idx], l[idx], u[idx], [("solve",), ("get",)], **kw)[1]
+    sub = {k: v[idx] for k, v in out.items()}
+    bad = compare(sub, ref, n, m)
+    assert not bad, bad[:5]
+
+
+def _subbatch_invariance(mdl, N, q, l, u, out, n, m, lo, hi, **kw):
+    gb = R.Batch(mdl, N, N, q[lo:hi], l[lo:hi], u[lo:hi], gpu_settings(**kw))
+    assert gb.solve() == 0
+    sub = gb.get()
+    gb.free()
+    bad = compare(sub, {k: v[lo:hi] for k, v in out.items()}, n, m)
+    assert not bad, bad[:5]
+
+
+@pytest.mark.parametrize("name,batch,sample", [("C1", 1024, 48), ("C3", 4096, 24), ("C3", 65536, 32)],
+                         ids=["C2_batch1024", "C3_batch4096_cold", "C5_batch65536"])
+def test_full_size_cold_solves(name, batch, sample):
+    cfg = mpc.CONFIGS[name]
+    mdl = mpc.make_model(cfg)
+    N = cfg["N"]
+    q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch), N)
+    gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+    assert gb.solve() == 0
+    out = gb.get()
+    n, m, _, _ = gb.dims()
+    gb.free()
+    solved = _check_properties(mdl, N, q, l, u, out)
+    assert solved >= batch - max(1, batch // 10000), solved      # C5: one instance of 65 536 ends at max_iter
+    _sample_vs_reference(mdl, N, q, l, u, out, n, m, sample, seed=batch)
+    _subbatch_invariance(mdl, N, q, l, u, out, n, m, batch // 2, batch // 2 + 40)
+
+
+def test_full_size_adaptive_rho_C4():
+    """C4: batch 2 048, adaptive rho every 25 iterations, rho_0 per instance from {1e-3, 10}; sample
+    against the reference's stock path."""
+    cfg = mpc.CONFIGS["C4"]
+    mdl = mpc.make_model(cfg)
+    N, batch = cfg["N"], 2048
+    q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch), N)
+    rho = np.where(np.arange(batch) % 2 == 0, 1e-3, 10.0)
+    kw = dict(adaptive_rho=1, adaptive_rho_interval=25, adaptive_rho_tolerance=1.5)
+    gb = R.Batch(mdl, N, N, q, l, u, gpu_settings(**kw), rho=rho)
+    assert gb.solve() == 0
+    out = gb.get()
+    n, m, _, _ = gb.dims()
+    gb.free()
+    assert _check_properties(mdl, N, q, l, u, out) == batch
+    idx = np.sort(np.random.default_rng(4).choice(batch, 24, replace=False))
+    ref = ref_run(mdl, N, N, q[idx], l[idx], u[idx], [("solve",), ("get",)], path="stock", rho=rho[idx], **kw)[1]
+    sub = {k: v[idx] for k, v in out.items()}
+    bad = compare(sub, ref, n, m)
+    assert not bad, bad[:5]
+    assert (sub["rho_updates"] == ref["rho_updates"]).all()
+
+
+def test_full_size_warm_restart_is_idempotent():
+    """Warm-starting every instance of a C3-sized batch at its own solution ends at the first
+    termination check with the same solution (reference tests/basic_qp 'warm start at optimum')."""
+    cfg = mpc.CONFIGS["C3"]
+    mdl = mpc.make_model(cfg)
+    N, batch = cfg["N"], 4096
+    q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch), N)
+    gb = R.Batch(mdl, N, N, q, l, u, gpu_settings(warm_start=1))
+    assert gb.solve() == 0
+    cold = gb.get()
+    assert gb.warm_start(cold["x"], cold["y"]) == 0
+    assert gb.solve() == 0
+    warm = gb.get()
+    n, m, _, _ = gb.dims()
+    gb.free()
+    ok = cold["status"] == 1
+    assert (warm["status"][ok] == 1).all()
+    assert (warm["iter"][ok] <= cold["iter"][ok]).all()
+    assert (warm["iter"][ok] == 25).mean() > 0.95
+    scale = np.abs(cold["x"][ok]).max()
+    assert np.abs(warm["x"][ok, :n] - cold["x"][ok, :n]).max() <= 1e-3 * scale      # both within eps of x*
+    assert np.allclose(warm["obj"][ok], cold["obj"][ok], rtol=1e-4)
+    idx = np.sort(np.random.default_rng(5).choice(batch, 24, replace=False))      # the same restart on the reference
+    ref = ref_run(mdl, N, N, q[idx], l[idx], u[idx], [("warm_start", cold["x"][idx], cold["y"][idx]), ("solve",),
+                                                      ("get",)], warm_start=1)[2]
+    bad = compare({k: v[idx] for k, v in warm.items()}, ref, n, m)
+    assert not bad, bad[:5]
