@@ -213,3 +213,98 @@ def make_model(cfg: dict) -> MPCModel:
     if cfg["model"] == "quadcopter":
         return quadcopter_model()
     return random_model(cfg["nx"], cfg["nu"])
+
+
+@dataclasses.dataclass
+class PolytopicModel(MPCModel):
+    """General stage blocks the reference's entry point admits (include/recursive_ldl.h:17-50):
+    ny polytopic path rows C (x_k,u_k) with several variables per row, nt terminal rows CN x_N,
+    and a stage cost with state-input cross terms S.  Stage 0 keeps the input columns of C
+    (x0 is data).  xmin/xmax/umin/umax of the base class are unused."""
+    C: np.ndarray = None       # ny x (nx+nu)
+    CN: np.ndarray = None      # nt x nx
+    S: np.ndarray = None       # nx x nu cross cost
+    cmin: np.ndarray = None
+    cmax: np.ndarray = None
+    tmin: np.ndarray = None
+    tmax: np.ndarray = None
+
+    @property
+    def ny(self):
+        return self.C.shape[0]
+
+    @property
+    def nt(self):
+        return self.CN.shape[0]
+
+    def dense_blocks(self):
+        nx, nu, ny = self.nx, self.nu, self.ny
+        a, b = nx + nu, nx + ny
+        Qi = np.zeros((a, a)); Qi[:nx, :nx] = self.Q; Qi[nx:, nx:] = self.R
+        Qi[:nx, nx:] = self.S; Qi[nx:, :nx] = self.S.T
+        A0 = np.zeros((b, nu)); A0[:ny, :] = self.C[:, nx:]; A0[ny:, :] = self.B
+        Ai = np.zeros((b, a)); Ai[:ny, :] = self.C; Ai[ny:, :nx] = self.A; Ai[ny:, nx:] = self.B
+        Aij = np.zeros((b, a)); Aij[ny:, :nx] = -np.eye(nx)
+        return dict(Q0=self.R.copy(), Qi=Qi, QN=self.Q.copy(), A0=A0, Ai=Ai, Aij=Aij, AN=self.CN.copy())
+
+    def stage_matrices(self):
+        d = self.dense_blocks()
+        return [_csc_full(d["Q0"], True), _csc_full(d["Qi"], True), _csc_full(d["QN"], True),
+                _csc_sparse(d["A0"]), _csc_sparse(d["Ai"]), _csc_sparse(d["Aij"]), _csc_sparse(d["AN"])]
+
+    def vectors(self, x0, N, Nmax=None):
+        Nmax = N if Nmax is None else Nmax
+        x0 = np.atleast_2d(np.asarray(x0, np.float64))
+        B_ = x0.shape[0]
+        nx, nu, ny, nt = self.nx, self.nu, self.ny, self.nt
+        a, b = nx + nu, nx + ny
+        n, m = Nmax * a, Nmax * b + nt
+        q = np.zeros((B_, n)); l = np.zeros((B_, m)); u = np.zeros((B_, m))
+        qx = -self.Q @ self.xr
+        for k in range(1, Nmax + 1):
+            off = nu + (k - 1) * a
+            q[:, off:off + nx] = qx
+        for k in range(Nmax):
+            r = k * b
+            l[:, r:r + ny] = self.cmin; u[:, r:r + ny] = self.cmax
+        dyn0 = -(x0 @ self.A.T)
+        l[:, ny:ny + nx] = dyn0; u[:, ny:ny + nx] = dyn0
+        for NN in sorted({N, Nmax}, reverse=True):   # the current terminal rows last
+            r = NN * b
+            l[:, r:r + nt] = self.tmin; u[:, r:r + nt] = self.tmax
+        return q, l, u
+
+    def assemble(self, N):
+        d = self.dense_blocks()
+        nx, nu, nt = self.nx, self.nu, self.nt
+        a, b = nx + nu, nx + self.ny
+        n, m = N * a, N * b + nt
+        P = np.zeros((n, n)); A = np.zeros((m, n))
+        P[:nu, :nu] = d["Q0"]; A[:b, :nu] = d["A0"]
+        for k in range(1, N):
+            c = nu + (k - 1) * a
+            P[c:c + a, c:c + a] = d["Qi"]
+            A[(k - 1) * b:k * b, c:c + a] += d["Aij"]
+            A[k * b:(k + 1) * b, c:c + a] += d["Ai"]
+        c = nu + (N - 1) * a
+        P[c:c + nx, c:c + nx] = d["QN"]
+        A[(N - 1) * b:N * b, c:c + nx] += d["Aij"][:, :nx]
+        A[N * b:N * b + nt, c:c + nx] += d["AN"]
+        return sp.csc_matrix(np.triu(P)), sp.csc_matrix(A)
+
+
+def polytopic_model(nx: int, nu: int, ny: int, nt: int, seed: int = 4321) -> PolytopicModel:
+    """Random stable-ish dynamics, dense polytopic path/terminal rows, cross-term cost.  The LAST path
+    row is loose (the reference types its terminal rows from the first nt rows of stage Nmax-1, SURVEY
+    §8c F3, so those must be plain inequalities like the terminal rows for its recursive path to be right)."""
+    base = random_model(nx, nu, seed)
+    rng = np.random.default_rng(seed + 1)
+    a = nx + nu
+    Cm = rng.uniform(-1.0, 1.0, (ny, a))
+    CN = rng.uniform(-1.0, 1.0, (nt, nx))
+    S = 0.02 * rng.uniform(-1.0, 1.0, (nx, nu))
+    cmin = -rng.uniform(1.0, 3.0, ny); cmax = rng.uniform(1.0, 3.0, ny)
+    cmin[-1] = -INF; cmax[-1] = INF
+    tmin = -rng.uniform(1.0, 2.0, nt); tmax = rng.uniform(1.0, 2.0, nt)
+    return PolytopicModel(nx, nu, base.A, base.B, base.Q, base.R, base.xmin, base.xmax, base.umin, base.umax,
+                          0.3 * np.ones(nx), 0.5, C=Cm, CN=CN, S=S, cmin=cmin, cmax=cmax, tmin=tmin, tmax=tmax)
