@@ -347,6 +347,27 @@ void  get_L_dimensions(OSQPWorkspace *work, c_int *n, c_int *m, c_int *nnz);
 /* recursive_ldl.h:52 (src/recursive_ldl.c:15) */
 void  cleanup_rldl(OSQPDataRLDL *data);
 
+/* =====================  reference include/cs.h, include/util.h  ===================== */
+/* Host-side data-format helpers a user program builds its inputs with (memory from malloc/calloc,
+ * i.e. the desktop build's c_malloc/c_calloc, glob_opts.h:64-66).  No numerical work. */
+
+/* util.h:19 */
+const char *osqp_version(void);
+/* cs.h:26 — wraps caller-owned x,i,p (no copies) */
+csc  *csc_matrix(c_int m, c_int n, c_int nzmax, c_float *x, c_int *i, c_int *p);
+/* cs.h:44 — allocates p,i (and x when values != 0); triplet form when triplet != 0 */
+csc  *csc_spalloc(c_int m, c_int n, c_int nzmax, c_int values, c_int triplet);
+/* cs.h:51 — frees p,i,x and the struct */
+void  csc_spfree(csc *A);
+/* cs.h:70 */
+csc  *copy_csc_mat(const csc *A);
+/* cs.h:76 — copy into an already allocated B */
+void  prea_copy_csc_mat(const csc *A, csc *B);
+/* cs.h:92 — triplet form to CSC; TtoC (optional) receives the position of every triplet */
+csc  *triplet_to_csc(const csc *T, c_int *TtoC);
+/* cs.h:113 — upper triangle (with diagonal) of a square CSC matrix, newly allocated */
+csc  *csc_to_triu(csc *M);
+
 /* =====================  additive batch API (new)  ===================== */
 /* One handle = `batch` independent QP instances that share the stage model in
  * `model` (dims + Q0,Qi,QN,A0,Ai,Aij,AN) and differ in q, l, u (and optionally

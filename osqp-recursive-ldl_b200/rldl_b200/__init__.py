@@ -99,6 +99,7 @@ class OSQPDataRLDL(C.Structure):
 
 # every symbol include/osqp_rldl_abi.h declares
 ABI_SYMBOLS = """
+osqp_version csc_matrix csc_spalloc csc_spfree copy_csc_mat prea_copy_csc_mat triplet_to_csc csc_to_triu
 osqp_set_default_settings osqp_setup osqp_solve osqp_cleanup osqp_update_lin_cost osqp_update_bounds
 osqp_update_lower_bound osqp_update_upper_bound osqp_warm_start osqp_warm_start_x osqp_warm_start_y
 osqp_update_P osqp_update_A osqp_update_P_A osqp_update_rho osqp_update_max_iter osqp_update_eps_abs

@@ -1,0 +1,29 @@
+"""Drop-in boundary on the GPU: ONE object file, compiled from tests/dropin/mpc_user.c against the
+reference's own headers, linked once against the unmodified reference and once against
+librldl_b200.so.  Both programs must print the same closed-loop MPC run (cold solve, two plant steps
+with osqp_partial_update_bounds + osqp_warm_start, osqp_update_lin_cost, osqp_update_recursive shrink and
+grow, osqp_update_bounds + tighter tolerances, a refused invalid bound update): same return codes,
+dimensions, status and iteration count at every solve, x / y / objective within 1e-6 relative
+(north_star).  The golden fixture is the reference-linked program's output committed from the build
+container; on a box that carries oracle/_ref the reference-linked program is also run live."""
+import os
+
+import pytest
+
+from dropin_common import GOLDEN, assert_same_run, binary, parse, run
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 1e-6
+
+
+@pytest.mark.parametrize("name", ["dropin_b200", "dropin_b200_ownhdr"])
+def test_user_program_linked_against_the_product_matches_the_reference(name):
+    assert os.path.exists(binary(name)), f"{name} not built: run `python __graft_entry__.py`"
+    cp = run(name)
+    assert cp.returncode == 0, (cp.returncode, cp.stdout[-500:], cp.stderr[-2000:])
+    got = parse(cp.stdout)
+    assert_same_run(got, parse(open(GOLDEN).read()), REL_TOL, f"{name} vs golden")
+    if os.path.exists(binary("dropin_ref")):
+        ref = run("dropin_ref")
+        assert ref.returncode == 0, ref.stderr[-2000:]
+        assert_same_run(got, parse(ref.stdout), REL_TOL, f"{name} vs live reference")
