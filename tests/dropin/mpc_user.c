@@ -16,9 +16,8 @@
  * caller-visible fields work->info->{status_val,status,iter,obj_val,pri_res,dua_res},
  * work->solution->{x,y}, work->data->{n,m}.
  *
- * The instance: nx=4, nu=2, N=20 (BASELINE config C1), box constraints on state and input
- * (ny = nx+nu, C = I), terminal box (nt = nx, AN = I), Nmax = N+1 and cost blocks stored as full
- * upper triangles (where the reference's own recursive path is well defined).
+ * The instance (mpc_model.h): nx=4, nu=2, N=20 (BASELINE config C1), box constraints on state and
+ * input, terminal box, Nmax = N+1, cost blocks stored as full upper triangles.
  * osqp_cleanup is not called: on a recursive workspace it is undefined behaviour in the
  * reference (F5), and this object file must run against it.
  */
@@ -33,42 +32,7 @@
 #include "cs.h"
 #endif
 
-#define NX 4
-#define NU 2
-#define NA (NX + NU)      /* stage variables */
-#define NY (NX + NU)      /* path rows */
-#define NB (NX + NY)      /* stage constraint rows */
-#define NT NX
-#define HN 20
-#define HNMAX 21
-#define BIG 1e30
-
-static unsigned long long lcg_state = 20261104ULL;
-static double urand(void) { /* U(-0.5, 0.5) */
-  lcg_state = lcg_state * 6364136223846793005ULL + 1442695040888963407ULL;
-  return (double)(lcg_state >> 11) / 9007199254740992.0 - 0.5;
-}
-
-/* dense column-major (rows x cols) -> CSC: upper != 0 keeps the whole upper triangle with explicit zeros
- * (cost blocks, F4), upper == 0 keeps the non-zero entries only (constraint blocks) */
-static csc *dense_to_csc(const double *M, int rows, int cols, int upper) {
-  c_int *p = (c_int *)malloc(sizeof(c_int) * (cols + 1));
-  c_int *i = (c_int *)malloc(sizeof(c_int) * rows * cols);
-  c_float *x = (c_float *)malloc(sizeof(c_float) * rows * cols);
-  c_int nnz = 0;
-  for (int j = 0; j < cols; j++) {
-    p[j] = nnz;
-    for (int r = 0; r < rows; r++) {
-      if (upper && r > j) break;
-      if (!upper && M[j * rows + r] == 0.0) continue;
-      i[nnz] = r;
-      x[nnz] = M[j * rows + r];
-      nnz++;
-    }
-  }
-  p[cols] = nnz;
-  return csc_matrix(rows, cols, nnz, x, i, p);
-}
+#include "mpc_model.h"
 
 static void report(const char *tag, OSQPWorkspace *w) {
   c_int n = w->data->n, m = w->data->m;
@@ -83,42 +47,9 @@ static void report(const char *tag, OSQPWorkspace *w) {
 }
 
 int main(void) {
-  double A[NX * NX], B[NX * NU], Q[NX * NX], R[NU * NU]; /* column-major */
-  for (int j = 0; j < NX; j++)
-    for (int r = 0; r < NX; r++) A[j * NX + r] = (r == j ? 0.9 : 0.0) + 0.1 * urand();
-  for (int k = 0; k < NX * NU; k++) B[k] = urand();
-  for (int j = 0; j < NX; j++)
-    for (int r = 0; r < NX; r++) Q[j * NX + r] = (r == j) ? 1.0 : 0.01 / (1 + abs(r - j));
-  for (int j = 0; j < NU; j++)
-    for (int r = 0; r < NU; r++) R[j * NU + r] = (r == j) ? 0.1 : 0.01 / (1 + abs(r - j));
-
-  /* stage blocks (recursive_ldl.h:30-36) */
-  double Qi[NA * NA] = {0}, A0[NB * NU] = {0}, Ai[NB * NA] = {0}, Aij[NB * NA] = {0}, AN[NT * NX] = {0};
-  for (int j = 0; j < NX; j++)
-    for (int r = 0; r < NX; r++) Qi[j * NA + r] = Q[j * NX + r];
-  for (int j = 0; j < NU; j++)
-    for (int r = 0; r < NU; r++) Qi[(NX + j) * NA + NX + r] = R[j * NU + r];
-  for (int j = 0; j < NU; j++) {
-    A0[j * NB + NX + j] = 1.0;                                         /* u0 box rows */
-    for (int r = 0; r < NX; r++) A0[j * NB + NY + r] = B[j * NX + r];  /* B u0 - x1 = -A x0 */
-  }
-  for (int j = 0; j < NA; j++) {
-    Ai[j * NB + j] = 1.0; /* C = I */
-    for (int r = 0; r < NX; r++) Ai[j * NB + NY + r] = (j < NX) ? A[j * NX + r] : B[(j - NX) * NX + r];
-  }
-  for (int j = 0; j < NX; j++) Aij[j * NB + NY + j] = -1.0;
-  for (int j = 0; j < NX; j++) AN[j * NT + j] = 1.0;
-
+  double A[NX * NX], B[NX * NU]; /* column-major */
   OSQPDataRLDL *d = (OSQPDataRLDL *)calloc(1, sizeof(OSQPDataRLDL));
-  /* the reference reads the dimensions from the struct as well as from the arguments */
-  d->Nmax = HNMAX; d->N = HN; d->nx = NX; d->nu = NU; d->ny = NY; d->nt = NT;
-  d->Q0 = dense_to_csc(R, NU, NU, 1);
-  d->Qi = dense_to_csc(Qi, NA, NA, 1);
-  d->QN = dense_to_csc(Q, NX, NX, 1);
-  d->A0 = dense_to_csc(A0, NB, NU, 0);
-  d->Ai = dense_to_csc(Ai, NB, NA, 0);
-  d->Aij = dense_to_csc(Aij, NB, NA, 0);
-  d->AN = dense_to_csc(AN, NT, NX, 0);
+  build_model(d, A, B);
 
   /* q, l, u sized for Nmax, bounds pre-filled stage-like up to Nmax */
   const c_int nmax = HNMAX * NA, mmax = HNMAX * NB + NT;
@@ -127,25 +58,7 @@ int main(void) {
   c_float *u = (c_float *)calloc(mmax, sizeof(c_float));
   double x0[NX], dyn0[NX];
   for (int r = 0; r < NX; r++) x0[r] = 8.0 * urand();
-  for (int k = 0; k < HNMAX; k++) {
-    for (int r = 0; r < NX; r++) {
-      l[k * NB + r] = k == 0 ? -BIG : -5.0;
-      u[k * NB + r] = k == 0 ? BIG : 5.0;
-    }
-    for (int r = 0; r < NU; r++) {
-      l[k * NB + NX + r] = -0.5;
-      u[k * NB + NX + r] = 0.5;
-    }
-  }
-  for (int r = 0; r < NT; r++) {
-    l[HNMAX * NB + r] = -5.0;
-    u[HNMAX * NB + r] = 5.0;
-  }
-  for (int r = 0; r < NX; r++) {
-    dyn0[r] = 0.0;
-    for (int j = 0; j < NX; j++) dyn0[r] -= A[j * NX + r] * x0[j];
-    l[NY + r] = u[NY + r] = dyn0[r];
-  }
+  fill_bounds(A, x0, l, u);
   d->data.n = nmax;
   d->data.m = mmax;
   d->data.q = q;

@@ -27,3 +27,17 @@ def test_user_program_linked_against_the_product_matches_the_reference(name):
         ref = run("dropin_ref")
         assert ref.returncode == 0, ref.stderr[-2000:]
         assert_same_run(got, parse(ref.stdout), REL_TOL, f"{name} vs live reference")
+
+
+@pytest.mark.parametrize("batch,threads", [(2048, 3), (64, 4)])
+def test_c_host_sharding_over_threads_and_devices_agrees_with_one_handle(batch, threads):
+    """SURVEY §8e from a C host (tests/dropin/sharded_user.c): contiguous shards, one host thread and one
+    RLDLBatch handle per shard, thread t on device t % G, no collective; same status / iterations / x / y as
+    the whole batch through one handle, for a cold solve and a shifted warm-started closed-loop step."""
+    import subprocess
+    exe = binary("sharded_b200")
+    assert os.path.exists(exe), "sharded_b200 not built: run `python __graft_entry__.py`"
+    cp = subprocess.run([exe, str(batch), str(threads)], capture_output=True, text=True, timeout=600)
+    assert cp.returncode == 0, (cp.returncode, cp.stdout[-1500:], cp.stderr[-1500:])
+    assert "SHARDED OK" in cp.stdout and cp.stdout.count("AGREE solve") == 2
+    assert cp.stdout.count("SHARD ") >= threads
