@@ -73,6 +73,9 @@ static cudaError_t dalloc(T **p, size_t count) {
   if (!count) count = 1;
   cudaError_t e = cudaMalloc((void **)p, count * sizeof(T));
   if (e == cudaSuccess) e = cudaMemset(*p, 0, count * sizeof(T));
+  // the memset runs on the legacy default stream and the handle's stream is non-blocking (no implicit order
+  // with it): without this wait a fill delayed by other host threads' work can land after the handle's first writes
+  if (e == cudaSuccess) e = cudaStreamSynchronize(0);
   return e;
 }
 
@@ -150,6 +153,7 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
   CK(cudaMalloc(&d_midx, mb.idx.size() * sizeof(int)));
   CK(cudaMemcpy(d_mval, mb.val.data(), mb.val.size() * sizeof(double), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(d_midx, mb.idx.data(), mb.idx.size() * sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaStreamSynchronize(0));  // pageable copies may still be in flight on the default stream when cudaMemcpy returns
   Md.val = d_mval; Md.idx = d_midx; Md.nval = (int)mb.val.size();
   if (D.rec) return configure_stream();  // a P / A update may change which specialisation serves the model
   return 0;

@@ -174,6 +174,17 @@ int main(int argc, char **argv) {
     printf("AGREE solve %d batch %lld threads %d devices %d solved %lld status_diff %lld iter_diff %lld x_rel %.3g y_rel %.3g\n",
            p + 1, (long long)batch, T, G, (long long)solved, (long long)diff_status, (long long)diff_iter,
            ex / fmax(nx_, 1e-12), ey / fmax(ny_, 1e-12));
+    for (int t = 0; t < T && (diff_status || diff_iter); t++) { /* which shards, and what they hold */
+      c_int ds = 0, di = 0;
+      for (c_int i = sh[t].i0; i < sh[t].i1; i++) {
+        ds += status[0][p][i] != status[1][p][i];
+        di += iter[0][p][i] != iter[1][p][i];
+      }
+      if (ds || di)
+        printf("  shard %d: %lld status / %lld iteration mismatches; first instance: status %lld vs %lld, iter %lld vs %lld\n",
+               t, (long long)ds, (long long)di, (long long)status[1][p][sh[t].i0], (long long)status[0][p][sh[t].i0],
+               (long long)iter[1][p][sh[t].i0], (long long)iter[0][p][sh[t].i0]);
+    }
     /* at least some instances must be plain solves, none may disagree */
     bad |= diff_status != 0 || diff_iter != 0 || ex > 1e-9 * fmax(nx_, 1e-12) || ey > 1e-9 * fmax(ny_, 1e-12) ||
            solved == 0;

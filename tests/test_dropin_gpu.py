@@ -29,7 +29,7 @@ def test_user_program_linked_against_the_product_matches_the_reference(name):
         assert_same_run(got, parse(ref.stdout), REL_TOL, f"{name} vs live reference")
 
 
-@pytest.mark.parametrize("batch,threads", [(2048, 3), (64, 4)])
+@pytest.mark.parametrize("batch,threads", [(2048, 3), (64, 4), (4096, 8)])
 def test_c_host_sharding_over_threads_and_devices_agrees_with_one_handle(batch, threads):
     """SURVEY §8e from a C host (tests/dropin/sharded_user.c): contiguous shards, one host thread and one
     RLDLBatch handle per shard, thread t on device t % G, no collective; same status / iterations / x / y as
