@@ -1,0 +1,160 @@
+/* tests/dropin/api_user.c — TEST INFRASTRUCTURE.
+ *
+ * Second user program compiled ONCE against the reference's own headers and linked against the
+ * reference and against librldl_b200.so (see mpc_user.c).  It takes the remaining entry points of
+ * the boundary through the same object file:
+ *   part A — the stock API on a small generic QP (the reference's own basic_qp test problem,
+ *     tests/basic_qp/generate_problem.py): osqp_setup, osqp_solve, osqp_update_lin_cost,
+ *     osqp_update_lower_bound / _upper_bound, osqp_warm_start_x / _y, osqp_update_rho,
+ *     osqp_update_P_A (new values, same pattern), osqp_update_max_iter, osqp_cleanup;
+ *   part B — the combine variant on the C1-shaped MPC of mpc_model.h:
+ *     osqp_setup_combine_recursive (head 15 + tail 3), osqp_solve_combine_recursive,
+ *     osqp_update_Z_horizon (tail +2).
+ */
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef RLDL_OWN_HEADER
+#include "osqp_rldl_abi.h"
+#else
+#include "osqp.h"
+#include "recursive_ldl.h"
+#include "cs.h"
+#endif
+#include "mpc_model.h"
+
+static void report(const char *tag, OSQPWorkspace *w, c_int rc) {
+  c_int n = w->data->n, m = w->data->m;
+  printf("SOLVE %s rc %lld n %lld m %lld status_val %lld iter %lld obj %.17g status \"%s\"\n", tag, (long long)rc,
+         (long long)n, (long long)m, (long long)w->info->status_val, (long long)w->info->iter, w->info->obj_val,
+         w->info->status);
+  printf("X %s", tag);
+  for (c_int k = 0; k < n; k++) printf(" %.17g", w->solution->x[k]);
+  printf("\nY %s", tag);
+  for (c_int k = 0; k < m; k++) printf(" %.17g", w->solution->y[k]);
+  printf("\n");
+}
+
+static int part_a(void) {
+  /* minimize 1/2 x'Px + q'x  s.t. l <= Ax <= u ;  P upper triangle */
+  c_float P_x[3] = {4.0, 1.0, 2.0};
+  c_int P_i[3] = {0, 0, 1}, P_p[3] = {0, 1, 3};
+  c_float q[2] = {1.0, 1.0};
+  c_float A_x[4] = {1.0, 1.0, 1.0, 1.0};
+  c_int A_i[4] = {0, 1, 0, 2}, A_p[3] = {0, 2, 4};
+  c_float l[3] = {1.0, 0.0, 0.0}, u[3] = {1.0, 0.7, 0.7};
+  OSQPData *data = (OSQPData *)calloc(1, sizeof(OSQPData));
+  data->n = 2;
+  data->m = 3;
+  data->P = csc_matrix(2, 2, 3, P_x, P_i, P_p);
+  data->q = q;
+  data->A = csc_matrix(3, 2, 4, A_x, A_i, A_p);
+  data->l = l;
+  data->u = u;
+  OSQPSettings *s = (OSQPSettings *)malloc(sizeof(OSQPSettings));
+  osqp_set_default_settings(s);
+  s->scaling = 0;
+  s->adaptive_rho = 0;
+  s->eps_abs = s->eps_rel = 1e-6;
+  s->check_termination = 5;
+  s->verbose = 0;
+  s->polish = 0;
+  s->warm_start = 1;
+  OSQPWorkspace *w = NULL;
+  c_int rc = osqp_setup(&w, data, s);
+  printf("SETUP generic rc %lld\n", (long long)rc);
+  if (rc) return 10 + (int)rc;
+  rc = osqp_solve(w);
+  report("qp", w, rc);
+
+  c_float q2[2] = {2.5, 3.2};
+  rc = osqp_update_lin_cost(w, q2);
+  rc |= osqp_solve(w);
+  report("qp_lincost", w, rc);
+
+  c_float l2[3] = {0.8, -0.1, -0.2}, u2[3] = {1.6, 0.9, 0.5};
+  rc = osqp_update_lower_bound(w, l2);
+  rc |= osqp_update_upper_bound(w, u2);
+  rc |= osqp_solve(w);
+  report("qp_bounds", w, rc);
+
+  c_float xw[2] = {0.3, 0.5}, yw[3] = {-2.0, 0.0, 0.1};
+  rc = osqp_warm_start_x(w, xw);
+  rc |= osqp_solve(w);
+  report("qp_warm_x", w, rc);
+  rc = osqp_warm_start_y(w, yw);
+  rc |= osqp_solve(w);
+  report("qp_warm_y", w, rc);
+
+  rc = osqp_update_rho(w, 0.7);
+  rc |= osqp_warm_start(w, xw, yw);
+  rc |= osqp_solve(w);
+  report("qp_rho", w, rc);
+
+  c_float P_new[3] = {5.0, 1.5, 1.0}, A_new[4] = {1.2, 1.5, 1.1, 0.8};
+  rc = osqp_update_P_A(w, P_new, NULL, 3, A_new, NULL, 4);
+  rc |= osqp_solve(w);
+  report("qp_P_A", w, rc);
+
+  /* iteration limit below the first termination check.  osqp_update_lin_cost comes first because only the
+   * data updates reset info->status_val: without one the reference leaves the previous solve's "solved" in
+   * place when the loop runs out (src/osqp.c:570 tests for OSQP_UNSOLVED), whatever the residuals are */
+  rc = osqp_update_max_iter(w, 3);
+  rc |= osqp_update_lin_cost(w, q);
+  rc |= osqp_warm_start(w, xw, yw);
+  rc |= osqp_solve(w);
+  report("qp_max_iter", w, rc);
+  printf("BADRHO rc %lld\n", (long long)osqp_update_rho(w, -1.0));
+  printf("CLEANUP rc %lld\n", (long long)osqp_cleanup(w));
+  return 0;
+}
+
+static int part_b(void) {
+  double A[NX * NX], B[NX * NU];
+  OSQPDataRLDL *d = (OSQPDataRLDL *)calloc(1, sizeof(OSQPDataRLDL));
+  build_model(d, A, B);
+  const c_int nmax = HNMAX * NA, mmax = HNMAX * NB + NT;
+  c_float *q = (c_float *)calloc(nmax, sizeof(c_float));
+  c_float *l = (c_float *)calloc(mmax, sizeof(c_float));
+  c_float *u = (c_float *)calloc(mmax, sizeof(c_float));
+  double x0[NX];
+  for (int r = 0; r < NX; r++) x0[r] = 8.0 * urand();
+  fill_bounds(A, x0, l, u);
+  d->data.n = nmax;
+  d->data.m = mmax;
+  d->data.q = q;
+  d->data.l = l;
+  d->data.u = u;
+  OSQPSettings *s = (OSQPSettings *)malloc(sizeof(OSQPSettings));
+  osqp_set_default_settings(s);
+  s->scaling = 0;
+  s->adaptive_rho = 0;
+  s->eps_abs = s->eps_rel = 1e-5;
+  s->check_termination = 25;
+  s->verbose = 0;
+  s->polish = 0;
+  s->warm_start = 1;
+  OSQPWorkspace *w = NULL;
+  const c_int head = 15, tail = 3;
+  d->N = head + tail;
+  c_int rc = osqp_setup_combine_recursive(&w, d, s, HNMAX, head, tail, NX, NU, NY, NT);
+  printf("SETUP combine rc %lld\n", (long long)rc);
+  if (rc) return 10 + (int)rc;
+  rc = osqp_solve_combine_recursive(w);
+  report("combine", w, rc);
+  rc = osqp_update_Z_horizon(w, d, 2);
+  rc |= osqp_solve_combine_recursive(w);
+  report("combine_grow", w, rc);
+  /* no tail shrink here: after osqp_update_Z_horizon(-1) the reference itself ends in "problem non convex"
+   * with a garbage objective on this instance (as it does for -2 from 15+5), so there is nothing to compare
+   * with; the product's shrink is checked against a fresh setup in tests/test_api_gpu.py */
+  return 0;
+}
+
+int main(int argc, char **argv) {
+  int which = argc > 1 ? atoi(argv[1]) : 3, rc = 0;
+  if (which & 1) rc = part_a();
+  if (!rc && (which & 2)) rc = part_b();
+  printf("DONE rc %d\n", rc);
+  return rc;
+}

@@ -8,7 +8,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "oracle", "_ref")
 GOLDEN = os.path.join(ROOT, "tests", "golden", "dropin_mpc_user_ref.txt")
-TAGS = ["cold", "step1", "step2", "lincost", "shrink", "grow", "tight"]
+GOLDEN_API = os.path.join(ROOT, "tests", "golden", "dropin_api_user_ref.txt")
 
 
 def binary(name):
@@ -20,25 +20,24 @@ def run(name, timeout=300):
 
 
 def parse(text):
-    """-> {"setup_rc", "dims", "badbounds_rc", "done_rc", "solves": {tag: {...}}}"""
-    out = {"solves": {}}
+    """-> {"rc": {line: value}, "dims": (n, m), "solves": {tag: {n, m, status_val, iter, obj, ..., status, x, y}}}"""
+    out = {"solves": {}, "rc": {}}
     for line in text.splitlines():
         w = line.split()
         if not w:
             continue
-        if w[0] == "SETUP":
-            out["setup_rc"] = int(w[2])
+        if w[0] in ("SETUP", "BADBOUNDS", "BADRHO", "CLEANUP", "DONE") and "rc" in w:
+            out["rc"][" ".join(w[:w.index("rc")])] = int(w[w.index("rc") + 1])
         elif w[0] == "DIMS":
             out["dims"] = (int(w[2]), int(w[4]))
-        elif w[0] == "BADBOUNDS":
-            out["badbounds_rc"] = int(w[2])
-        elif w[0] == "DONE":
-            out["done_rc"] = int(w[2])
         elif w[0] == "SOLVE":
             rec = out["solves"].setdefault(w[1], {})
-            rec.update(n=int(w[3]), m=int(w[5]), status_val=int(w[7]), iter=int(w[9]), obj=float(w[11]),
-                       pri=float(w[13]), dua=float(w[15]), status=line.split('"')[1])
-        elif w[0] in ("X", "Y") and len(w) > 1 and w[1] in TAGS:
+            k = 2
+            while k + 1 < len(w) and w[k] != "status":
+                rec[w[k]] = float(w[k + 1]) if w[k] in ("obj", "pri", "dua") else int(w[k + 1])
+                k += 2
+            rec["status"] = line.split('"')[1]
+        elif w[0] in ("X", "Y") and len(w) > 1:
             out["solves"].setdefault(w[1], {})[w[0].lower()] = np.array([float(v) for v in w[2:]])
     return out
 
@@ -49,13 +48,13 @@ def rel(a, b):
 
 def assert_same_run(got, want, tol, what):
     """Same return codes, dimensions, status and iteration count at every solve; x, y, obj within tol."""
-    for key in ("setup_rc", "dims", "badbounds_rc", "done_rc"):
-        assert got.get(key) == want.get(key), (what, key, got.get(key), want.get(key))
-    assert list(got["solves"]) == TAGS == list(want["solves"]), (what, list(got["solves"]))
-    for tag in TAGS:
-        g, w = got["solves"][tag], want["solves"][tag]
-        for key in ("n", "m", "status_val", "iter", "status"):
-            assert g[key] == w[key], (what, tag, key, g[key], w[key])
+    assert got["rc"] == want["rc"], (what, got["rc"], want["rc"])
+    assert got.get("dims") == want.get("dims"), (what, got.get("dims"), want.get("dims"))
+    assert list(got["solves"]) == list(want["solves"]) and want["solves"], (what, list(got["solves"]))
+    for tag, w in want["solves"].items():
+        g = got["solves"][tag]
+        for key in ("rc", "n", "m", "status_val", "iter", "status"):
+            assert g.get(key) == w.get(key), (what, tag, key, g.get(key), w.get(key))
         assert g["x"].shape == (w["n"],) and g["y"].shape == (w["m"],), (what, tag)
         assert rel(g["x"], w["x"]) < tol, (what, tag, "x", rel(g["x"], w["x"]))
         assert rel(g["y"], w["y"]) < tol, (what, tag, "y", rel(g["y"], w["y"]))

@@ -15,7 +15,7 @@ import numpy as np
 import pytest
 
 import rldl_b200 as R
-from dropin_common import GOLDEN, assert_same_run, binary, parse, run
+from dropin_common import GOLDEN, GOLDEN_API, assert_same_run, binary, parse, run
 
 
 def _need(name):
@@ -28,19 +28,29 @@ def test_reference_linked_user_program_reproduces_the_golden_output():
     cp = run("dropin_ref")
     assert cp.returncode == 0, cp.stderr[-2000:]
     got, want = parse(cp.stdout), parse(open(GOLDEN).read())
-    assert want["setup_rc"] == 0 and want["done_rc"] == 0 and want["badbounds_rc"] == 1
+    assert want["rc"] == {"SETUP": 0, "BADBOUNDS": 1, "DONE": 0} and want["dims"] == (324, 324)
     assert [want["solves"][t]["iter"] for t in want["solves"]] == [175, 125, 75, 75, 50, 50, 175]
     assert_same_run(got, want, 1e-9, "reference vs golden")
 
 
-@pytest.mark.parametrize("name", ["dropin_b200", "dropin_b200_ownhdr"])
+def test_reference_linked_api_program_reproduces_the_golden_output():
+    _need("api_ref")
+    cp = run("api_ref")
+    assert cp.returncode == 0, cp.stderr[-2000:]
+    got, want = parse(cp.stdout), parse(open(GOLDEN_API).read())
+    assert want["rc"] == {"SETUP generic": 0, "BADRHO": 1, "CLEANUP": 0, "SETUP combine": 0, "DONE": 0}
+    assert abs(want["solves"]["qp"]["obj"] - 1.88) < 1e-5          # the reference's basic_qp known answer
+    assert_same_run(got, want, 1e-9, "reference vs golden (api_user)")
+
+
+@pytest.mark.parametrize("name", ["dropin_b200", "dropin_b200_ownhdr", "api_b200"])
 def test_product_linked_user_program_fails_loudly_without_a_device(name):
     _need(name)
     if R.lib().rldl_device_count() > 0:
         pytest.skip("a CUDA device is present; covered by the gpu test")
     cp = run(name)
     assert cp.returncode == 13, (cp.returncode, cp.stderr[-500:])      # 10 + OSQP_LINSYS_SOLVER_LOAD_ERROR
-    assert "SETUP rc 3" in cp.stdout
+    assert "rc 3" in cp.stdout.splitlines()[0] and cp.stdout.startswith("SETUP")
     assert "no CPU path" in cp.stderr
 
 

@@ -10,21 +10,26 @@ import os
 
 import pytest
 
-from dropin_common import GOLDEN, assert_same_run, binary, parse, run
+from dropin_common import GOLDEN, GOLDEN_API, assert_same_run, binary, parse, run
 
 pytestmark = pytest.mark.gpu
 REL_TOL = 1e-6
 
 
-@pytest.mark.parametrize("name", ["dropin_b200", "dropin_b200_ownhdr"])
-def test_user_program_linked_against_the_product_matches_the_reference(name):
+@pytest.mark.parametrize("name,golden,ref_name", [("dropin_b200", GOLDEN, "dropin_ref"),
+                                                  ("dropin_b200_ownhdr", GOLDEN, "dropin_ref"),
+                                                  ("api_b200", GOLDEN_API, "api_ref")])
+def test_user_program_linked_against_the_product_matches_the_reference(name, golden, ref_name):
+    """api_b200 (tests/dropin/api_user.c): the stock API on the reference's basic_qp problem (osqp_setup,
+    osqp_solve, update_lin_cost, update_lower/upper_bound, warm_start_x/_y, update_rho, update_P_A,
+    update_max_iter, cleanup) and the combine variant (setup 15+3, solve, update_Z_horizon +2)."""
     assert os.path.exists(binary(name)), f"{name} not built: run `python __graft_entry__.py`"
     cp = run(name)
     assert cp.returncode == 0, (cp.returncode, cp.stdout[-500:], cp.stderr[-2000:])
     got = parse(cp.stdout)
-    assert_same_run(got, parse(open(GOLDEN).read()), REL_TOL, f"{name} vs golden")
-    if os.path.exists(binary("dropin_ref")):
-        ref = run("dropin_ref")
+    assert_same_run(got, parse(open(golden).read()), REL_TOL, f"{name} vs golden")
+    if os.path.exists(binary(ref_name)):
+        ref = run(ref_name)
         assert ref.returncode == 0, ref.stderr[-2000:]
         assert_same_run(got, parse(ref.stdout), REL_TOL, f"{name} vs live reference")
 
