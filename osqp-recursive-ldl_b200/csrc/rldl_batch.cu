@@ -402,6 +402,17 @@ c_int Batch::factor(int k0, bool only_flagged) {
   return 0;
 }
 
+c_int Batch::failed_factorisations() {
+  if (cudaSetDevice(device) != cudaSuccess) return -1;
+  std::vector<int> flag(batch);
+  if (cudaMemcpyAsync(flag.data(), D.fact_flag, (size_t)batch * sizeof(int), cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+      cudaStreamSynchronize(stream) != cudaSuccess)
+    return -1;
+  c_int bad = 0;
+  for (int v : flag) bad += v != 0;
+  return bad;
+}
+
 c_int Batch::solve() {
   CK(cudaSetDevice(device));
   CK(cudaEventRecord(ev0, stream));

@@ -36,6 +36,17 @@ double now_s() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// osqp_setup fails with OSQP_NONCVX_ERROR when the KKT factorisation does not have n positive pivots
+// (src/osqp.c:214-216 via init_linsys_solver, qdldl_interface.c LDL_factor: "The problem seems to be
+// non-convex").  Here: a non-positive pivot in the stage recursion.  Frees the handle on failure.
+bool noncvx_at_setup(Batch *B) {
+  if (B->failed_factorisations() == 0) return false;
+  fprintf(stderr, "ERROR in LDL_factor: Error in KKT matrix LDL factorization when computing the nonzero elements. "
+                  "The problem seems to be non-convex\n");
+  delete B;
+  return true;
+}
+
 struct PrivSolver {
   struct linsys_solver vt;  // must stay first: work->linsys_solver is cast to LinSysSolver*
   Batch *batch;
@@ -230,6 +241,7 @@ c_int setup_mpc(OSQPWorkspace **workp, OSQPDataRLDL *r, const OSQPSettings *sett
   c_int rc = Batch::create(&B, r->Q0, r->Qi, r->QN, r->A0, r->Ai, r->Aij, r->AN, settings, Nmax, N, nx,
                            nu, ny, nt, 1, r->data.q, r->data.l, r->data.u, nullptr, false);
   if (rc) return osqp_error((int)rc);
+  if (noncvx_at_setup(B)) return osqp_error(OSQP_NONCVX_ERROR);
   OSQPWorkspace *w = nullptr;
   if (alloc_workspace(&w, settings, nmax, mmax)) { delete B; return osqp_error(OSQP_MEM_ALLOC_ERROR); }
   *workp = w;
@@ -365,6 +377,7 @@ c_int osqp_setup(OSQPWorkspace **workp, const OSQPData *data, const OSQPSettings
   c_int rc = Batch::create(&B, nullptr, nullptr, data->P, nullptr, nullptr, nullptr, data->A, settings, 0, 0,
                            data->n, 0, 0, data->m, 1, data->q, data->l, data->u, nullptr, true);
   if (rc) return osqp_error((int)rc);
+  if (noncvx_at_setup(B)) return osqp_error(OSQP_NONCVX_ERROR);
   OSQPWorkspace *w = nullptr;
   if (alloc_workspace(&w, settings, data->n, data->m)) { delete B; return osqp_error(OSQP_MEM_ALLOC_ERROR); }
   *workp = w;

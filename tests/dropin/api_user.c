@@ -9,7 +9,8 @@
  *     osqp_update_P_A (new values, same pattern), osqp_update_max_iter, osqp_cleanup;
  *   part B — the combine variant on the C1-shaped MPC of mpc_model.h:
  *     osqp_setup_combine_recursive (head 15 + tail 3), osqp_solve_combine_recursive,
- *     osqp_update_Z_horizon (tail +2).
+ *     osqp_update_Z_horizon (tail +2);
+ *   part C — the reference's own unconstrained / non_cvx / primal_dual_infeasibility test problems.
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -151,10 +152,112 @@ static int part_b(void) {
   return 0;
 }
 
+
+/* part C — the reference's own small test problems (tests/unconstrained, tests/non_cvx,
+ * tests/primal_dual_infeasibility generate_problem.py): m = 0, a non-convex P refused at setup with
+ * sigma 1e-6 and detected in the loop with sigma 5, optimal / primal infeasible / dual infeasible /
+ * primal infeasible variants of one QP */
+static OSQPSettings *small_settings(void) {
+  OSQPSettings *s = (OSQPSettings *)malloc(sizeof(OSQPSettings));
+  osqp_set_default_settings(s);
+  s->scaling = 0;
+  s->adaptive_rho = 0;
+  s->eps_abs = s->eps_rel = 1e-5;
+  s->check_termination = 1;
+  s->verbose = 0;
+  s->polish = 0;
+  s->warm_start = 0;
+  s->max_iter = 2500;
+  return s;
+}
+
+static int part_c(void) {
+  c_int rc;
+  OSQPWorkspace *w = NULL;
+  { /* unconstrained: x = -P^-1 q, obj -19.2097520268 */
+    c_float P_x[5] = {0.617022, 0.92032449, 0.20011437, 0.50233257, 0.34675589};
+    c_int P_i[5] = {0, 1, 2, 3, 4}, P_p[6] = {0, 1, 2, 3, 4, 5};
+    c_float q[5] = {-1.10593508, -1.65451545, -2.3634686, 1.13534535, -1.01701414};
+    c_int A_p[6] = {0, 0, 0, 0, 0, 0};
+    c_float dummy_x[1] = {0.0}, none[1] = {0.0};
+    c_int dummy_i[1] = {0};
+    OSQPData *data = (OSQPData *)calloc(1, sizeof(OSQPData));
+    data->n = 5;
+    data->m = 0;
+    data->P = csc_matrix(5, 5, 5, P_x, P_i, P_p);
+    data->q = q;
+    data->A = csc_matrix(0, 5, 0, dummy_x, dummy_i, A_p);
+    data->l = none;
+    data->u = none;
+    rc = osqp_setup(&w, data, small_settings());
+    printf("SETUP unconstrained rc %lld\n", (long long)rc);
+    if (rc) return 10 + (int)rc;
+    rc = osqp_solve(w);
+    report("unconstrained", w, rc);
+    osqp_cleanup(w);
+  }
+  { /* non convex */
+    c_float P_x[3] = {2.0, 5.0, 1.0};
+    c_int P_i[3] = {0, 0, 1}, P_p[3] = {0, 1, 3};
+    c_float q[2] = {3.0, 4.0};
+    c_float A_x[8] = {-1.0, -1.0, 2.0, 3.0, -1.0, 3.0, 5.0, 4.0};
+    c_int A_i[8] = {0, 2, 3, 4, 1, 2, 3, 4}, A_p[3] = {0, 4, 8};
+    c_float l[5] = {-1e30, -1e30, -1e30, -1e30, -1e30}, u[5] = {0.0, 0.0, -15.0, 100.0, 80.0};
+    OSQPData *data = (OSQPData *)calloc(1, sizeof(OSQPData));
+    data->n = 2;
+    data->m = 5;
+    data->P = csc_matrix(2, 2, 3, P_x, P_i, P_p);
+    data->q = q;
+    data->A = csc_matrix(5, 2, 8, A_x, A_i, A_p);
+    data->l = l;
+    data->u = u;
+    OSQPSettings *s = small_settings();
+    s->sigma = 1e-6;
+    w = NULL;
+    rc = osqp_setup(&w, data, s);
+    printf("SETUP non_cvx_small_sigma rc %lld\n", (long long)rc);
+    s->sigma = 5.0;
+    rc = osqp_setup(&w, data, s);
+    printf("SETUP non_cvx rc %lld\n", (long long)rc);
+    if (rc) return 10 + (int)rc;
+    rc = osqp_solve(w);
+    report("non_cvx", w, rc);
+    osqp_cleanup(w);
+  }
+  for (int v = 1; v <= 4; v++) { /* primal / dual infeasibility */
+    c_float P_x[2] = {1.0, 0.0};
+    c_int P_i[2] = {0, 1}, P_p[3] = {0, 1, 2};
+    c_float q[2] = {1.0, -1.0};
+    c_float A12_x[4] = {1.0, 1.0, 1.0, 1.0}, A34_x[3] = {1.0, 1.0, 1.0};
+    c_int A12_i[4] = {0, 1, 0, 2}, A12_p[3] = {0, 2, 4}, A34_i[3] = {0, 1, 2}, A34_p[3] = {0, 2, 3};
+    c_float l[3] = {0.0, 1.0, 1.0};
+    c_float uu[4][3] = {{5.0, 3.0, 3.0}, {0.0, 3.0, 3.0}, {2.0, 3.0, 1e30}, {0.0, 3.0, 1e30}};
+    OSQPData *data = (OSQPData *)calloc(1, sizeof(OSQPData));
+    data->n = 2;
+    data->m = 3;
+    data->P = csc_matrix(2, 2, 2, P_x, P_i, P_p);
+    data->q = q;
+    data->A = v <= 2 ? csc_matrix(3, 2, 4, A12_x, A12_i, A12_p) : csc_matrix(3, 2, 3, A34_x, A34_i, A34_p);
+    data->l = l;
+    data->u = uu[v - 1];
+    w = NULL;
+    rc = osqp_setup(&w, data, small_settings());
+    printf("SETUP infeasibility%d rc %lld\n", v, (long long)rc);
+    if (rc) return 10 + (int)rc;
+    rc = osqp_solve(w);
+    char tag[32];
+    snprintf(tag, sizeof tag, "infeasibility%d", v);
+    report(tag, w, rc);
+    osqp_cleanup(w);
+  }
+  return 0;
+}
+
 int main(int argc, char **argv) {
-  int which = argc > 1 ? atoi(argv[1]) : 3, rc = 0;
+  int which = argc > 1 ? atoi(argv[1]) : 7, rc = 0;
   if (which & 1) rc = part_a();
   if (!rc && (which & 2)) rc = part_b();
+  if (!rc && (which & 4)) rc = part_c();
   printf("DONE rc %d\n", rc);
   return rc;
 }

@@ -43,6 +43,8 @@ def parse(text):
 
 
 def rel(a, b):
+    if np.asarray(b).size == 0:
+        return 0.0 if np.asarray(a).size == 0 else np.inf
     return float(np.abs(np.asarray(a) - np.asarray(b)).max() / max(np.abs(np.asarray(b)).max(), 1e-12))
 
 

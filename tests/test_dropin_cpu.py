@@ -38,7 +38,14 @@ def test_reference_linked_api_program_reproduces_the_golden_output():
     cp = run("api_ref")
     assert cp.returncode == 0, cp.stderr[-2000:]
     got, want = parse(cp.stdout), parse(open(GOLDEN_API).read())
-    assert want["rc"] == {"SETUP generic": 0, "BADRHO": 1, "CLEANUP": 0, "SETUP combine": 0, "DONE": 0}
+    assert want["rc"] == {"SETUP generic": 0, "BADRHO": 1, "CLEANUP": 0, "SETUP combine": 0, "SETUP unconstrained": 0,
+                          "SETUP non_cvx_small_sigma": 5, "SETUP non_cvx": 0, "SETUP infeasibility1": 0,
+                          "SETUP infeasibility2": 0, "SETUP infeasibility3": 0, "SETUP infeasibility4": 0, "DONE": 0}
+    sv = {t: r["status_val"] for t, r in want["solves"].items()}
+    assert (sv["unconstrained"], sv["non_cvx"], sv["infeasibility1"], sv["infeasibility2"], sv["infeasibility3"]) == \
+        (1, -7, 1, -3, -4)
+    assert abs(want["solves"]["unconstrained"]["obj"] + 19.209752026813277) < 1e-5   # tests/unconstrained
+    assert abs(want["solves"]["infeasibility1"]["obj"] + 1.5) < 1e-3                 # tests/primal_dual_infeasibility
     assert abs(want["solves"]["qp"]["obj"] - 1.88) < 1e-5          # the reference's basic_qp known answer
     assert_same_run(got, want, 1e-9, "reference vs golden (api_user)")
 
