@@ -414,6 +414,11 @@ c_int rldl_batch_get_solution(RLDLBatch *b, c_float *x, c_float *y);
 c_int rldl_batch_get_info(RLDLBatch *b, c_int *iter, c_int *status_val, c_float *obj_val,
                           c_float *pri_res, c_float *dua_res, c_int *rho_updates,
                           c_float *rho_estimate);
+/* number of instances whose last stage recursion met a non-positive pivot (the condition on which the
+ * reference's osqp_setup fails with OSQP_NONCVX_ERROR); flag (optional, [batch]) receives 0, or 1 + the
+ * stage of the first such pivot.  The scalar setups return OSQP_NONCVX_ERROR themselves; a batch keeps its
+ * healthy instances and reports the others as OSQP_NON_CVX at the next solve.  -1 on a device error. */
+c_int rldl_batch_failed_factorisations(RLDLBatch *b, c_int *flag);
 /* settings of the whole batch (validated like the reference's osqp_update_* setters) */
 c_int rldl_batch_update_settings(RLDLBatch *b, const OSQPSettings *settings);
 void  rldl_batch_dims(const RLDLBatch *b, c_int *n, c_int *m, c_int *N, c_int *batch);

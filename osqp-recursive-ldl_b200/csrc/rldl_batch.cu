@@ -402,14 +402,17 @@ c_int Batch::factor(int k0, bool only_flagged) {
   return 0;
 }
 
-c_int Batch::failed_factorisations() {
+c_int Batch::failed_factorisations(c_int *flag_out) {
   if (cudaSetDevice(device) != cudaSuccess) return -1;
   std::vector<int> flag(batch);
   if (cudaMemcpyAsync(flag.data(), D.fact_flag, (size_t)batch * sizeof(int), cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
       cudaStreamSynchronize(stream) != cudaSuccess)
     return -1;
   c_int bad = 0;
-  for (int v : flag) bad += v != 0;
+  for (int i = 0; i < batch; i++) {
+    bad += flag[i] != 0;
+    if (flag_out) flag_out[i] = flag[i];
+  }
   return bad;
 }
 

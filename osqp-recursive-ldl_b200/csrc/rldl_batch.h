@@ -54,7 +54,7 @@ struct Batch {
   c_int factor(int k0, bool only_flagged);
   // instances whose last stage recursion met a non-positive pivot (the reference's "problem seems to be
   // non-convex", lin_sys/direct/qdldl/qdldl_interface.c LDL_factor); -1 on a CUDA error
-  c_int failed_factorisations();
+  c_int failed_factorisations(c_int *flag_out = nullptr);
   c_int factor_launch(int k0, bool only_flagged, bool mark = false);  // kernels only, no events / sync
   c_int ensure_unpacked();
   c_int pack(int k0, int parts);

@@ -727,6 +727,7 @@ c_int rldl_batch_setup(RLDLBatch **out, const OSQPDataRLDL *model, const OSQPSet
 }
 #define HB(h) if (!(h) || !(h)->b) return osqp_error(OSQP_WORKSPACE_NOT_INIT_ERROR)
 c_int rldl_batch_solve(RLDLBatch *h) { HB(h); return h->b->solve(); }
+c_int rldl_batch_failed_factorisations(RLDLBatch *h, c_int *flag) { HB(h); return h->b->failed_factorisations(flag); }
 c_int rldl_batch_update_bounds(RLDLBatch *h, const c_float *l, const c_float *u) {
   HB(h);
   const c_int rc = h->b->update_bounds(l, u, true, true, true);  // l <= u is validated on the device

@@ -111,7 +111,7 @@ osqp_solve_combine_recursive osqp_update_Z_horizon osqp_update_X_horizon
 osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions cleanup_rldl
 rldl_batch_setup rldl_batch_solve rldl_batch_update_bounds rldl_batch_partial_update_bounds
 rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
-rldl_batch_refactor rldl_batch_kkt_solve rldl_batch_get_solution rldl_batch_get_info
+rldl_batch_refactor rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_get_solution rldl_batch_get_info
 rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel
 rldl_batch_free
 rldl_device_count rldl_set_device rldl_version
@@ -171,6 +171,7 @@ def lib():
         "rldl_batch_update_horizon": [vp, c_int],
         "rldl_batch_update_rho": [vp, vp],
         "rldl_batch_refactor": [vp],
+        "rldl_batch_failed_factorisations": [vp, vp],
         "rldl_batch_kkt_solve": [vp, vp],
         "rldl_batch_get_solution": [vp, vp, vp],
         "rldl_batch_get_info": [vp] * 8,
@@ -298,6 +299,12 @@ class Batch:
 
     def refactor(self):
         return lib().rldl_batch_refactor(self.h)
+
+    def failed_factorisations(self):
+        """(count, flag[batch]) — flag = 0, or 1 + the stage of the first non-positive pivot."""
+        n, m, N, batch = self.dims()
+        flag = np.zeros(batch, np.int64)
+        return lib().rldl_batch_failed_factorisations(self.h, _p(flag)), flag
 
     def update_settings(self, settings):
         return lib().rldl_batch_update_settings(self.h, C.byref(settings))

@@ -13,7 +13,7 @@ import pytest
 
 import rldl_b200 as R
 from rldl_b200 import mpc
-from common import gpu_settings, ref_run, compare
+from common import gpu_settings, ref_run, compare, problem
 
 pytestmark = pytest.mark.gpu
 
@@ -136,3 +136,39 @@ def test_update_settings_between_solves():
     bad = compare(gb.get(), r2, n, m)
     gb.free()
     assert not bad, bad[:3]
+
+
+def test_non_convex_stage_cost_is_reported_like_the_reference():
+    """A stage cost that leaves Q + sigma I + C' rho C indefinite: the reference's osqp_setup fails with
+    OSQP_NONCVX_ERROR (src/osqp.c:214-216, "The problem seems to be non-convex"; its own tests/non_cvx).  The
+    scalar setup returns that error; a batch keeps going, names the instances through
+    rldl_batch_failed_factorisations and reports them as OSQP_NON_CVX (-7) with NaN solution at the solve."""
+    import ctypes as C
+    mdl, N, x0, q, l, u = problem("C1", 4, Nmax=21)
+    mdl.Q = mdl.Q.copy()
+    mdl.Q[1, 1] = -1.0e3                    # far below what sigma, rho and the dynamics rows' 1e3 rho add back
+    gb = R.Batch(mdl, N, 21, q, l, u, gpu_settings())
+    count, flag = gb.failed_factorisations()
+    assert count == 4 and (flag > 0).all()   # 1 + stage of the first non-positive pivot
+    assert gb.solve() == 0
+    out = gb.get()
+    assert (out["status"] == -7).all()
+    n, m, _, _ = gb.dims()
+    assert (out["x"][:, :n] == float(0x7fc00000)).all() or np.isnan(out["x"][:, :n]).all()
+    gb.free()
+    # the healthy model of the same shape factors cleanly
+    mdl2, _, _, q2, l2, u2 = problem("C1", 4, Nmax=21)
+    ok = R.Batch(mdl2, N, 21, q2, l2, u2, gpu_settings())
+    assert ok.failed_factorisations()[0] == 0
+    ok.free()
+    # scalar API: setup refuses
+    L = R.lib()
+    sm = R.StageModel(mdl)
+    d = sm.data
+    q0, l0, u0 = (np.ascontiguousarray(v[0]) for v in (q, l, u))
+    d.data.n, d.data.m = q.shape[1], l.shape[1]
+    d.data.q = q0.ctypes.data_as(C.POINTER(C.c_double)); d.data.l = l0.ctypes.data_as(C.POINTER(C.c_double))
+    d.data.u = u0.ctypes.data_as(C.POINTER(C.c_double))
+    w = C.POINTER(R.OSQPWorkspace)()
+    s = gpu_settings()
+    assert L.osqp_setup_recursive(C.byref(w), C.byref(d), C.byref(s), 21, N, mdl.nx, mdl.nu, mdl.ny, mdl.nt) == 5
