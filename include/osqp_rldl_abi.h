@@ -404,6 +404,11 @@ c_int rldl_batch_warm_start_shift(RLDLBatch *b);
 c_int rldl_batch_update_horizon(RLDLBatch *b, c_int N);
 /* batched osqp_update_rho (per-instance value) */
 c_int rldl_batch_update_rho(RLDLBatch *b, const c_float *rho);
+/* batched osqp_update_P_A (src/osqp.c:1166-1266) for time-varying / re-linearised MPC: new values for the
+ * shared stage matrices Q0,Qi,QN,A0,Ai,Aij,AN (same dimensions as at setup; sparsity patterns may differ),
+ * followed by the full stage recursion of every instance.  Resets the per-instance info like the
+ * reference's update (status OSQP_UNSOLVED); iterates are kept for warm starts. */
+c_int rldl_batch_update_model(RLDLBatch *b, const OSQPDataRLDL *model);
 /* re-run the full stage recursion (what osqp_setup_recursive does after allocation) */
 c_int rldl_batch_refactor(RLDLBatch *b);
 /* one KKT solve per instance: rhs [batch][n+m] (current sizes) is overwritten with

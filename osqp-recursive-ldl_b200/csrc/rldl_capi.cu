@@ -727,6 +727,17 @@ c_int rldl_batch_setup(RLDLBatch **out, const OSQPDataRLDL *model, const OSQPSet
 }
 #define HB(h) if (!(h) || !(h)->b) return osqp_error(OSQP_WORKSPACE_NOT_INIT_ERROR)
 c_int rldl_batch_solve(RLDLBatch *h) { HB(h); return h->b->solve(); }
+c_int rldl_batch_update_model(RLDLBatch *h, const OSQPDataRLDL *model) {
+  HB(h);
+  if (!model) return osqp_error(OSQP_DATA_VALIDATION_ERROR);
+  Batch *B = h->b;
+  if (B->generic) return osqp_error(OSQP_DATA_VALIDATION_ERROR);
+  c_int rc = B->upload_model(model->Q0, model->Qi, model->QN, model->A0, model->Ai, model->Aij, model->AN);
+  if (rc) return rc;
+  rc = B->reset_info();
+  if (rc) return rc;
+  return B->refactor();
+}
 c_int rldl_batch_failed_factorisations(RLDLBatch *h, c_int *flag) { HB(h); return h->b->failed_factorisations(flag); }
 c_int rldl_batch_update_bounds(RLDLBatch *h, const c_float *l, const c_float *u) {
   HB(h);

@@ -111,7 +111,7 @@ osqp_solve_combine_recursive osqp_update_Z_horizon osqp_update_X_horizon
 osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions cleanup_rldl
 rldl_batch_setup rldl_batch_solve rldl_batch_update_bounds rldl_batch_partial_update_bounds
 rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
-rldl_batch_refactor rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_get_solution rldl_batch_get_info
+rldl_batch_refactor rldl_batch_update_model rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_get_solution rldl_batch_get_info
 rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel
 rldl_batch_free
 rldl_device_count rldl_set_device rldl_version
@@ -172,6 +172,7 @@ def lib():
         "rldl_batch_update_rho": [vp, vp],
         "rldl_batch_refactor": [vp],
         "rldl_batch_failed_factorisations": [vp, vp],
+        "rldl_batch_update_model": [vp, vp],
         "rldl_batch_kkt_solve": [vp, vp],
         "rldl_batch_get_solution": [vp, vp, vp],
         "rldl_batch_get_info": [vp] * 8,
@@ -299,6 +300,12 @@ class Batch:
 
     def refactor(self):
         return lib().rldl_batch_refactor(self.h)
+
+    def update_model(self, mdl):
+        """New values for the shared stage matrices (same shapes), then the full recursion."""
+        sm = StageModel(mdl)
+        self._models = getattr(self, "_models", []) + [sm]
+        return lib().rldl_batch_update_model(self.h, C.byref(sm.data))
 
     def failed_factorisations(self):
         """(count, flag[batch]) — flag = 0, or 1 + the stage of the first non-positive pivot."""

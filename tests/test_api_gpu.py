@@ -309,3 +309,31 @@ def test_setup_validation_errors():
     info = w.contents.info.contents
     assert (info.status_val, info.iter) == (-2, 10)
     assert L.osqp_cleanup(w) == 0
+
+
+def test_batch_update_model_matches_fresh_setup():
+    """rldl_batch_update_model — the batched osqp_update_P_A (src/osqp.c:1166-1266): new stage-matrix values
+    for a whole batch, full recursion re-run; equals a batch set up on the new model, cold and warm-started,
+    on the specialised kernels (batch above and below the latency-mode hand-off) and the generic one."""
+    N, Nmax = 12, 13
+    m1, m2 = mpc.random_model(4, 2, seed=21), mpc.random_model(4, 2, seed=22)
+    for batch, generic in ((24, False), (1500, False), (24, True)):
+        x0 = mpc.sample_x0(m1, batch, 7)
+        q, l, u = m1.vectors(x0, N, Nmax)
+        q2, l2, u2 = m2.vectors(x0, N, Nmax)
+        a = R.Batch(m1, N, Nmax, q, l, u, gpu_settings())
+        b = R.Batch(m2, N, Nmax, q2, l2, u2, gpu_settings())
+        if generic:
+            assert a.select_kernel(1) == 0 and b.select_kernel(1) == 0
+        assert a.solve() == 0                       # a has iterates and a factor of model 1
+        assert a.update_model(m2) == 0
+        assert (a.get()["status"] == -10).all()     # info reset like the reference's update (OSQP_UNSOLVED)
+        assert a.update_lin_cost(q2) == 0 and a.update_bounds(l2, u2) == 0
+        assert a.solve() == 0 and b.solve() == 0
+        n, m, _, _ = b.dims()
+        assert not compare(a.get(), b.get(), n, m)
+        # a model of another shape is refused and leaves the handle usable
+        assert a.update_model(mpc.random_model(3, 2, seed=5)) != 0
+        assert a.solve() == 0
+        assert not compare(a.get(), b.get(), n, m)
+        a.free(); b.free()
