@@ -84,7 +84,8 @@ static bool check_dims(const csc *M, c_int m, c_int n) { return M && M->m == m &
 c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc *A0, const csc *Ai,
                           const csc *Aij, const csc *AN) {
   ModelBuilder mb;
-  ModelDev &Md = M;
+  ModelDev Mnew = M;  // built aside: a refused update must leave the resident model untouched
+  ModelDev &Md = Mnew;
   Md.nx = nx; Md.nu = nu; Md.ny = ny; Md.nt = nt; Md.a = a; Md.b = b;
   memset(Md.sc, 0, sizeof(Md.sc));
   Md.bd = 0;
@@ -146,6 +147,7 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
     s.C = mb.add_ell(C, nt, nx, false); s.Ct = mb.add_ell(C, nt, nx, true);
     s.F.rows = s.F.width = s.F.off = 0; s.Ft = s.F;
   }
+  if (stream) CK(cudaStreamSynchronize(stream));  // nothing of this handle may still read the old model
   if (d_mval) cudaFree(d_mval);
   if (d_midx) cudaFree(d_midx);
   d_mval = nullptr; d_midx = nullptr;
@@ -155,6 +157,7 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
   CK(cudaMemcpy(d_midx, mb.idx.data(), mb.idx.size() * sizeof(int), cudaMemcpyHostToDevice));
   CK(cudaStreamSynchronize(0));  // pageable copies may still be in flight on the default stream when cudaMemcpy returns
   Md.val = d_mval; Md.idx = d_midx; Md.nval = (int)mb.val.size();
+  M = Mnew;
   if (D.rec) return configure_stream();  // a P / A update may change which specialisation serves the model
   return 0;
 }
