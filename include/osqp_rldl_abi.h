@@ -437,6 +437,16 @@ void  rldl_batch_counters(const RLDLBatch *b, double *admm_bytes, double *factor
  * Both compute the same iteration; the switch exists for cross-checking and profiling.
  * which = 2 changes nothing and returns 0 iff the handle's stage shape has specialised kernels. */
 c_int rldl_batch_select_kernel(RLDLBatch *b, c_int which);
+/* Launch knobs of this handle (per handle, not process-global; the defaults are the measured optima on B200
+ * and no setting can change results beyond rounding — the tests use them to steer which kernel finishes a solve):
+ *   "lat_below"   unfinished instances at which the streaming kernel hands its tail to the latency-mode kernel
+ *                 (default 1024; 0 = streaming kernel only; >= batch = latency-mode kernel only)
+ *   "ring_depth"  stage records in flight per lane group of the streaming kernel (default 2)
+ *   "sched_s0"    iterations a fresh instance runs before it may be pre-empted (default check_termination;
+ *                 0 = device priority scheduler off)
+ *   "ctas_per_sm" resident CTAs per SM of the streaming kernel (default 4, 3 without the hand-off)
+ * value = -1 restores the default.  Returns 0, or 1 for an unknown name / invalid value. */
+c_int rldl_batch_set_tuning(RLDLBatch *b, const char *name, c_int value);
 /* the CUDA stream (cudaStream_t) every launch and copy of this handle is issued on, so a
  * caller can bracket calls with its own events on the launching stream */
 void *rldl_batch_stream(const RLDLBatch *b);

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <vector>
 #include "rldl_batch.h"
 
@@ -147,15 +148,23 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
     s.C = mb.add_ell(C, nt, nx, false); s.Ct = mb.add_ell(C, nt, nx, true);
     s.F.rows = s.F.width = s.F.off = 0; s.Ft = s.F;
   }
+  // the new buffers are allocated and filled before the old ones go: a failure leaves the resident model as it was
+  double *nval = nullptr;
+  int *nidx = nullptr;
+  if (cudaMalloc(&nval, mb.val.size() * sizeof(double)) != cudaSuccess ||
+      cudaMalloc(&nidx, mb.idx.size() * sizeof(int)) != cudaSuccess ||
+      cudaMemcpy(nval, mb.val.data(), mb.val.size() * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess ||
+      cudaMemcpy(nidx, mb.idx.data(), mb.idx.size() * sizeof(int), cudaMemcpyHostToDevice) != cudaSuccess ||
+      cudaStreamSynchronize(0) != cudaSuccess) {  // (pageable copies may still be in flight when cudaMemcpy returns)
+    fprintf(stderr, "ERROR in %s: CUDA failure while uploading the stage model\n", __func__);
+    if (nval) cudaFree(nval);
+    if (nidx) cudaFree(nidx);
+    return OSQP_LINSYS_SOLVER_INIT_ERROR;
+  }
   if (stream) CK(cudaStreamSynchronize(stream));  // nothing of this handle may still read the old model
   if (d_mval) cudaFree(d_mval);
   if (d_midx) cudaFree(d_midx);
-  d_mval = nullptr; d_midx = nullptr;
-  CK(cudaMalloc(&d_mval, mb.val.size() * sizeof(double)));
-  CK(cudaMalloc(&d_midx, mb.idx.size() * sizeof(int)));
-  CK(cudaMemcpy(d_mval, mb.val.data(), mb.val.size() * sizeof(double), cudaMemcpyHostToDevice));
-  CK(cudaMemcpy(d_midx, mb.idx.data(), mb.idx.size() * sizeof(int), cudaMemcpyHostToDevice));
-  CK(cudaStreamSynchronize(0));  // pageable copies may still be in flight on the default stream when cudaMemcpy returns
+  d_mval = nval; d_midx = nidx;
   Md.val = d_mval; Md.idx = d_midx; Md.nval = (int)mb.val.size();
   M = Mnew;
   if (D.rec) return configure_stream();  // a P / A update may change which specialisation serves the model
@@ -242,6 +251,7 @@ void Batch::push_settings() {
   int ai = (int)settings.adaptive_rho_interval;
   if (settings.adaptive_rho && !ai) ai = settings.check_termination ? 4 * (int)settings.check_termination : 100;
   S.adaptive_rho_interval = ai;
+  S.time_limit_ns = 0;  // set per solve (Batch::solve)
 }
 
 // ------------------------------ lifetime ------------------------------
@@ -261,7 +271,8 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
     fprintf(stderr, "ERROR in rldl: invalid dimensions (need 1 <= N <= Nmax, batch >= 1)\n");
     return OSQP_DATA_VALIDATION_ERROR;
   }
-  Batch *B = new Batch();
+  std::unique_ptr<Batch> guard(new Batch());  // every early return below frees the handle and its device buffers
+  Batch *B = guard.get();
   B->generic = generic;
   B->nx = (int)nx; B->nu = (int)nu; B->ny = (int)ny; B->nt = (int)nt;
   B->a = (int)(nx + nu); B->b = (int)(nx + ny);
@@ -271,12 +282,11 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   B->settings = *st;
   CK(cudaGetDevice(&B->device));
   c_int rc = B->upload_model(Q0, Qi, QN, A0, Ai, Aij, AN);
-  if (rc) { delete B; return rc; }
+  if (rc) return rc;
   const size_t per_f = factor_smem_doubles(B->a, B->nx, B->ny, B->nt) * sizeof(double);
   const size_t per_a = admm_smem_doubles(B->a, B->nx, B->ny, B->nt) * sizeof(double);
   if (per_f > 220 * 1024 || per_a > 220 * 1024) {
     fprintf(stderr, "ERROR in rldl: stage blocks too large for on-chip staging (a=%d, nx=%d)\n", B->a, B->nx);
-    delete B;
     return OSQP_DATA_VALIDATION_ERROR;
   }
   BatchDev &D = B->D;
@@ -299,7 +309,7 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(dalloc(&B->d_changed, bs));
   CK(dalloc(&D.sched, kSchedCounters));
   rc = B->configure_stream();
-  if (rc) { delete B; return rc; }
+  if (rc) return rc;
   CK(cudaStreamCreateWithFlags(&B->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&B->ev0)); CK(cudaEventCreate(&B->ev1));
   B->set_sizes();
@@ -310,21 +320,33 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(cudaMemcpyAsync(D.u, u, bs * D.mmax * sizeof(double), cudaMemcpyHostToDevice, B->stream));
   if (rho) {
     for (size_t i = 0; i < bs; i++)
-      if (!(rho[i] > 0.0)) { fprintf(stderr, "ERROR in rldl: rho must be positive\n"); delete B; return OSQP_SETTINGS_VALIDATION_ERROR; }
+      if (!(rho[i] > 0.0)) { fprintf(stderr, "ERROR in rldl: rho must be positive\n"); return OSQP_SETTINGS_VALIDATION_ERROR; }
     CK(cudaMemcpyAsync(D.rho, rho, bs * sizeof(double), cudaMemcpyHostToDevice, B->stream));
   } else {
     CK(launch_fill(D.rho, st->rho, bs, B->stream));
     B->launches++;
   }
-  std::vector<int> st0(bs, OSQP_UNSOLVED);
-  CK(cudaMemcpyAsync(D.status, st0.data(), bs * sizeof(int), cudaMemcpyHostToDevice, B->stream));
-  CK(cudaStreamSynchronize(B->stream));
-  // set_rho_vec (auxil.c:79) + full stage recursion (recursive_ldl.c:1139)
-  CK(launch_set_rho_vec(D, D.mmax, nullptr, B->stream));
+  CK(launch_fill_int(D.status, OSQP_UNSOLVED, bs, B->stream));
   B->launches++;
+  // validate_data (auxil.c:794-887): l <= u on every row, checked on the device for the whole batch
+  {
+    int bad = 0;
+    CK(launch_check_bounds(D.l, D.u, D.mmax, D.mmax, B->batch, D.sched + 1, B->stream));
+    B->launches++;
+    CK(cudaMemcpyAsync(&bad, D.sched + 1, sizeof(int), cudaMemcpyDeviceToHost, B->stream));
+    CK(cudaStreamSynchronize(B->stream));
+    if (bad) {
+      fprintf(stderr, "ERROR in validate_data: Lower bound must be lower than or equal to upper bound\n");
+      return OSQP_DATA_VALIDATION_ERROR;
+    }
+    CK(cudaMemsetAsync(D.sched + 1, 0, sizeof(int), B->stream));
+  }
+  // set_rho_vec (auxil.c:79) + full stage recursion (recursive_ldl.c:1139)
+  rc = B->retype(0, 3, false, false, true);
+  if (rc) return rc;
   rc = B->factor(0, false);
-  if (rc) { delete B; return rc; }
-  *out = B;
+  if (rc) return rc;
+  *out = guard.release();
   return 0;
 }
 
@@ -367,8 +389,6 @@ c_int Batch::factor_launch(int k0, bool only_flagged, bool mark) {
     launches++;
     if (mark) CK(cudaEventRecord(ev1, stream));  // last_factor_ms times the recursion kernel alone
     if (!need_unpacked) unpacked_valid = false;
-    CK(launch_pack_records(M, D, only_flagged ? 0 : k0, 2, fl, stream));
-    launches++;
     records_stale = false;
   } else {
     CK(launch_factor(M, D, settings.sigma, k0, fl, stream));
@@ -398,9 +418,9 @@ c_int Batch::factor(int k0, bool only_flagged) {
   float ms = 0;
   cudaEventElapsedTime(&ms, ev0, ev1);
   last_factor_ms = ms;
-  // algorithmic bytes: pivot inverses written once (diagonal-packed records on the streaming path),
-  // rho_vec read once, per stage and instance
-  const double per_stage = streaming ? (double)D.PX + D.PS + b : (double)a * a + (double)nx * nx + b;
+  // algorithmic bytes: pivot inverses written once (diagonal-packed records on the streaming path), the row
+  // classes of the record (streaming) or rho_vec (runtime shapes) read once, per stage and instance
+  const double per_stage = streaming ? (double)D.PX + D.PS + kClsWords : (double)a * a + (double)nx * nx + b;
   factor_bytes = 8.0 * batch * ((N - k0) * per_stage + (streaming ? (double)D.PX : (double)nx * nx) + nt);
   return 0;
 }
@@ -422,15 +442,24 @@ c_int Batch::failed_factorisations(c_int *flag_out) {
 c_int Batch::solve() {
   CK(cudaSetDevice(device));
   CK(cudaEventRecord(ev0, stream));
+  // time_limit (osqp.c:389-405): what is left of it when the solve starts (the scalar entry points subtract
+  // their setup / update time), tested on the device against %globaltimer
+  S.time_limit_ns = 0;
+  if (settings.time_limit > 0.0) {
+    const double left = settings.time_limit - time_spent_before_solve;
+    S.time_limit_ns = left > 1e-9 ? (long long)(left * 1e9) : 1;
+    CK(launch_mark_time(D, stream));
+    launches++;
+  }
   if (z_pending) {
     CK(launch_warm_start_z(M, D, stream));
     launches++;
     z_pending = false;
   }
   if (use_stream() && records_stale) {  // a generic-kernel adaptive solve re-factorised behind the records
-    CK(launch_set_rho_vec(D, D.m, nullptr, stream));
-    launches++;
-    c_int rc = factor_launch(0, false);
+    c_int rc = retype(0, 2, false, false);
+    if (rc) return rc;
+    rc = factor_launch(0, false);
     if (rc) return rc;
   }
   if (!use_stream()) {
@@ -447,8 +476,6 @@ c_int Batch::solve() {
     // full stage recursion); parked instances are re-typed, re-factorised and re-packed together, then resumed.
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    int lat_below = 1024;
-    if (const char *e = getenv("RLDL_LAT_BELOW")) lat_below = atoi(e);
     const size_t lat_smem = latency_smem_bytes(M, N);
     const bool lat_ok = lat_below > 0 && lat_smem != (size_t)-1 && lat_smem <= 227 * 1024;
     if (lat_ok && !d_latT) CK(cudaMalloc(&d_latT, (size_t)sms * latency_t_blocks(Nmax) * nx * (nx + 2) * sizeof(double)));
@@ -457,12 +484,12 @@ c_int Batch::solve() {
     for (;;) {
       const bool run_stream = !lat_ok || unfinished > lat_below;
       if (run_stream) {
-        CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, lat_ok ? lat_below : 0, stream));
+        CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, lat_ok ? lat_below : 0, tune, stream));
         launches++;
       }
       if (lat_ok) {
         CK(launch_admm_latency(M, D, S, (int)settings.warm_start, (resume || run_stream) ? 1 : 0, d_latT,
-                               std::min(sms, batch), run_stream ? 0 : 1, stream));
+                               std::min(sms, batch), run_stream ? 0 : 1, run_stream ? 1 : 0, stream));
         launches++;
       }
       if (!settings.adaptive_rho) break;
@@ -472,9 +499,9 @@ c_int Batch::solve() {
       CK(cudaStreamSynchronize(stream));
       if (!cnt[0]) break;
       unfinished = cnt[1];
-      CK(launch_set_rho_vec(D, D.m, d_changed, stream));
-      launches++;
-      c_int rc = factor_launch(0, true);
+      c_int rc = retype(0, 2, true, true);  // the parked instances: new rho_vec, flagged, resumable again
+      if (rc) return rc;
+      rc = factor_launch(0, true);
       if (rc) return rc;
       resume = 1;
       solve_rounds++;
@@ -495,17 +522,31 @@ bool Batch::use_stream() const {
   return streaming && kernel_choice != 1;
 }
 
-c_int Batch::pack(int k0, int parts) {
-  if (!streaming) return 0;
-  CK(launch_pack_records(M, D, k0, parts, nullptr, stream));
-  launches++;
+// Everything that is derived from (l, u, rho, q) for stages >= k0 (reference set_rho_vec / update_rho_vec,
+// src/auxil.c:79-145): constraint typing, rho_vec, and on the streaming shapes the vector part of the stage
+// records (parts bit 0: q, bit 1: row classes, l, u).  want_flags: d_changed[inst] = 1 for the instances whose
+// row types changed (or that an adaptive-rho update parked) — they need the stage recursion again.
+// only_parked: only the instances parked by an adaptive-rho update are touched.  all_rows: type the rows of
+// the whole Nmax-sized problem (setup), not just the current horizon.
+c_int Batch::retype(int k0, int parts, bool only_parked, bool want_flags, bool all_rows) {
+  if (streaming) {
+    CK(launch_vec_records(M, D, k0, parts | (only_parked ? 4 : 0), nullptr, want_flags ? d_changed : nullptr, stream));
+    launches++;
+    if (!all_rows) return 0;
+    // rows beyond the current horizon are typed once at setup, as the reference does (recursive_ldl.c:2190)
+  }
+  if ((parts & 2) && (!streaming || all_rows)) {
+    CK(launch_set_rho_vec(D, all_rows ? D.mmax : D.m, (want_flags && !streaming) ? d_changed : nullptr, stream));
+    launches++;
+  }
   return 0;
 }
 
 c_int Batch::retype_and_refactor() {
   // update_rho_vec (auxil.c:103-145): re-type rows; refactor instances whose types changed
-  CK(launch_set_rho_vec(D, D.m, d_changed, stream));
-  launches++;
+  c_int rc = retype(0, 2, false, true);
+  if (rc) return rc;
+  if (streaming) return factor_launch(0, true);  // flags stay on the device: instances without a change are skipped
   std::vector<int> ch(batch);
   CK(cudaMemcpyAsync(ch.data(), d_changed, batch * sizeof(int), cudaMemcpyDeviceToHost, stream));
   CK(cudaStreamSynchronize(stream));
@@ -515,11 +556,10 @@ c_int Batch::retype_and_refactor() {
   return 0;
 }
 
-c_int Batch::reset_info() {
-  std::vector<int> st0(batch, OSQP_UNSOLVED);
-  CK(cudaMemcpyAsync(D.status, st0.data(), batch * sizeof(int), cudaMemcpyHostToDevice, stream));
+c_int Batch::reset_info() {  // reset_info, src/auxil.c:635-652 — stream-ordered, no host round trip
+  CK(launch_fill_int(D.status, OSQP_UNSOLVED, (size_t)batch, stream));
+  launches++;
   CK(cudaMemsetAsync(D.rho_updates, 0, batch * sizeof(int), stream));
-  CK(cudaStreamSynchronize(stream));
   return 0;
 }
 
@@ -547,9 +587,7 @@ c_int Batch::update_bounds(const c_float *l, const c_float *u, bool have_l, bool
   }
   c_int rc = reset_info();
   if (rc) return rc;
-  rc = retype_and_refactor();
-  if (rc) return rc;
-  return pack(0, 2);
+  return retype_and_refactor();
 }
 
 c_int Batch::partial_update_bounds(c_int start, c_int stop, const c_float *l, const c_float *u) {
@@ -567,15 +605,13 @@ c_int Batch::partial_update_bounds(c_int start, c_int stop, const c_float *l, co
   if (rc) return rc;
   // The reference re-types the rows but never refactors (src/recursive_ldl.c:160-189, F6),
   // which leaves factor and rho_vec inconsistent when a type changes; we keep them consistent.
-  rc = retype_and_refactor();
-  if (rc) return rc;
-  return pack(0, 2);
+  return retype_and_refactor();
 }
 
 c_int Batch::update_lin_cost(const c_float *q) {
   CK(cudaSetDevice(device));
   CK(cudaMemcpyAsync(D.q, q, (size_t)batch * D.nmax * sizeof(double), cudaMemcpyHostToDevice, stream));
-  c_int rc = pack(0, 2);
+  c_int rc = retype(0, 1, false, false);
   if (rc) return rc;
   return reset_info();
 }
@@ -609,6 +645,8 @@ c_int Batch::update_horizon(c_int Nnew) {
   const int k0 = std::min((int)Nnew, N);  // first stage whose pivots change
   N = (int)Nnew;
   set_sizes();
+  c_int rc = retype(k0, 3, false, false);  // the terminal stage moved: its q, rows and bounds change
+  if (rc) return rc;
   return factor(k0, false);
 }
 
@@ -617,15 +655,15 @@ c_int Batch::update_rho(const c_float *rho) {
   for (int i = 0; i < batch; i++)
     if (!(rho[i] > 0.0)) { fprintf(stderr, "ERROR in osqp_update_rho: rho must be positive\n"); return 1; }
   CK(cudaMemcpyAsync(D.rho, rho, (size_t)batch * sizeof(double), cudaMemcpyHostToDevice, stream));
-  CK(launch_set_rho_vec(D, D.m, nullptr, stream));
-  launches++;
+  c_int rc = retype(0, 2, false, false);
+  if (rc) return rc;
   return factor(0, false);
 }
 
 c_int Batch::refactor() {
   CK(cudaSetDevice(device));
-  CK(launch_set_rho_vec(D, D.mmax, nullptr, stream));
-  launches++;
+  c_int rc = retype(0, 3, false, false);
+  if (rc) return rc;
   return factor(0, false);
 }
 

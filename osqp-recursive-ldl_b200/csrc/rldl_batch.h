@@ -13,6 +13,8 @@ struct Batch {
   int device = 0;
   bool generic = false;  // osqp_setup path: one dense stage (N == 0)
   int kernel_choice = 0;   // 0 auto, 1 force the generic (runtime-shape) ADMM kernel
+  int lat_below = 1024;    // hand-off threshold: unfinished instances at which the latency-mode kernel takes over (0: never)
+  StreamTuning tune;       // launch knobs of the streaming kernel (rldl_batch_set_tuning)
   bool streaming = false;  // shapes the streaming kernels cover (rldl_stream.cu)
   bool need_unpacked = false;   // a generic-kernel consumer wants Xinv/Sinv unpacked as well as the records
   bool unpacked_valid = false;  // D.Xinv / D.Sinv match the current factorisation
@@ -35,6 +37,7 @@ struct Batch {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double last_factor_ms = 0, last_solve_ms = 0, factor_bytes = 0;
   long long launches = 0;
+  double time_spent_before_solve = 0.0;  // seconds already charged against settings.time_limit (scalar API)
   long long solve_rounds = 0;  // extra ADMM launches caused by adaptive-rho refactorisations
 
   static c_int create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, const csc *A0,
@@ -57,7 +60,7 @@ struct Batch {
   c_int failed_factorisations(c_int *flag_out = nullptr);
   c_int factor_launch(int k0, bool only_flagged, bool mark = false);  // kernels only, no events / sync
   c_int ensure_unpacked();
-  c_int pack(int k0, int parts);
+  c_int retype(int k0, int parts, bool only_parked, bool want_flags, bool all_rows = false);
   bool use_stream() const;
   c_int solve();
   c_int retype_and_refactor();

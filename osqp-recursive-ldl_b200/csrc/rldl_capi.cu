@@ -402,6 +402,8 @@ c_int osqp_solve(OSQPWorkspace *work) {
   if (work->clear_update_time == 1) work->info->update_time = 0.0;
   const double t0 = now_s();
   sync_settings(work);
+  // run time so far, as the reference counts it (osqp.c:391-396): setup time on the first run, update time after
+  B->time_spent_before_solve = work->first_run ? work->info->setup_time : work->info->update_time;
   c_int rc = B->solve();
   if (rc) return 1;
   c_int iter = 0, status = 0, ru = 0;
@@ -604,34 +606,38 @@ static c_int scatter_vals(csc *M, const c_float *v, const c_int *idx, c_int cnt)
 }
 
 // Re-extract the stage blocks from the updated global matrices (stage-structured workspaces).
-static c_int stage_blocks_from_global(OSQPWorkspace *work) {
+// commit = false: only check that the update keeps the stage structure (every interior stage equal to stage 1,
+// Aij untouched) — nothing is written; commit = true: copy the new values into the user's stage blocks.
+static c_int stage_blocks_from_global(OSQPWorkspace *work, bool commit) {
   PrivSolver *p = priv(work);
   OSQPDataRLDL *r = p->rldl;
   const csc *P = work->data->P, *A = work->data->A;
   const c_int a = r->nx + r->nu, N = r->N;
   c_int pp = 0, ap = 0;
-  auto take = [](csc *blk, const csc *G, c_int &pos) {
+  auto take = [commit](csc *blk, const csc *G, c_int &pos) {
     const c_int nnz = blk->p[blk->n];
-    memcpy(blk->x, G->x + pos, sizeof(c_float) * nnz);
+    if (commit) memcpy(blk->x, G->x + pos, sizeof(c_float) * nnz);
     pos += nnz;
-  };
-  auto same = [](const csc *blk, const csc *G, c_int &pos) {
-    const c_int nnz = blk->p[blk->n];
-    bool ok = memcmp(blk->x, G->x + pos, sizeof(c_float) * nnz) == 0;
-    pos += nnz;
-    return ok;
   };
   // columns are stored stage by stage: [Q0|A0] , then per stage [Qi] and [Aij;Ai] interleaved per column
   take(r->Q0, P, pp); take(r->A0, A, ap);
   bool ok = true;
+  c_int p1 = -1;                 // position of stage 1's Qi values in P
+  std::vector<c_int> a1(a, -1);  // position of stage 1's Ai column values in A
   for (c_int k = 1; k < N; k++) {
-    if (k == 1) take(r->Qi, P, pp); else ok &= same(r->Qi, P, pp);
+    const c_int nq = r->Qi->p[r->Qi->n];
+    if (k == 1) { p1 = pp; take(r->Qi, P, pp); }
+    else { ok &= memcmp(P->x + p1, P->x + pp, sizeof(c_float) * nq) == 0; pp += nq; }
     for (c_int j = 0; j < a; j++) {
       const c_int nij = r->Aij->p[j + 1] - r->Aij->p[j], ni = r->Ai->p[j + 1] - r->Ai->p[j];
       for (c_int e = 0; e < nij; e++) ok &= A->x[ap + e] == r->Aij->x[r->Aij->p[j] + e];
       ap += nij;
-      if (k == 1) memcpy(r->Ai->x + r->Ai->p[j], A->x + ap, sizeof(c_float) * ni);
-      else ok &= memcmp(r->Ai->x + r->Ai->p[j], A->x + ap, sizeof(c_float) * ni) == 0;
+      if (k == 1) {
+        a1[j] = ap;
+        if (commit) memcpy(r->Ai->x + r->Ai->p[j], A->x + ap, sizeof(c_float) * ni);
+      } else {
+        ok &= memcmp(A->x + a1[j], A->x + ap, sizeof(c_float) * ni) == 0;
+      }
       ap += ni;
     }
   }
@@ -640,22 +646,33 @@ static c_int stage_blocks_from_global(OSQPWorkspace *work) {
     const c_int nij = r->Aij->p[j + 1] - r->Aij->p[j], ni = r->AN->p[j + 1] - r->AN->p[j];
     for (c_int e = 0; e < nij; e++) ok &= A->x[ap + e] == r->Aij->x[r->Aij->p[j] + e];
     ap += nij;
-    memcpy(r->AN->x + r->AN->p[j], A->x + ap, sizeof(c_float) * ni);
+    if (commit) memcpy(r->AN->x + r->AN->p[j], A->x + ap, sizeof(c_float) * ni);
     ap += ni;
   }
-  if (!ok) {
-    fprintf(stderr, "ERROR in osqp_update_P_A: on a recursive workspace all interior stages must keep sharing one (Qi, Ai) block and Aij is fixed\n");
-    return 1;
-  }
-  return 0;
+  return ok ? 0 : 1;
 }
 
 static c_int update_PA_common(OSQPWorkspace *work, const c_float *Px, const c_int *Pi, c_int Pn,
                               const c_float *Ax, const c_int *Ai_, c_int An) {
   tic_update(work);
-  if (Px && scatter_vals(work->data->P, Px, Pi, Pn)) { fprintf(stderr, "ERROR in osqp_update_P: new number of elements greater than elements in P\n"); return 1; }
-  if (Ax && scatter_vals(work->data->A, Ax, Ai_, An)) { fprintf(stderr, "ERROR in osqp_update_A: new number of elements greater than elements in A\n"); return Px ? 2 : 1; }
-  if (priv(work)->kind != 0 && stage_blocks_from_global(work)) return 1;
+  // a refused update leaves the workspace as it was: the host mirrors are restored from these copies
+  csc *P = work->data->P, *A = work->data->A;
+  const std::vector<c_float> Pold(P->x, P->x + P->p[P->n]), Aold(A->x, A->x + A->p[A->n]);
+  auto refuse = [&](c_int rc) {
+    memcpy(P->x, Pold.data(), sizeof(c_float) * Pold.size());
+    memcpy(A->x, Aold.data(), sizeof(c_float) * Aold.size());
+    toc_update(work);
+    return rc;
+  };
+  if (Px && scatter_vals(P, Px, Pi, Pn)) { fprintf(stderr, "ERROR in osqp_update_P: new number of elements greater than elements in P\n"); return refuse(1); }
+  if (Ax && scatter_vals(A, Ax, Ai_, An)) { fprintf(stderr, "ERROR in osqp_update_A: new number of elements greater than elements in A\n"); return refuse(Px ? 2 : 1); }
+  if (priv(work)->kind != 0) {
+    if (stage_blocks_from_global(work, false)) {
+      fprintf(stderr, "ERROR in osqp_update_P_A: on a recursive workspace all interior stages must keep sharing one (Qi, Ai) block and Aij is fixed\n");
+      return refuse(1);
+    }
+    stage_blocks_from_global(work, true);
+  }
   c_int rc = rebuild_model(work);
   reset_info(work->info);
   toc_update(work);
@@ -790,6 +807,17 @@ c_int rldl_batch_select_kernel(RLDLBatch *h, c_int which) {
   if (which == 2) return h->b->streaming ? 0 : 1;  // query: is this shape in the specialisation table?
   if (which < 0 || which > 1) return 1;
   h->b->kernel_choice = (int)which;
+  return 0;
+}
+c_int rldl_batch_set_tuning(RLDLBatch *h, const char *name, c_int value) {
+  HB(h);
+  if (!name || value < -1) return 1;
+  Batch *B = h->b;
+  if (!strcmp(name, "lat_below")) B->lat_below = (int)value < 0 ? 1024 : (int)value;
+  else if (!strcmp(name, "ring_depth")) B->tune.ring_depth = (int)value < 0 ? 0 : (int)value;
+  else if (!strcmp(name, "sched_s0")) B->tune.sched_s0 = (int)value;
+  else if (!strcmp(name, "ctas_per_sm")) B->tune.ctas_per_sm = (int)value < 0 ? 0 : (int)value;
+  else return 1;
   return 0;
 }
 void *rldl_batch_stream(const RLDLBatch *h) { return (h && h->b) ? (void *)h->b->stream : nullptr; }

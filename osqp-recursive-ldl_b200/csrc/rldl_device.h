@@ -48,6 +48,9 @@ struct SettingsDev {
   double sigma, alpha, eps_abs, eps_rel, eps_prim_inf, eps_dual_inf;
   double adaptive_rho_tolerance;
   int max_iter, check_termination, adaptive_rho, adaptive_rho_interval;
+  // time_limit (reference src/osqp.c:389-405): nanoseconds of solve time left when the launch sequence of a
+  // solve starts (0 = no limit), measured on the device against sched[kSchedT0] (%globaltimer at solve start)
+  long long time_limit_ns;
 };
 
 // Per-instance arrays are instance-major with the strides below.
@@ -89,7 +92,8 @@ constexpr int kSchedBuckets = 32;  // priority buckets: floor(2*log2(residual / 
 // sched[kSchedUnfinished]: instances of the current solve not yet finished (kept across the launches of
 // one solve: streaming launch, latency-mode launch, adaptive-rho resume rounds); kSchedCounters = array size
 constexpr int kSchedUnfinished = 2 + 2 * kSchedBuckets;
-constexpr int kSchedCounters = kSchedUnfinished + 2;
+constexpr int kSchedT0 = kSchedUnfinished + 2;  // 64-bit %globaltimer value at the start of the current solve
+constexpr int kSchedCounters = kSchedT0 + 2;
 
 constexpr int STATUS_FACTOR_ERROR = -7;  // reported as OSQP_NON_CVX
 // device-internal: instance parked by an adaptive-rho update until its factor has been refreshed (never

@@ -522,6 +522,20 @@ __device__ int check_termination(const ModelDev &M, const BatchDev &B, const Set
   return 0;
 }
 
+// time_limit (src/osqp.c:389-405).  The reference tests its run time at the top of every iteration; the batch
+// kernels test at the iterations that run a termination check (every 25th when the checks are off), where the
+// residuals are at hand, so a time-limited instance stops at a multiple of check_termination.
+__device__ __forceinline__ bool time_is_up(const BatchDev &B, const SettingsDev &S) {
+  if (S.time_limit_ns <= 0) return false;
+  unsigned long long now;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+  const unsigned long long t0 = *reinterpret_cast<const volatile unsigned long long *>(B.sched + kSchedT0);
+  return (long long)(now - t0) >= S.time_limit_ns;
+}
+__device__ __forceinline__ bool time_check_due(const SettingsDev &S, int iter, bool can_check) {
+  return S.time_limit_ns > 0 && (can_check || (!S.check_termination && iter % 25 == 0));
+}
+
 // compute_rho_estimate (auxil.c:13-55)
 __device__ __forceinline__ double rho_estimate(const Resid &R, double rho) {
   const double pr = R.pri / (fmax(R.nz, R.nAx) + 1e-10);

@@ -102,11 +102,13 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
   }
   double rho = B.rho[inst];
   int status = -10, rho_updates = 0, can_check = 0, iter;
+  bool timed_out = false;
   double obj = 0.0, rho_est = rho;
   Resid R = {0, 0, 0, 0, 0, 0, 0, 0};
   for (iter = 1; iter <= S.max_iter; iter++) {
     can_check = S.check_termination && (iter % S.check_termination == 0);
-    const bool store_delta = can_check || iter == S.max_iter;
+    const bool time_due = time_check_due(S, iter, can_check);
+    const bool store_delta = can_check || iter == S.max_iter || time_due;
     kkt_sweep<32, false>(M, B, S, inst, lane, FULL, sm, nullptr, store_delta);
     __syncwarp();
     if (can_check) {
@@ -129,6 +131,11 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
         if (flag) { status = -7; obj = kOsqpNan; if (lane == 0) B.fact_flag[inst] = flag; break; }
       }
     }
+    if (time_due) {  // osqp.c:389-405
+      int up = lane == 0 ? (int)time_is_up(B, S) : 0;
+      up = __shfl_sync(FULL, up, 0);
+      if (up) { timed_out = true; break; }
+    }
   }
   int it_done = (iter > S.max_iter) ? S.max_iter : iter;
   if (status == -10) {
@@ -137,8 +144,8 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
       obj = R.obj;
       check_termination<32>(M, B, S, inst, lane, FULL, sm, R, 0, &status, &obj);
     }
-    if (status == -10) {  // osqp.c:562-567
-      if (!check_termination<32>(M, B, S, inst, lane, FULL, sm, R, 1, &status, &obj)) status = -2;
+    if (status == -10) {  // osqp.c:562-567 (max_iter) and :570-576 (time limit)
+      if (!check_termination<32>(M, B, S, inst, lane, FULL, sm, R, 1, &status, &obj)) status = timed_out ? -6 : -2;
     }
   }
   const bool has_sol = !(status == -3 || status == 3 || status == -4 || status == 4 || status == -7);
@@ -242,6 +249,23 @@ __global__ void k_fill(double *p, double v, size_t n) {
   for (; i < n; i += st) p[i] = v;
 }
 
+// %globaltimer at the start of a solve: the reference point of the device-side time_limit test
+__global__ void k_mark_time(int *sched) {
+  unsigned long long now;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+  *reinterpret_cast<unsigned long long *>(sched + kSchedT0) = now;
+}
+cudaError_t launch_mark_time(const BatchDev &B, cudaStream_t st) {
+  k_mark_time<<<1, 1, 0, st>>>(B.sched);
+  return cudaGetLastError();
+}
+
+__global__ void k_fill_int(int *p, int v, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t st = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += st) p[i] = v;
+}
+
 // strided scatter of a [batch][len] host-staged block into rows [start,start+len)
 __global__ void k_scatter_rows(double *dst, int ld, const double *src, int len, int start, int batch) {
   const size_t tot = (size_t)batch * len;
@@ -340,6 +364,14 @@ cudaError_t launch_fill(double *p, double v, size_t n, cudaStream_t st) {
   size_t blocks = (n + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
   k_fill<<<(unsigned)blocks, 256, 0, st>>>(p, v, n);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_fill_int(int *p, int v, size_t n, cudaStream_t st) {
+  if (!n) return cudaSuccess;
+  size_t blocks = (n + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  k_fill_int<<<(unsigned)blocks, 256, 0, st>>>(p, v, n);
   return cudaGetLastError();
 }
 

@@ -18,20 +18,30 @@ cudaError_t launch_check_bounds(const double *l, const double *u, int ld, int m,
                                 cudaStream_t st);
 cudaError_t launch_shift_rows(double *v, int ld, int len, int sh, int batch, cudaStream_t st);
 cudaError_t launch_fill(double *p, double v, size_t n, cudaStream_t st);
+cudaError_t launch_mark_time(const BatchDev &B, cudaStream_t st);
+cudaError_t launch_fill_int(int *p, int v, size_t n, cudaStream_t st);
 cudaError_t launch_scatter_rows(double *dst, int ld, const double *src, int len, int start, int batch,
                                 cudaStream_t st);
 // streaming path (rldl_stream.cu)
 bool stream_supported(const ModelDev &M, int N);
 void stream_record_dims(const ModelDev &M, int *qa, int *PX, int *PS, int *bb, int *bd, int *PXX);
-cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,
-                                cudaStream_t st);
+// vector part of the stage records (parts bit 0: q; bit 1: row classes, rho_vec, l, u + change flags)
+cudaError_t launch_vec_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,
+                               int *changed, cudaStream_t st);
+// launch knobs of the streaming kernel (rldl_batch_set_tuning; 0 / -1 = the measured default)
+struct StreamTuning {
+  int ring_depth = 0;   // stage records in flight per lane group (default 2)
+  int sched_s0 = -1;    // iterations a fresh instance runs before it may yield (default check_termination; 0 = scheduler off)
+  int ctas_per_sm = 0;  // resident CTAs per SM (default 4 with the latency-mode hand-off, 3 without)
+};
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                               int resume, int park_below, cudaStream_t st);
+                               int resume, int park_below, const StreamTuning &tune, cudaStream_t st);
 // latency-mode kernel (rldl_latency.cu): one instance per CTA, factor resident in shared memory
 int latency_t_blocks(int Nmax);  // nx x (nx+2) blocks of global scratch per CTA of the latency-mode kernel
 size_t latency_smem_bytes(const ModelDev &M, int N);  // (size_t)-1 if the shape is not in the table
 cudaError_t launch_admm_latency(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                int resume, double *Tg, int ctas, int reset_parked, cudaStream_t st);
+                                int resume, double *Tg, int ctas, int reset_parked, int from_buckets,
+                                cudaStream_t st);
 cudaError_t launch_factor_stream(const ModelDev &M, const BatchDev &B, double sigma, int k0,
                                  const int *only_flagged, int write_unpacked, cudaStream_t st);
 }  // namespace rldl

@@ -68,7 +68,7 @@ struct LatLayout {  // shared-memory layout (doubles) of k_admm_cta for horizon 
 
 template <class SH>
 __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDev B, SettingsDev S, int warm_start,
-                                                              int resume, double *Tg) {
+                                                              int resume, double *Tg, int from_buckets) {
   constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, NT = SH::NT, CW = SH::CW, G = SH::G, NYT = SH::NYT,
                 ROWS = SH::ROWS, RS = SH::RS, BQ = SH::B, AE = SH::AE, NXE = SH::NXE, NG = LatLayout<SH>::NG;
   extern __shared__ __align__(16) double smem[];
@@ -274,8 +274,20 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
   auto item_hi = [&](int it) -> int { return it == 0 ? 0 : (it <= J ? 2 * it : N); };
 
   for (;;) {
-    // ---------------- claim an instance (same counter / resume rules as the streaming kernel) ----------------
-    if (threadIdx.x == 0) {
+    // ---------------- claim an instance ----------------
+    // from_buckets: the tail of a streaming launch — every unfinished instance sits suspended in its priority
+    // bucket; the most-unconverged ones (the longest remaining chains) are resumed first.
+    // otherwise: the fresh counter, with the same resume rules as the streaming kernel.
+    if (threadIdx.x == 0 && from_buckets) {
+      int i = -1;
+      for (int b = kSchedBuckets - 1; b >= 0 && i < 0; b--)
+        while (ld_volatile(B.sched + 2 + kSchedBuckets + b) > ld_volatile(B.sched + 2 + b)) {
+          i = sched_pop(B, b);
+          if (i >= 0) break;
+        }
+      if (i >= 0) __threadfence();  // order the loads of the iterates after the hand-over
+      ctl[0] = i;
+    } else if (threadIdx.x == 0) {
       int i = -1;
       for (;;) {
         i = atomicAdd(B.sched, 1);
@@ -454,7 +466,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       const bool can_check = S.check_termination && (iter % S.check_termination == 0);
       const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval && (iter % S.adaptive_rho_interval == 0);
       const bool last = iter == S.max_iter;
-      const bool store_delta = can_check || last;
+      const bool time_due = time_check_due(S, iter, can_check);
+      const bool store_delta = can_check || last || time_due;
       // ===== phases B and C, pipelined.  B (group 0): sp_k = c_k + T_k sp_{k-1}, in place in vc.
       //       C (groups 2..): e_k = a_k + Xinv_k (F_k' sp_k - J' sp_{k-1}), d_k = e_k[0:nx], as soon as the scan
       //       has published sp_k =====
@@ -591,7 +604,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
        }
        pre_fwd(it);
       }
-      if (!(can_check || can_adapt || last)) {
+      if (!(can_check || can_adapt || last || time_due)) {
         __syncthreads();  // iterates of this iteration visible to every group of the CTA
         PT(4);
         continue;
@@ -737,13 +750,18 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
             rho_new = fmin(fmax(rn, kRhoMin), kRhoMax);
           }
         }
-        if (!done && last) {
+        bool timed_out = false;
+        if (!done && time_due && !last) {  // osqp.c:389-405
+          int up = gl == 0 ? (int)time_is_up(B, S) : 0;
+          timed_out = __shfl_sync(gm, up, 0, G) != 0;
+        }
+        if (!done && (last || timed_out)) {
           if (!can_check) {
             obj = R.obj;
             check_term(0);
           }
-          if (status == -10) {
-            if (!check_term(1)) status = -2;
+          if (status == -10) {  // osqp.c:562-576
+            if (!check_term(1)) status = timed_out ? -6 : -2;
           }
           done = true;
         }
@@ -808,7 +826,8 @@ static size_t latency_smem_t(int N) {
 
 template <class SH>
 static cudaError_t launch_latency_t(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                    int resume, double *Tg, int ctas, int reset_parked, cudaStream_t st) {
+                                    int resume, double *Tg, int ctas, int reset_parked, int from_buckets,
+                                    cudaStream_t st) {
   const size_t shm = latency_smem_t<SH>(B.N);
   auto kern = k_admm_cta<SH>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm);
@@ -816,7 +835,7 @@ static cudaError_t launch_latency_t(const ModelDev &M, const BatchDev &B, const 
   // fresh counter; the parked-for-rho counter only if no streaming launch of this round has counted into it
   e = cudaMemsetAsync(B.sched, 0, (reset_parked ? 2 : 1) * sizeof(int), st);
   if (e != cudaSuccess) return e;
-  kern<<<(unsigned)ctas, kLatThreads, shm, st>>>(M, B, S, warm_start, resume, Tg);
+  kern<<<(unsigned)ctas, kLatThreads, shm, st>>>(M, B, S, warm_start, resume, Tg, from_buckets);
   return cudaGetLastError();
 }
 
@@ -832,11 +851,13 @@ size_t latency_smem_bytes(const ModelDev &M, int N) {
 }
 
 cudaError_t launch_admm_latency(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                int resume, double *Tg, int ctas, int reset_parked, cudaStream_t st) {
+                                int resume, double *Tg, int ctas, int reset_parked, int from_buckets,
+                                cudaStream_t st) {
   const int cw = max_c_width(M);
 #define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                    \
   if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))         \
-    return launch_latency_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, Tg, ctas, reset_parked, st);
+    return launch_latency_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, Tg, ctas, reset_parked, \
+                                                                 from_buckets, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;

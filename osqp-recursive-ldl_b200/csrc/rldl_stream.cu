@@ -37,115 +37,97 @@
 namespace rldl {
 
 // ---------------------------------------------------------------------------
-// Record packing: (Xinv, Sinv, q, l, u, rho_vec) -> rec, stages k0..N of every instance.
-// One thread per record element.
+// Vector part of the stage records, stages k0..N of every instance, straight from the flat per-instance
+// vectors (one warp per instance, the rows of a stage across the lanes: coalesced reads of q, l, u and
+// coalesced writes of the record parts):
+//   parts bit 0: q_k
+//   parts bit 1: constraint typing of every row from (l, u) (reference src/auxil.c:79-145: loose / equality /
+//                inequality), written as the 2-bit class words of the record and as rho_vec (the per-row values
+//                the runtime-shape kernels and the scalar API read), l_k, u_k; the instance's rho is clipped to
+//                [RHO_MIN, RHO_MAX] and an instance parked by an adaptive-rho update becomes resumable again.
+//                changed[inst] = 1 iff a class differs from the one the record held (update_rho_vec's
+//                "constr_type_changed": the caller re-runs the stage recursion for those instances only) or the
+//                instance was parked by an adaptive-rho update.
+//   parts bit 2: touch only the instances parked by an adaptive-rho update (the others get changed = 0).
+// Replaces the k_set_rho_vec + k_pack_records pair of round 1 (two passes over rho_vec with per-element
+// index decoding) by one pass at streaming speed.
 // ---------------------------------------------------------------------------
-__global__ void k_pack_records(ModelDev M, BatchDev B, int k0, int parts /*bit0 factor, bit1 vectors*/,
-                               const int *only_flagged) {
-  const int a = M.a, nx = M.nx, b = M.b, nt = M.nt, N = B.N;
-  const int ns = N + 1 - k0;
-  const long long total = (long long)B.batch * ns * B.RS;
-  long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long step = (long long)gridDim.x * blockDim.x;
-  for (; t < total; t += step) {
-    const int e = (int)(t % B.RS);
-    const long long rest = t / B.RS;
-    const int k = k0 + (int)(rest % ns);
-    const int inst = (int)(rest / ns);
-    if (only_flagged && !only_flagged[inst]) continue;
+__device__ __forceinline__ unsigned long long spread_bits(unsigned v) {  // bit r -> bit 2r
+  unsigned long long x = v;
+  x = (x | (x << 16)) & 0x0000ffff0000ffffull;
+  x = (x | (x << 8)) & 0x00ff00ff00ff00ffull;
+  x = (x | (x << 4)) & 0x0f0f0f0f0f0f0f0full;
+  x = (x | (x << 2)) & 0x3333333333333333ull;
+  x = (x | (x << 1)) & 0x5555555555555555ull;
+  return x;
+}
+
+template <class SH>
+__global__ void __launch_bounds__(256) k_vec_records(BatchDev B, int k0, int parts, const int *only_flagged,
+                                                     int *changed) {
+  constexpr int A = SH::A, NX = SH::NX, NT = SH::NT, BQ = SH::B, RS = SH::RS;
+  const int lane = threadIdx.x & 31;
+  const int inst = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  if (inst >= B.batch) return;
+  if (only_flagged && !only_flagged[inst]) return;
+  const bool parked = B.status[inst] == kStatusParkedRho;
+  if ((parts & 4) && !parked) {  // adaptive-rho refresh: only the parked instances
+    if (changed && lane == 0) changed[inst] = 0;
+    return;
+  }
+  const int N = B.N;
+  const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
+  const double rho = fmin(fmax(B.rho[inst], kRhoMin), kRhoMax);
+  double *rec = B.rec + (size_t)inst * B.rec_stride;
+  int ch = parked ? 1 : 0;  // a parked instance has a new rho: its recursion is re-run whatever its row types
+#pragma unroll 2
+  for (int k = k0; k <= N; k++) {
     const bool term = (k == N);
-    double *dst = B.rec + (long long)inst * B.rec_stride + (long long)k * B.RS + e;
-    const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
-    int o = e;
-    if (o < B.qa) {  // q_k
-      if (!(parts & 2)) continue;
-      const int dim = term ? nx : a, ilo = (k == 0 && !term) ? nx : 0, xoff = k * a - nx;
-      *dst = (o >= ilo && o < dim) ? B.q[vo + xoff + o] : 0.0;
-      continue;
+    double *rk = rec + (size_t)k * RS;
+    if (parts & 1) {
+      const int dim = term ? NX : A, ilo = (k == 0 && !term) ? NX : 0, xoff = k * A - NX;
+      for (int o = lane; o < SH::QA; o += 32) rk[o] = (o >= ilo && o < dim) ? B.q[vo + xoff + o] : 0.0;
     }
-    o -= B.qa;
-    if (o < B.PX) {  // Xinv_k, a x a diagonal-packed (terminal: [Xinv_N 0; 0 I])
-      if (!(parts & 1)) continue;
-      double v = 0.0;
-      int i = -1, j = -1;  // the entry of the a x a block this element holds
-      if (!B.bd) {
-        if (o < dp_size(a)) {
-          const int d = o / a;
-          i = o - d * a;
-          j = i + d;
-          if (j >= a) j -= a;
+    if (parts & 2) {
+      const int rows = term ? NT : BQ;
+#pragma unroll
+      for (int w = 0; w < kClsWords; w++) {
+        if (32 * w >= SH::BB) break;
+        const int r = 32 * w + lane;
+        double lv = 0.0, uv = 0.0;
+        int c = 0;
+        if (r < rows) {
+          const size_t ri = ro + (size_t)k * BQ + r;
+          lv = B.l[ri]; uv = B.u[ri];
+          c = (lv < -kInfBound && uv > kInfBound) ? 2 : ((uv - lv < kRhoTol) ? 1 : 0);
+          B.rho_vec[ri] = c == 2 ? kRhoMin : (c == 1 ? kRhoEq * rho : rho);
         }
-      } else if (o < B.PXX) {  // block-diagonal pivots: the nx x nx block, then the nu x nu block
-        if (o < dp_size(nx)) {
-          const int d = o / nx;
-          i = o - d * nx;
-          j = i + d;
-          if (j >= nx) j -= nx;
+        const unsigned long long wv = spread_bits(__ballot_sync(FULL, c == 1)) |
+                                      (spread_bits(__ballot_sync(FULL, c == 2)) << 1);
+        if (lane == 0) {
+          const unsigned long long old = (unsigned long long)__double_as_longlong(rk[SH::CLS + w]);
+          if (old != wv) ch = 1;
+          rk[SH::CLS + w] = __longlong_as_double((long long)wv);
         }
-      } else {
-        const int nu = a - nx, ou = o - B.PXX;
-        if (ou < dp_size(nu)) {
-          const int d = ou / nu;
-          i = ou - d * nu;
-          j = i + d;
-          if (j >= nu) j -= nu;
-          i += nx; j += nx;
-        }
+        if (r < SH::BB) { rk[SH::LO + r] = lv; rk[SH::UP + r] = uv; }
       }
-      if (i >= 0) {
-        const double *Xk = B.Xinv + (size_t)inst * B.xstride + (size_t)k * a * a;
-        if (!term) v = (i >= j) ? Xk[j * a + i] : Xk[i * a + j];  // lower triangle of the stored inverse
-        else v = (i < nx && j < nx) ? ((i >= j) ? Xk[j * nx + i] : Xk[i * nx + j]) : (i == j ? 1.0 : 0.0);
-      }
-      *dst = v;
-      continue;
+#pragma unroll
+      for (int w = (SH::BB + 31) / 32; w < kClsWords; w++)
+        if (lane == 0) rk[SH::CLS + w] = 0.0;
     }
-    o -= B.PX;
-    if (o < B.PS) {  // Sinv_k, nx x nx diagonal-packed
-      if (!(parts & 1)) continue;
-      double v = 0.0;
-      if (!term && o < dp_size(nx)) {
-        const int d = o / nx, i = o - d * nx;
-        int j = i + d;
-        if (j >= nx) j -= nx;
-        const double *Sk = B.Sinv + (size_t)inst * B.sstride + (size_t)k * nx * nx;
-        v = (i >= j) ? Sk[j * nx + i] : Sk[i * nx + j];
-      }
-      *dst = v;
-      continue;
-    }
-    o -= B.PS;
-    if (!(parts & 2)) continue;
-    const int rows = term ? nt : b;
-    if (o < kClsWords) {  // 2-bit classes of rows 32*o .. 32*o+31: 0 inequality, 1 equality, 2 loose
-      const double rho_in = B.rho[inst];
-      unsigned long long wv = 0ull;
-      for (int r = 32 * o; r < 32 * o + 32 && r < rows; r++) {
-        const double rv = B.rho_vec[ro + (size_t)k * b + r];
-        const unsigned long long cl = (rv == kRhoMin) ? 2ull : (rv == rho_in ? 0ull : 1ull);
-        wv |= cl << (2 * (r & 31));
-      }
-      *dst = __longlong_as_double((long long)wv);
-      continue;
-    }
-    o -= kClsWords;
-    const int which = o / B.bb, r = o - which * B.bb;
-    double v = 0.0;
-    if (r < rows) {
-      const size_t ri = ro + (size_t)k * b + r;
-      v = which == 0 ? B.l[ri] : B.u[ri];
-    }
-    *dst = v;
+  }
+  if ((parts & 2) && lane == 0) {
+    B.rho[inst] = rho;
+    if (changed) changed[inst] = ch;
+    if (B.status[inst] == kStatusParkedRho) B.status[inst] = -10;  // parked for this refresh: resumable again
   }
 }
 
-cudaError_t launch_pack_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,
-                                cudaStream_t st) {
-  const long long total = (long long)B.batch * (B.N + 1 - k0) * B.RS;
-  if (total <= 0) return cudaSuccess;
-  long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 32) blocks = 148 * 32;
-  k_pack_records<<<(unsigned)blocks, 256, 0, st>>>(M, B, k0, parts, only_flagged);
+template <class SH>
+static cudaError_t launch_vec_records_t(const BatchDev &B, int k0, int parts, const int *only_flagged, int *changed,
+                                        cudaStream_t st) {
+  const int threads = 256, wpb = threads / 32;
+  k_vec_records<SH><<<(B.batch + wpb - 1) / wpb, threads, 0, st>>>(B, k0, parts, only_flagged, changed);
   return cudaGetLastError();
 }
 
@@ -180,27 +162,6 @@ found:
 // priority early.  Buckets are multi-producer/multi-consumer rings of capacity `batch` (an
 // instance sits in at most one ring), heads claimed by CAS, slots handed over with atomicExch.
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ int ld_volatile(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
-
-__device__ __forceinline__ void sched_push(const BatchDev &B, int b, int inst) {
-  const int idx = atomicAdd(B.sched + 2 + kSchedBuckets + b, 1);
-  int *sl = B.sched_slots + (size_t)b * B.batch + (idx % B.batch);
-  while (atomicCAS(sl, -1, inst) != -1) __nanosleep(32);
-}
-__device__ __forceinline__ int sched_pop(const BatchDev &B, int b) {
-  int *head = B.sched + 2 + b;
-  const int *tail = B.sched + 2 + kSchedBuckets + b;
-  for (;;) {
-    const int h = ld_volatile(head), t = ld_volatile(tail);
-    if (h >= t) return -1;
-    if (atomicCAS(head, h, h + 1) == h) {
-      int *sl = B.sched_slots + (size_t)b * B.batch + (h % B.batch);
-      int v;
-      while ((v = atomicExch(sl, -1)) < 0) __nanosleep(32);
-      return v;
-    }
-  }
-}
 // highest non-empty bucket (-1 if none); every lane of the group scans a strided share
 template <int G>
 __device__ __forceinline__ int sched_best(const BatchDev &B, int gl, unsigned gm) {
@@ -343,7 +304,9 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   auto tail_reached = [&]() -> bool {  // few enough instances left: they go to the latency-mode kernel
     int t = 0;
     if (park_below > 0) {
-      if (gl == 0) t = ld_volatile(B.sched + kSchedUnfinished) <= park_below;
+      // only once every instance has been started by this kernel: the latency-mode kernel resumes suspended
+      // instances, it never starts one (an instance that was never claimed has no saved iteration count)
+      if (gl == 0) t = ld_volatile(B.sched) >= B.batch && ld_volatile(B.sched + kSchedUnfinished) <= park_below;
       t = __shfl_sync(gm, t, 0, G);
     }
     return t != 0;
@@ -442,7 +405,8 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       iter++;
       const bool can_check = S.check_termination && (iter % S.check_termination == 0);
       const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval && (iter % S.adaptive_rho_interval == 0);
-      const bool store_delta = can_check || iter == S.max_iter;
+      const bool time_due = time_check_due(S, iter, can_check);
+      const bool store_delta = can_check || iter == S.max_iter || time_due;
       double yv_reg = 0.0;  // this lane's entry of Xinv*t of the last forward stage
       MutVec<NYT> nxt;
       // =============================== forward sweep ===============================
@@ -583,14 +547,19 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           rho_new = fmin(fmax(rn, kRhoMin), kRhoMax);
         }
       }
-      if (!done && iter == S.max_iter) {
+      bool timed_out = false;
+      if (!done && time_due && iter != S.max_iter) {  // osqp.c:389-405
+        int up = gl == 0 ? (int)time_is_up(B, S) : 0;
+        timed_out = __shfl_sync(gm, up, 0, G) != 0;
+      }
+      if (!done && (iter == S.max_iter || timed_out)) {
         if (!can_check) {
           R = compute_residuals<G>(M, B, inst, gl, gm, rs);
           obj = R.obj;
           check_termination<G>(M, B, S, inst, gl, gm, rs, R, 0, &status, &obj);
         }
-        if (status == -10) {
-          if (!check_termination<G>(M, B, S, inst, gl, gm, rs, R, 1, &status, &obj)) status = -2;
+        if (status == -10) {  // osqp.c:562-576: approximate check, else max_iter / time limit reached
+          if (!check_termination<G>(M, B, S, inst, gl, gm, rs, R, 1, &status, &obj)) status = timed_out ? -6 : -2;
         }
         done = true;
       }
@@ -637,8 +606,12 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         drain();
         have = start_next();
       } else if (can_check && tail_reached()) {
-        // suspended as it stands (status stays OSQP_UNSOLVED): the latency-mode kernel resumes it
+        // suspended as it stands (status stays OSQP_UNSOLVED) into its priority bucket: the latency-mode kernel
+        // resumes the suspended instances most-unconverged first (the longest remaining chains start first)
         if (gl == 0) B.iter[inst] = iter;
+        __threadfence();
+        __syncwarp(gm);
+        if (gl == 0) sched_push(B, urgency_bucket(S, R), inst);
         drain();
         have = false;
       } else {
@@ -646,10 +619,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         int myb = 0;
         if (sched_on && can_check) {
           // urgency of this instance: distance from its tolerances (auxil.c:259-288, 323-362)
-          const double ep = S.eps_abs + S.eps_rel * fmax(R.nz, R.nAx);
-          const double ed = S.eps_abs + S.eps_rel * fmax(fmax(R.nq, R.nAty), R.nPx);
-          const double ratio = fmax(R.pri / ep, R.dua / ed);
-          myb = ratio > 1.0 ? min(kSchedBuckets - 1, (int)(2.0 * log2(ratio))) : 0;
+          myb = urgency_bucket(S, R);
           int fresh_left = 0;
           if (gl == 0) fresh_left = ld_volatile(B.sched) < B.batch;
           fresh_left = __shfl_sync(gm, fresh_left, 0, G);
@@ -675,13 +645,12 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
 // ------------------------------- launcher --------------------------------
 template <class SH>
 static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                   int resume, int park_below, cudaStream_t st) {
+                                   int resume, int park_below, const StreamTuning &tune, cudaStream_t st) {
   const int threads = 128, groups = (threads / 32) * SH::GPW;
-  int D = 2;  // ring depth: two stage steps of look-ahead cover the HBM latency
-  if (const char *e = getenv("RLDL_RING_DEPTH")) D = atoi(e) > 1 ? atoi(e) : 2;
+  int D = tune.ring_depth > 1 ? tune.ring_depth : 2;  // two stage steps of look-ahead cover the HBM latency
   if (D > 2 * (B.N + 1)) D = 2 * (B.N + 1);
-  int s0 = S.check_termination;  // fresh instances run up to their first check before they may yield
-  if (const char *e = getenv("RLDL_SCHED_S0")) s0 = atoi(e);
+  // fresh instances run up to their first check before they may yield (sched_s0 = 0 turns the scheduler off)
+  const int s0 = tune.sched_s0 >= 0 ? tune.sched_s0 : S.check_termination;
   const size_t shm = ((size_t)SH::M_END + (size_t)groups * SH::group_doubles(D)) * sizeof(double);
   if (shm > 220 * 1024) return cudaErrorInvalidValue;
   auto kern = k_admm_stream<SH>;
@@ -696,8 +665,7 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   // 3 CTAs/SM nearly saturate the memory system; a 4th adds 2.5 % of bulk throughput but lengthens every
   // instance's iteration (the machine is shared equally) and with it the chain of the longest instance — a net
   // loss (1 316 vs 1 273 ms at C5) unless the latency-mode kernel takes the tail over (1 147 vs 1 174 ms)
-  int cap = park_below > 0 ? 4 : 3;
-  if (const char *e = getenv("RLDL_CTAS_PER_SM")) cap = atoi(e) > 0 ? atoi(e) : cap;
+  const int cap = tune.ctas_per_sm > 0 ? tune.ctas_per_sm : (park_below > 0 ? 4 : 3);
   if (per_sm > cap) per_sm = cap;
   long long grid = (long long)sms * per_sm;
   const long long need = ((long long)B.batch + groups - 1) / groups;
@@ -725,12 +693,13 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
 //   X_{k+1} = M_{k+1} + J' S_k^-1 J
 // ---------------------------------------------------------------------------
 template <int NP, int NE>
-__device__ __forceinline__ void sweep_rows(double (&X)[NP], double *rowbuf, int gl, unsigned gm, int &bad) {
-  // X = this lane's row of an NP x NP SPD block (lanes >= NP hold zero rows); NE = even_up(NP)
+__device__ __forceinline__ void sweep_rows(double (&X)[NP], double *rowbuf, int row, unsigned gm, int &bad) {
+  // X = this lane's row `row` of an NP x NP SPD block (lanes with row outside [0, NP) hold zero rows and stay
+  // zero); NE = even_up(NP)
 #pragma unroll
   for (int p = 0; p < NP; p++) {
     double *buf = rowbuf + (p & 1) * NE;
-    if (gl == p) {
+    if (row == p) {
 #pragma unroll
       for (int j = 0; j < NP; j++) buf[j] = X[j];
     }
@@ -740,21 +709,25 @@ __device__ __forceinline__ void sweep_rows(double (&X)[NP], double *rowbuf, int 
     for (int j = 0; j < NP; j++) rp[j] = buf[j];
     if (!(rp[p] > 0.0)) bad = 1;
     const double d = 1.0 / rp[p];
-    const double f = (gl == p) ? (1.0 - d) : X[p] * d;
+    const double f = (row == p) ? (1.0 - d) : X[p] * d;
 #pragma unroll
     for (int j = 0; j < NP; j++)
       if (j != p) X[j] = fma(-f, rp[j], X[j]);
-    X[p] = (gl == p) ? -d : f;
+    X[p] = (row == p) ? -d : f;
   }
 #pragma unroll
   for (int j = 0; j < NP; j++) X[j] = -X[j];
 }
 
+// BD (block-diagonal pivots, every BASELINE model): X_k = blkdiag(X^xx_k, X^uu_k), so the state block (lanes < NX)
+// and the input block (lanes NX..A-1) are swept separately — 12^3 + 4^3 instead of 16^3 multiply-adds at C5 — and
+// W = Xinv F' only multiplies the non-zero block of each row.
 template <class SH>
 __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B, double sigma, int k0,
                                                           const int *only_flagged, int write_unpacked) {
-  constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, CW = SH::CW, G = SH::G, RS = SH::RS, BQ = SH::B;
-  constexpr int AE = SH::AE, NXE = SH::NXE;
+  constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, CW = SH::CW, G = SH::G, RS = SH::RS;
+  constexpr int AE = SH::AE, NXE = SH::NXE, NU = SH::NU, BD = SH::BD;
+  constexpr int XW = BD ? NX : A;                                 // width of the register row of the (state) block
   constexpr int TB = A * A > A * NXE ? A * A : A * NXE;          // transposition buffer (doubles)
   constexpr int M_F = 0, M_FT = M_F + 2 * A * NX, M_Q = M_FT + 2 * A * NX, M_C2 = M_Q + 3 * A * A,
                 M_CI = M_C2 + 3 * AE, M_END = (M_CI + (3 * AE + 1) / 2 + 1) & ~1;
@@ -764,6 +737,7 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
   const unsigned gm = (G == 32) ? FULL : (((1u << G) - 1u) << (gw * G));
   const int grp = wid * SH::GPW + gw, groups = (blockDim.x >> 5) * SH::GPW;
   const int N = B.N;
+  (void)CW;
 
   // ---- CTA-shared model: dense F / F' (class 0, 1), Q blocks padded to A x A, squared C' entries ----
   double *Fd = smem + M_F, *FdT = smem + M_FT, *Qs = smem + M_Q, *c2 = smem + M_C2;
@@ -799,10 +773,14 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
   __syncthreads();
   double *gbuf = smem + M_END + (size_t)grp * (2 * AE + TB);
   double *rowbuf = gbuf, *tb = gbuf + 2 * AE;
+  const int urow = gl - NX;  // this lane's row of the input block (BD), negative on the state lanes
 
   for (int inst = blockIdx.x * groups + grp; inst < B.batch; inst += gridDim.x * groups) {
     if (only_flagged && !only_flagged[inst]) continue;
-    const double *rv = B.rho_vec + (size_t)inst * B.mmax;
+    // per-row step sizes from the 2-bit row classes of the record (written by k_vec_records) and the
+    // instance's rho: no rho_vec traffic
+    const double rho_in = B.rho[inst], rho_eq = kRhoEq * rho_in;
+    const double inv_in = 1.0 / rho_in, inv_eq = 1.0 / rho_eq, inv_min = 1.0 / kRhoMin;
     double *rec = B.rec + (size_t)inst * B.rec_stride;
     double Sx[NX];  // row gl of Sinv_{k-1} (lanes < NX)
 #pragma unroll
@@ -822,36 +800,64 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
       const bool term = (k == N);
       const int cls = term ? 2 : (k == 0 ? 0 : 1);
       const int dim = term ? NX : A;
-      const int roff = k * BQ;
       double *rk = rec + (size_t)k * RS;
-      // ---- X_k row gl ----
-      double Xr[A];
-#pragma unroll
-      for (int j = 0; j < A; j++) Xr[j] = (gl < A) ? Qs[cls * A * A + j * A + gl] : 0.0;
+      // ---- X_k row gl (BD: the row of the state block in Xr, the row of the input block in Xu) ----
+      double Xr[XW], Xu[BD ? NU : 1];
+      double dg = 0.0;
       if (gl < dim) {
-        double dg = sigma;
+        dg = sigma;
         const double cc = c2[cls * AE + gl];
-        if (cc != 0.0) dg = fma(cc, rv[roff + ci[cls * AE + gl]], dg);
-#pragma unroll
-        for (int j = 0; j < A; j++)
-          if (j == gl) Xr[j] += dg;
-        if (k > 0 && gl < NX) {
-#pragma unroll
-          for (int j = 0; j < NX; j++) Xr[j] += Sx[j];
+        if (cc != 0.0) {
+          const int rc = row_class(rk + SH::CLS, ci[cls * AE + gl]);
+          dg = fma(cc, rc == 0 ? rho_in : (rc == 1 ? rho_eq : kRhoMin), dg);
         }
       }
+      if constexpr (BD) {
+#pragma unroll
+        for (int j = 0; j < NX; j++) {
+          Xr[j] = (gl < NX) ? Qs[cls * A * A + j * A + gl] : 0.0;
+          if (j == gl) Xr[j] += dg;
+          if (k > 0 && gl < NX) Xr[j] += Sx[j];
+        }
+#pragma unroll
+        for (int j = 0; j < NU; j++) {
+          Xu[j] = (urow >= 0 && gl < A) ? Qs[cls * A * A + (NX + j) * A + gl] : 0.0;
+          if (j == urow && gl < A) Xu[j] += dg;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < A; j++) {
+          Xr[j] = (gl < A) ? Qs[cls * A * A + j * A + gl] : 0.0;
+          if (j == gl) Xr[j] += dg;
+          if (k > 0 && gl < NX && j < NX) Xr[j] += Sx[j < NX ? j : 0];
+        }
+        Xu[0] = 0.0;
+      }
       int bad = 0;
-      sweep_rows<A, AE>(Xr, rowbuf, gl, gm, bad);
+      if constexpr (BD) {
+        sweep_rows<NX, NXE>(Xr, rowbuf, gl, gm, bad);
+        __syncwarp(gm);  // the second sweep reuses the pivot-row line
+        sweep_rows<NU, ((NU + 1) & ~1)>(Xu, rowbuf, urow, gm, bad);
+      } else {
+        sweep_rows<A, AE>(Xr, rowbuf, gl, gm, bad);
+      }
       if (bad && !flag) flag = 1 + k;
       // ---- store Xinv_k: diagonal-packed into the record (and unpacked on request) ----
       __syncwarp(gm);
-      if (gl < A) {
+      if constexpr (BD) {
+        if (gl < NX) {
 #pragma unroll
-        for (int j = 0; j < A; j++) tb[j * A + gl] = Xr[j];  // symmetric: column-major == row-major
+          for (int j = 0; j < NX; j++) tb[j * A + gl] = Xr[j];  // symmetric: column-major == row-major
+        } else if (gl < A) {
+#pragma unroll
+          for (int j = 0; j < NU; j++) tb[(NX + j) * A + gl] = Xu[j];
+        }
+      } else if (gl < A) {
+#pragma unroll
+        for (int j = 0; j < A; j++) tb[j * A + gl] = Xr[j];
       }
       __syncwarp(gm);
-      if constexpr (SH::BD) {  // the nx x nx block, then the nu x nu block (the cross blocks are exactly zero)
-        constexpr int NU = SH::NU;
+      if constexpr (BD) {  // the nx x nx block, then the nu x nu block (the cross blocks are exactly zero)
         if (gl < NX) {
 #pragma unroll
           for (int d = 0; d <= NX / 2; d++) {
@@ -878,9 +884,22 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
       }
       if (write_unpacked && gl < dim) {
         double *Xk = B.Xinv + (size_t)inst * B.xstride + (size_t)k * A * A + (size_t)gl * dim;
+        if constexpr (BD) {
 #pragma unroll
-        for (int j = 0; j < A; j++)
-          if (j < dim) Xk[j] = Xr[j];
+          for (int j = 0; j < A; j++)
+            if (j < dim) Xk[j] = 0.0;
+          if (gl < NX) {
+#pragma unroll
+            for (int j = 0; j < NX; j++) Xk[j] = Xr[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < NU; j++) Xk[NX + j] = Xu[j];
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < A; j++)
+            if (j < dim) Xk[j] = Xr[j];
+        }
       }
       if (term) break;
       // ---- W = Xinv F' (row gl), S = diag(1/rho_d) + F W (row gl, lanes < NX) ----
@@ -891,15 +910,38 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
       const double *Ft = FdT + (k == 0 ? 0 : A * NX);
       __syncwarp(gm);
       if (gl < A) {
+        if constexpr (BD) {
+          if (gl < NX) {
 #pragma unroll
-        for (int r = 0; r < NX; r++) {
-          double acc0 = 0.0, acc1 = 0.0;
+            for (int r = 0; r < NX; r++) {
+              double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll
-          for (int j = 0; j < A; j += 2) {
-            acc0 = fma(Xr[j], Ft[r * A + j], acc0);
-            if (j + 1 < A) acc1 = fma(Xr[j + 1], Ft[r * A + j + 1], acc1);
+              for (int j = 0; j < NX; j += 2) {
+                acc0 = fma(Xr[j], Ft[r * A + j], acc0);
+                if (j + 1 < NX) acc1 = fma(Xr[j + 1], Ft[r * A + j + 1], acc1);
+              }
+              tb[gl * NXE + r] = acc0 + acc1;
+            }
+          } else {
+#pragma unroll
+            for (int r = 0; r < NX; r++) {
+              double acc = 0.0;
+#pragma unroll
+              for (int j = 0; j < NU; j++) acc = fma(Xu[j], Ft[r * A + NX + j], acc);
+              tb[gl * NXE + r] = acc;
+            }
           }
-          tb[gl * NXE + r] = acc0 + acc1;
+        } else {
+#pragma unroll
+          for (int r = 0; r < NX; r++) {
+            double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+            for (int j = 0; j < A; j += 2) {
+              acc0 = fma(Xr[j], Ft[r * A + j], acc0);
+              if (j + 1 < A) acc1 = fma(Xr[j + 1], Ft[r * A + j + 1], acc1);
+            }
+            tb[gl * NXE + r] = acc0 + acc1;
+          }
         }
       }
       __syncwarp(gm);
@@ -911,7 +953,8 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
         for (int c = 0; c < NX; c++) Sx[c] = fma(Fr[i], tb[i * NXE + c], Sx[c]);
       }
       if (gl < NX) {
-        const double rinv = 1.0 / rv[roff + NY + gl];
+        const int rc = row_class(rk + SH::CLS, NY + gl);
+        const double rinv = rc == 0 ? inv_in : (rc == 1 ? inv_eq : inv_min);
 #pragma unroll
         for (int c = 0; c < NX; c++)
           if (c == gl) Sx[c] += rinv;
@@ -980,11 +1023,22 @@ bool stream_supported(const ModelDev &M, int N) {
 }
 
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                               int resume, int park_below, cudaStream_t st) {
+                               int resume, int park_below, const StreamTuning &tune, cudaStream_t st) {
   const int cw = max_c_width(M);
 #define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                                          \
   if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))      \
-    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, park_below, st);
+    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, park_below, tune, st);
+  RLDL_SHAPES(RLDL_X)
+#undef RLDL_X
+  return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_vec_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,
+                               int *changed, cudaStream_t st) {
+  const int cw = max_c_width(M);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                                          \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))      \
+    return launch_vec_records_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(B, k0, parts, only_flagged, changed, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;

@@ -38,6 +38,37 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 }
 
 
+// ------------------------------ device work scheduler (see rldl_stream.cu) ------------------------------
+__device__ __forceinline__ int ld_volatile(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
+
+__device__ __forceinline__ void sched_push(const BatchDev &B, int b, int inst) {
+  const int idx = atomicAdd(B.sched + 2 + kSchedBuckets + b, 1);
+  int *sl = B.sched_slots + (size_t)b * B.batch + (idx % B.batch);
+  while (atomicCAS(sl, -1, inst) != -1) __nanosleep(32);
+}
+__device__ __forceinline__ int sched_pop(const BatchDev &B, int b) {
+  int *head = B.sched + 2 + b;
+  const int *tail = B.sched + 2 + kSchedBuckets + b;
+  for (;;) {
+    const int h = ld_volatile(head), t = ld_volatile(tail);
+    if (h >= t) return -1;
+    if (atomicCAS(head, h, h + 1) == h) {
+      int *sl = B.sched_slots + (size_t)b * B.batch + (h % B.batch);
+      int v;
+      while ((v = atomicExch(sl, -1)) < 0) __nanosleep(32);
+      return v;
+    }
+  }
+}
+// urgency of an instance at a termination check: how far it is from its tolerances (auxil.c:259-288, 323-362),
+// floor(2*log2(max(r_p/eps_p, r_d/eps_d))) clamped to the bucket range
+__device__ __forceinline__ int urgency_bucket(const SettingsDev &S, const Resid &R) {
+  const double ep = S.eps_abs + S.eps_rel * fmax(R.nz, R.nAx);
+  const double ed = S.eps_abs + S.eps_rel * fmax(fmax(R.nq, R.nAty), R.nPx);
+  const double ratio = fmax(R.pri / ep, R.dua / ed);
+  return ratio > 1.0 ? min(kSchedBuckets - 1, (int)(2.0 * log2(ratio))) : 0;
+}
+
 __host__ __device__ inline int even_up(int v) { return (v + 1) & ~1; }
 // The per-row step size of an instance takes one of three values (constraint typing, reference
 // src/auxil.c:79-101): rho (inequality), 1e3*rho (equality), 1e-6 (loose).  The stage records carry the

@@ -112,7 +112,7 @@ osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions clea
 rldl_batch_setup rldl_batch_solve rldl_batch_update_bounds rldl_batch_partial_update_bounds
 rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
 rldl_batch_refactor rldl_batch_update_model rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_get_solution rldl_batch_get_info
-rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel
+rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel rldl_batch_set_tuning
 rldl_batch_free
 rldl_device_count rldl_set_device rldl_version
 """.split()
@@ -189,6 +189,8 @@ def lib():
                                       "rldl_batch_counters", "rldl_batch_free") else c_int
     L.rldl_batch_select_kernel.argtypes = [vp, c_int]
     L.rldl_batch_select_kernel.restype = c_int
+    L.rldl_batch_set_tuning.argtypes = [vp, C.c_char_p, c_int]
+    L.rldl_batch_set_tuning.restype = c_int
     L.rldl_batch_stream.argtypes = [vp]
     L.rldl_batch_stream.restype = vp
     for name in ("max_iter", "warm_start", "scaled_termination", "check_termination", "polish",
@@ -335,6 +337,13 @@ class Batch:
 
     def select_kernel(self, which):
         return lib().rldl_batch_select_kernel(self.h, which)
+
+    def set_tuning(self, **kw):
+        """rldl_batch_set_tuning: lat_below, ring_depth, sched_s0, ctas_per_sm (-1 = default)."""
+        for k, v in kw.items():
+            rc = lib().rldl_batch_set_tuning(self.h, k.encode(), int(v))
+            if rc:
+                raise ValueError(f"rldl_batch_set_tuning({k!r}, {v}) refused")
 
     def stream(self):
         return lib().rldl_batch_stream(self.h)

@@ -172,3 +172,62 @@ def test_non_convex_stage_cost_is_reported_like_the_reference():
     w = C.POINTER(R.OSQPWorkspace)()
     s = gpu_settings()
     assert L.osqp_setup_recursive(C.byref(w), C.byref(d), C.byref(s), 21, N, mdl.nx, mdl.nu, mdl.ny, mdl.nt) == 5
+
+
+@pytest.mark.parametrize("kernel,below", [(0, 0), (0, 100000), (1, 0)], ids=["stream", "latency", "generic"])
+def test_time_limit_is_enforced(kernel, below):
+    """time_limit (src/osqp.c:389-405, :570-576): a solve that runs out of time stops with
+    OSQP_TIME_LIMIT_REACHED (-6) — 'solved inaccurate' if the 10x tolerances hold — and returns its iterates;
+    the kernels test the clock at the termination checks, so the iteration count is a multiple of
+    check_termination, well below what the solve needs."""
+    mdl, q, l, u = _c1(32, 20)
+    full, n, m = _gpu(mdl, 20, 20, q, l, u, kernel, eps_abs=1e-9, eps_rel=1e-9, max_iter=4000)
+    gb = R.Batch(mdl, 20, 20, q, l, u, gpu_settings(eps_abs=1e-9, eps_rel=1e-9, max_iter=4000, time_limit=1e-7))
+    assert gb.select_kernel(kernel) == 0
+    gb.set_tuning(lat_below=below)
+    assert gb.solve() == 0
+    out = gb.get()
+    assert (out["status"] == -6).all(), out["status"]
+    assert (out["iter"] == 25).all() and (full["iter"] > 25).all()
+    assert np.isfinite(out["x"][:, :n]).all() and np.abs(out["x"][:, :n]).max() > 0
+    # without the limit the same handle solves normally again
+    assert gb.update_settings(gpu_settings(eps_abs=1e-9, eps_rel=1e-9, max_iter=4000, time_limit=0.0)) == 0
+    assert gb.solve() == 0
+    again = gb.get()
+    gb.free()
+    assert (again["iter"] == full["iter"]).all() and (again["status"] == full["status"]).all()
+
+
+def test_hand_off_never_skips_unclaimed_instances():
+    """with fewer resident lane groups than the hand-off threshold the streaming kernel used to stop
+    claiming fresh instances once the unfinished count fell below it, leaving never-started instances with a
+    stale status for the latency-mode kernel to skip.  One CTA per SM (1 184 groups at the C1 shape), threshold
+    1 024, a warm-started batch larger than the resident groups whose instances all finish at their first check."""
+    mdl, q, l, u = _c1(6000, 20)
+    ref = R.Batch(mdl, 20, 20, q, l, u, gpu_settings(warm_start=1))
+    assert ref.select_kernel(1) == 0
+    assert ref.solve() == 0 and ref.solve() == 0     # second solve: warm-started at the optimum
+    want = ref.get()
+    ref.free()
+    gb = R.Batch(mdl, 20, 20, q, l, u, gpu_settings(warm_start=1))
+    gb.set_tuning(ctas_per_sm=1, lat_below=1024)
+    assert gb.solve() == 0
+    first = gb.get()
+    assert gb.refactor() == 0                         # bench.py's step: refactor + solve without a status reset
+    assert gb.solve() == 0
+    out = gb.get()
+    n, m, _, _ = gb.dims()
+    gb.free()
+    assert (out["status"] == 1).all()
+    assert (out["iter"] == want["iter"]).all(), np.flatnonzero(out["iter"] != want["iter"])[:10]
+    assert (first["iter"] > out["iter"]).any()
+    assert np.abs(out["x"][:, :n] - want["x"][:, :n]).max() < 1e-6
+
+
+def test_batch_setup_validates_bounds():
+    """validate_data (src/auxil.c:794-887): l > u is refused at setup — on the device for a batch."""
+    mdl, q, l, u = _c1(64, 20)
+    l = l.copy()
+    l[37, 11] = u[37, 11] + 1.0
+    with pytest.raises(RuntimeError, match="code 1"):
+        R.Batch(mdl, 20, 20, q, l, u, gpu_settings())

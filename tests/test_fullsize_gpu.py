@@ -153,3 +153,46 @@ def test_full_size_warm_restart_is_idempotent():
                                                       ("get",)], warm_start=1)[2]
     bad = compare({k: v[idx] for k, v in warm.items()}, ref, n, m)
     assert not bad, bad[:5]
+
+
+def test_c5_every_instance_against_the_reference_fixture(capsys):
+    """BASELINE config C5 as bench.py runs it, ALL 65 536 instances against the unmodified reference
+    (tests/golden/c5_full.npz, written by tests/golden/make_c5_full.py: status, iteration count, objective of
+    every instance; x, y of every 64th).  Mismatch counts are printed, not hidden; the bar is zero status and
+    iteration-count mismatches and x, y, obj within 1e-6 relative.  The solve is then repeated on the same
+    handle (refactor + solve, the bench step): which instances the latency-mode kernel finishes is timing
+    dependent, so the second run must reproduce status and iteration count of every instance and the iterates
+    to rounding."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c5_full.npz"))
+    cfg = mpc.CONFIGS["C5"]
+    mdl, N, batch = mpc.make_model(cfg), cfg["N"], int(g["batch"])
+    q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch, int(g["seed"])), N)
+    gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+    assert gb.solve() == 0
+    out = gb.get()
+    n, m, _, _ = gb.dims()
+    assert (n, m) == (int(g["n"]), int(g["m"]))
+    st_bad = int((out["status"] != g["status"]).sum())
+    it_bad = int(((out["status"] == g["status"]) & (out["iter"] != g["iter"])).sum())
+    same = (out["status"] == g["status"]) & (out["iter"] == g["iter"])
+    rel_obj = np.abs(out["obj"] - g["obj"]) / np.maximum(np.abs(g["obj"]), 1e-12)
+    keep = int(g["keep"])
+    sub = np.arange(0, batch, keep)
+    ex = np.abs(out["x"][sub, :n] - g["x"]).max(axis=1) / np.maximum(np.abs(g["x"]).max(axis=1), 1e-12)
+    ey = np.abs(out["y"][sub, :m] - g["y"]).max(axis=1) / np.maximum(np.abs(g["y"]).max(axis=1), 1e-12)
+    with capsys.disabled():
+        print(f"\nC5 vs reference, {batch} instances: status mismatches {st_bad}, iteration mismatches {it_bad}, "
+              f"max rel obj {rel_obj[same].max():.2e}; {len(sub)} instances with x, y: max rel x {ex[same[sub]].max():.2e}, "
+              f"max rel y {ey[same[sub]].max():.2e}")
+    assert st_bad == 0 and it_bad == 0
+    assert rel_obj[same].max() < REL_TOL and ex[same[sub]].max() < REL_TOL and ey[same[sub]].max() < REL_TOL
+    # the bench step again on the same handle
+    assert gb.refactor() == 0 and gb.solve() == 0
+    again = gb.get()
+    gb.free()
+    flips = int(((again["status"] != out["status"]) | (again["iter"] != out["iter"])).sum())
+    dx = np.abs(again["x"][:, :n] - out["x"][:, :n]).max()
+    with capsys.disabled():
+        print(f"C5 solved twice: {flips} instances with a different status / iteration count, max |dx| {dx:.2e}")
+    assert flips == 0 and dx < 1e-9

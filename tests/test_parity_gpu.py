@@ -58,10 +58,11 @@ def test_scheduler_does_not_change_results(monkeypatch):
     oversubscribe the groups and force preemptions, results are bitwise those of first-come order."""
     mdl, N, x0, q, l, u = problem("C1", 40000)
     outs = []
-    monkeypatch.setenv("RLDL_LAT_BELOW", "0")  # streaming kernel only: which instances the latency-mode
-    for s0 in ("0", "25"):                      # kernel finishes is timing dependent (rounding-level differences)
-        monkeypatch.setenv("RLDL_SCHED_S0", s0)
+    for s0 in (0, 25):
         gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+        # streaming kernel only: which instances the latency-mode kernel finishes is timing dependent
+        # (rounding-level differences)
+        gb.set_tuning(lat_below=0, sched_s0=s0)
         assert gb.solve() == 0
         outs.append(gb.get())
         gb.free()
@@ -70,14 +71,13 @@ def test_scheduler_does_not_change_results(monkeypatch):
     assert outs[0]["iter"].max() > outs[0]["iter"].min()  # the batch really is imbalanced
 
 
-@pytest.mark.parametrize("below", ["0", "16", "100000"])
+@pytest.mark.parametrize("below", [0, 16, 100000])
 @pytest.mark.parametrize("name,batch", [("C4", 48), ("C1", 64)])
 def test_adaptive_rho_streaming_matches_generic_kernel(name, batch, below, monkeypatch):
     """Adaptive rho: the streaming / latency-mode kernels park an instance, the host re-factorises the parked
     ones in one batched launch and resumes them; the generic kernel re-factorises in place.  Same iteration,
     whether the streaming kernel runs alone (0), hands its tail to the latency-mode kernel (16) or the
     latency-mode kernel runs alone (100000)."""
-    monkeypatch.setenv("RLDL_LAT_BELOW", below)
     mdl, N, x0, q, l, u = problem(name, batch)
     rng = np.random.default_rng(5)
     rho = rng.choice([1e-3, 0.1, 10.0], size=batch)
@@ -86,6 +86,7 @@ def test_adaptive_rho_streaming_matches_generic_kernel(name, batch, below, monke
         gb = R.Batch(mdl, N, N, q, l, u, gpu_settings(adaptive_rho=1, adaptive_rho_interval=25,
                                                       adaptive_rho_tolerance=1.5), rho=rho)
         assert gb.select_kernel(which) == 0
+        gb.set_tuning(lat_below=below)
         assert gb.solve() == 0
         outs.append(gb.get())
         n, m, _, _ = gb.dims()
@@ -127,9 +128,9 @@ def test_latency_mode_kernel_matches_streaming_kernel(name, batch, mode, monkeyp
     streaming kernel alone: same status / iterations, x, y, obj within 1e-6."""
     mdl, N, x0, q, l, u = problem(name, batch)
     outs = []
-    for below in ("0", "100000" if mode == "latency_only" else str(batch // 3)):
-        monkeypatch.setenv("RLDL_LAT_BELOW", below)
+    for below in (0, 100000 if mode == "latency_only" else batch // 3):
         gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+        gb.set_tuning(lat_below=below)
         assert gb.solve() == 0
         outs.append(gb.get())
         n, m, _, _ = gb.dims()
@@ -153,9 +154,9 @@ def test_other_specialised_shapes_match_reference(nx, nu, monkeypatch):
     ref, (n, m) = res[1], res[2]
     rhs = rng.standard_normal((batch, n + m))
     kk = ref_run(mdl, N, N + 1, q, l, u, [("kkt_solve", k, rhs[k]) for k in range(3)])
-    for below in ("0", "100000"):
-        monkeypatch.setenv("RLDL_LAT_BELOW", below)
+    for below in (0, 100000):
         gb = R.Batch(mdl, N, N + 1, q, l, u, gpu_settings())
+        gb.set_tuning(lat_below=below)
         assert gb.select_kernel(2) == 0          # the shape-specialised kernels serve this shape
         got = gb.kkt_solve(rhs)
         for k in range(3):

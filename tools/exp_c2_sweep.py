@@ -8,8 +8,8 @@ cfg = mpc.CONFIGS["C1"]; mdl = mpc.make_model(cfg); N = cfg["N"]
 for batch in (1024, 4096, 16384):
     q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch, 1234), N)
     for lat in ("0", "148", "296", "1024", "4096"):
-        os.environ["RLDL_LAT_BELOW"] = lat
         gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+        gb.set_tuning(lat_below=int(lat))
         ts = []
         for _ in range(6):
             gb.refactor(); gb.solve(); ts.append(gb.last_times())

@@ -15,7 +15,7 @@ st = R.default_settings(**bench.SETTINGS)
 for batch in [int(a) for a in sys.argv[1].split(",")]:
     gb = R.Batch(mdl, N, N, q[:batch], l[:batch], u[:batch], st)
     for below in sys.argv[2].split(","):
-        os.environ["RLDL_LAT_BELOW"] = below
+        gb.set_tuning(lat_below=int(below))
         ts = []
         for _ in range(3):
             gb.solve(); ts.append(gb.last_times()[1])
