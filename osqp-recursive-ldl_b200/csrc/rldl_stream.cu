@@ -38,8 +38,8 @@ namespace rldl {
 
 // ---------------------------------------------------------------------------
 // Vector part of the stage records, stages k0..N of every instance, straight from the flat per-instance
-// vectors (one warp per instance, the rows of a stage across the lanes: coalesced reads of q, l, u and
-// coalesced writes of the record parts):
+// vectors (one CTA per instance, one warp per stage, the rows of a stage across the lanes: coalesced reads of
+// q, l, u and coalesced writes of the record parts):
 //   parts bit 0: q_k
 //   parts bit 1: constraint typing of every row from (l, u) (reference src/auxil.c:79-145: loose / equality /
 //                inequality), written as the 2-bit class words of the record and as rho_vec (the per-row values
@@ -65,23 +65,28 @@ __device__ __forceinline__ unsigned long long spread_bits(unsigned v) {  // bit 
 template <class SH>
 __global__ void __launch_bounds__(256) k_vec_records(BatchDev B, int k0, int parts, const int *only_flagged,
                                                      int *changed) {
+  // one CTA per instance, one warp per stage (stages k0 + w, k0 + w + 8, ...): at every step the CTA reads
+  // 8 consecutive stages of q / l / u (2 KB runs) — a warp walking its own row alone leaves HBM at a tenth of
+  // its bandwidth (one 224-byte access per DRAM page and 9 000 concurrent streams)
   constexpr int A = SH::A, NX = SH::NX, NT = SH::NT, BQ = SH::B, RS = SH::RS;
-  const int lane = threadIdx.x & 31;
-  const int inst = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-  if (inst >= B.batch) return;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int inst = blockIdx.x;
   if (only_flagged && !only_flagged[inst]) return;
   const bool parked = B.status[inst] == kStatusParkedRho;
   if ((parts & 4) && !parked) {  // adaptive-rho refresh: only the parked instances
-    if (changed && lane == 0) changed[inst] = 0;
+    if (changed && threadIdx.x == 0) changed[inst] = 0;
     return;
   }
+  __shared__ int s_ch;
+  if (threadIdx.x == 0) s_ch = parked ? 1 : 0;  // a parked instance has a new rho: its recursion is re-run anyway
+  __syncthreads();
   const int N = B.N;
   const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
   const double rho = fmin(fmax(B.rho[inst], kRhoMin), kRhoMax);
   double *rec = B.rec + (size_t)inst * B.rec_stride;
-  int ch = parked ? 1 : 0;  // a parked instance has a new rho: its recursion is re-run whatever its row types
+  int ch = 0;
 #pragma unroll 2
-  for (int k = k0; k <= N; k++) {
+  for (int k = k0 + wid; k <= N; k += nw) {
     const bool term = (k == N);
     double *rk = rec + (size_t)k * RS;
     if (parts & 1) {
@@ -116,18 +121,23 @@ __global__ void __launch_bounds__(256) k_vec_records(BatchDev B, int k0, int par
         if (lane == 0) rk[SH::CLS + w] = 0.0;
     }
   }
-  if ((parts & 2) && lane == 0) {
-    B.rho[inst] = rho;
-    if (changed) changed[inst] = ch;
-    if (B.status[inst] == kStatusParkedRho) B.status[inst] = -10;  // parked for this refresh: resumable again
+  if (parts & 2) {
+    if (ch) atomicOr(&s_ch, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      B.rho[inst] = rho;
+      if (changed) changed[inst] = s_ch;
+      if (parked) B.status[inst] = -10;  // parked for this refresh: resumable again
+    }
   }
 }
 
 template <class SH>
 static cudaError_t launch_vec_records_t(const BatchDev &B, int k0, int parts, const int *only_flagged, int *changed,
                                         cudaStream_t st) {
-  const int threads = 256, wpb = threads / 32;
-  k_vec_records<SH><<<(B.batch + wpb - 1) / wpb, threads, 0, st>>>(B, k0, parts, only_flagged, changed);
+  const int stages = B.N + 1 - k0;
+  const int threads = stages >= 8 ? 256 : (stages >= 4 ? 128 : (stages >= 2 ? 64 : 32));
+  k_vec_records<SH><<<B.batch, threads, 0, st>>>(B, k0, parts, only_flagged, changed);
   return cudaGetLastError();
 }
 
@@ -182,7 +192,7 @@ __device__ __forceinline__ int sched_best(const BatchDev &B, int gl, unsigned gm
 // ---------------------------------------------------------------------------
 template <class SH>
 __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, SettingsDev S, int warm_start, int D,
-                                                        int resume, int s0, int park_below) {
+                                                        int resume, int s0, int park_below, int l2_hints) {
   constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, NT = SH::NT, CW = SH::CW, G = SH::G, NYT = SH::NYT,
                 ROWS = SH::ROWS, RS = SH::RS, BQ = SH::B;
   extern __shared__ __align__(16) double smem[];
@@ -267,6 +277,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   // step size of a row and its reciprocal from the row's class (0 inequality, 1 equality, 2 loose)
   auto rho_of = [&](int c) -> double { return c == 0 ? rho_in : (c == 1 ? rho_eq : kRhoMin); };
   auto rinv_of = [&](int c) -> double { return c == 0 ? inv_in : (c == 1 ? inv_eq : inv_min); };
+  const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
   // leader only: issue the packet at position ipos into ring slot `s`, advance ipos
   auto issue = [&](int s) {
     const bool fwd = ipos <= N;
@@ -275,7 +286,8 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     const uint32_t bytes = fwd ? SH::FWD_BYTES : SH::BWD_BYTES;
     const uint32_t bar = bars_s + 8u * s;
     mbar_expect_tx(bar, bytes);
-    bulk_g2s(ring_s + 8u * (s * RS + (fwd ? 0 : SH::XOFF)), src, bytes, bar);
+    if (l2_hints & 1) bulk_g2s_hint(ring_s + 8u * (s * RS + (fwd ? 0 : SH::XOFF)), src, bytes, bar, pol_first);
+    else bulk_g2s(ring_s + 8u * (s * RS + (fwd ? 0 : SH::XOFF)), src, bytes, bar);
     ipos = (ipos + 1 == npos) ? 0 : ipos + 1;
   };
   // Mutable per-stage values are register-prefetched one stage step ahead by the lane that owns
@@ -295,8 +307,13 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     r.zd = r.yd = r.yk = r.sk = 0.0;
     if (!term && gl < NX) { r.zd = __ldcg(z + roff + NY + gl); r.yd = __ldcg(y + roff + NY + gl); }
     if (bwd && !term) {
-      if (gl < A) r.yk = __ldcg(ykg + k * A + gl);
-      if (gl < NX) r.sk = __ldcg(skg + k * NX + gl);
+      if (l2_hints & 2) {  // last use of the round trip: the line may go
+        if (gl < A) r.yk = ldcg_hint(ykg + k * A + gl, pol_first);
+        if (gl < NX) r.sk = ldcg_hint(skg + k * NX + gl, pol_first);
+      } else {
+        if (gl < A) r.yk = __ldcg(ykg + k * A + gl);
+        if (gl < NX) r.sk = __ldcg(skg + k * NX + gl);
+      }
     }
   };
   // claim an instance: fresh ones first, then the most urgent suspended one, provided its
@@ -438,7 +455,10 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         if (gl < A) {
           yvv = xinv_mv<SH>(sl_, gl, tv2, wr);
           yvs[gl] = yvv;
-          if (gl < dim) ykg[k * A + gl] = yvv;
+          if (gl < dim) {
+            if (l2_hints & 2) st_hint(ykg + k * A + gl, yvv, pol_last);
+            else ykg[k * A + gl] = yvv;
+          }
         }
         yv_reg = yvv;
         __syncwarp(gm);
@@ -452,7 +472,8 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           if (gl < NX) {
             const double sv = dmv<NX, SH::WNS>(sl_ + SH::SOFF, sl_ + SH::SOFF + gl, td2 + gl, wrapS);
             sp[gl] = sv;
-            skg[k * NX + gl] = sv;
+            if (l2_hints & 2) st_hint(skg + k * NX + gl, sv, pol_last);
+            else skg[k * NX + gl] = sv;
           }
           __syncwarp(gm);
         }
@@ -676,7 +697,7 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   // (instances suspended for the latency-mode kernel may be left in the rings of an earlier launch)
   e = cudaMemsetAsync(B.sched_slots, 0xff, (size_t)kSchedBuckets * B.batch * sizeof(int), st);
   if (e != cudaSuccess) return e;
-  kern<<<(unsigned)grid, threads, shm, st>>>(M, B, S, warm_start, D, resume, s0, park_below);
+  kern<<<(unsigned)grid, threads, shm, st>>>(M, B, S, warm_start, D, resume, s0, park_below, tune.l2_hints);
   return cudaGetLastError();
 }
 
