@@ -424,6 +424,14 @@ c_int rldl_batch_get_info(RLDLBatch *b, c_int *iter, c_int *status_val, c_float 
  * stage of the first such pivot.  The scalar setups return OSQP_NONCVX_ERROR themselves; a batch keeps its
  * healthy instances and reports the others as OSQP_NON_CVX at the next solve.  -1 on a device error. */
 c_int rldl_batch_failed_factorisations(RLDLBatch *b, c_int *flag);
+/* polish outcome of the last solve per instance (settings.polish = 1; reference src/polish.c:212-350,
+ * info->status_polish): 1 polished point accepted (x, y, obj_val, pri_res, dua_res are the polished ones),
+ * -1 polish rejected or failed, 0 not attempted (the instance did not end OSQP_SOLVED, or polish is off) */
+c_int rldl_batch_get_polish(RLDLBatch *b, c_int *status_polish);
+/* Ruiz equilibration of every instance (settings.scaling > 0; reference scale_data, src/scaling.c:44-156, and
+ * the OSQPScaling members of include/types.h:44-52): D [batch x nmax], E [batch x mmax], c [batch].
+ * Returns 1 when scaling is off.  x, y, obj, residuals and every other output are always unscaled. */
+c_int rldl_batch_get_scaling(RLDLBatch *b, c_float *D, c_float *E, c_float *c);
 /* settings of the whole batch (validated like the reference's osqp_update_* setters) */
 c_int rldl_batch_update_settings(RLDLBatch *b, const OSQPSettings *settings);
 void  rldl_batch_dims(const RLDLBatch *b, c_int *n, c_int *m, c_int *N, c_int *batch);

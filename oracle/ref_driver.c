@@ -262,6 +262,47 @@ int refb_kkt_solve(RefBatch *h, c_int k, c_float *rhs) {
   return (int)w->linsys_solver->solve(w->linsys_solver, rhs);
 }
 
+/* Equilibration of every instance as the reference computed it (work->scaling, src/scaling.c:44-156):
+ * D batch x nmax, E batch x mmax, c batch.  Returns 1 when scaling is off. */
+int refb_get_scaling(RefBatch *h, c_float *D, c_float *E, c_float *c) {
+  for (c_int k = 0; k < h->batch; k++) {
+    OSQPWorkspace *w = h->work[k];
+    if (!w->scaling) return 1;
+    memset(D + k * h->nmax, 0, sizeof(c_float) * h->nmax);
+    memset(E + k * h->mmax, 0, sizeof(c_float) * h->mmax);
+    memcpy(D + k * h->nmax, w->scaling->D, sizeof(c_float) * w->data->n);
+    memcpy(E + k * h->mmax, w->scaling->E, sizeof(c_float) * w->data->m);
+    c[k] = w->scaling->c;
+  }
+  return 0;
+}
+
+/* polish outcome per instance (info->status_polish, src/polish.c) */
+void refb_get_polish(RefBatch *h, c_int *status_polish) {
+  for (c_int k = 0; k < h->batch; k++) status_polish[k] = h->work[k]->info->status_polish;
+}
+
+/* osqp_update_P_A with complete value arrays (the same for every instance; stock path: the values of the
+ * assembled global P (upper triangle) and A in CSC order; recursive workspaces hold the same global CSC). */
+static int job_pa(void *c, c_int k) {
+  Job *j = (Job *)c; RefBatch *h = j->h;
+  OSQPWorkspace *w = h->work[k];
+  return osqp_update_P_A(w, j->a, OSQP_NULL, w->data->P->p[w->data->P->n], j->b, OSQP_NULL,
+                         w->data->A->p[w->data->A->n]) != 0;
+}
+int refb_update_PA(RefBatch *h, const c_float *Px, const c_float *Ax, int nthreads) {
+  if (h->path == 0) return -1; /* the recursive workspace has no KKT to update (F1) */
+  Job j = {h, Px, Ax, 0, 0};
+  return parfor(job_pa, &j, h->batch, nthreads);
+}
+/* nnz of the global P / A of instance 0 and their values (to build update arrays in the same order) */
+void refb_get_PA(RefBatch *h, c_int *nnzP, c_int *nnzA, c_float *Px, c_float *Ax) {
+  OSQPWorkspace *w = h->work[0];
+  *nnzP = w->data->P->p[w->data->P->n]; *nnzA = w->data->A->p[w->data->A->n];
+  if (Px) memcpy(Px, w->data->P->x, sizeof(c_float) * *nnzP);
+  if (Ax) memcpy(Ax, w->data->A->x, sizeof(c_float) * *nnzA);
+}
+
 void refb_dims(RefBatch *h, c_int *n, c_int *m) {
   *n = h->work[0]->data->n; *m = h->work[0]->data->m;
 }

@@ -58,6 +58,10 @@ def lib():
             ("refb_update_rho", [C.c_void_p, C.c_void_p, C.c_int]),
             ("refb_kkt_solve", [C.c_void_p, c_int, C.c_void_p]),
             ("refb_dims", [C.c_void_p, C.c_void_p, C.c_void_p]),
+            ("refb_get_scaling", [C.c_void_p] * 4),
+            ("refb_get_polish", [C.c_void_p, C.c_void_p]),
+            ("refb_update_PA", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
+            ("refb_get_PA", [C.c_void_p] * 5),
             ("refb_free", [C.c_void_p]),
             ("refb_default_settings", [C.POINTER(OSQPSettings)]),
         ]:
@@ -145,6 +149,30 @@ class RefBatch:
 
     def update_rho(self, rho):
         return lib().refb_update_rho(self.h, _p(np.ascontiguousarray(rho, np.float64)), self.nthreads)
+
+    def get_scaling(self):
+        """(D [batch, nmax], E [batch, mmax], c [batch]) of the reference's equilibration, None if scaling is off."""
+        D = np.zeros((self.batch, self.nmax)); E = np.zeros((self.batch, self.mmax)); c = np.zeros(self.batch)
+        if lib().refb_get_scaling(self.h, _p(D), _p(E), _p(c)):
+            return None
+        return D, E, c
+
+    def get_polish(self):
+        sp = np.zeros(self.batch, np.int64)
+        lib().refb_get_polish(self.h, _p(sp))
+        return sp
+
+    def get_PA(self):
+        """Values of the reference's global P (upper triangle) and A of instance 0, CSC order (scaled if scaling is on)."""
+        a, b = c_int(), c_int()
+        lib().refb_get_PA(self.h, C.byref(a), C.byref(b), None, None)
+        Px, Ax = np.zeros(a.value), np.zeros(b.value)
+        lib().refb_get_PA(self.h, C.byref(a), C.byref(b), _p(Px), _p(Ax))
+        return Px, Ax
+
+    def update_PA(self, Px, Ax):
+        return lib().refb_update_PA(self.h, _p(np.ascontiguousarray(Px, np.float64)),
+                                    _p(np.ascontiguousarray(Ax, np.float64)), self.nthreads)
 
     def kkt_solve(self, k, rhs):
         rhs = np.ascontiguousarray(rhs, np.float64).copy()

@@ -24,6 +24,12 @@ What is restated (file:line into /root/reference):
                           residuals/tolerances src/auxil.c:243-362, infeasibility certificates
                           :364-515, check_termination :684-789, compute_rho_estimate/adapt_rho
                           :13-77, osqp_update_rho src/osqp.c:1268-1319
+  ruiz_scale ............ scale_data, src/scaling.c:44-156; with settings.scaling > 0 the Solver holds the
+                          SCALED data and iterates, as the reference does, unscales residuals / tolerances /
+                          certificates per src/auxil.c:251-515 and the solution per scaling.c:177-192
+                          (pinned against the reference's stock path with scaling = 10: tests/test_oracle_cpu.py)
+  Solver.polish ......... polish, src/polish.c:212-350 (reduced KKT of the active constraints, iterative
+                          refinement :120-168, acceptance test :300-330)
 """
 from __future__ import annotations
 
@@ -179,7 +185,7 @@ class Settings:
         self.eps_prim_inf, self.eps_dual_inf = 1e-4, 1e-4
         self.check_termination, self.warm_start = 25, 1
         self.adaptive_rho, self.adaptive_rho_interval, self.adaptive_rho_tolerance = 1, 0, 5.0
-        self.scaling, self.polish = 10, 0
+        self.scaling, self.polish, self.delta, self.polish_refine_iter = 10, 0, 1e-6, 3
         for k, v in kw.items():
             setattr(self, k, v)
 
@@ -189,11 +195,18 @@ class Solver:
     (StageKKT for the recursive path, DenseKKT for the generic path)."""
 
     def __init__(self, P, A, q, l, u, kkt, settings: Settings):
-        assert settings.scaling == 0 and settings.polish == 0, "out of scope (SURVEY §8b preconditions)"
         self.P, self.A = np.asarray(P, float), np.asarray(A, float)   # P full symmetric
         self.q, self.l, self.u = np.array(q, float), np.array(l, float), np.array(u, float)
         self.s, self.kkt = settings, kkt
         self.n, self.m = self.P.shape[0], self.A.shape[0]
+        self.P0, self.A0 = self.P, self.A                               # the unscaled problem (polish works on it)
+        self.D, self.E, self.c = np.ones(self.n), np.ones(self.m), 1.0
+        if settings.scaling:
+            # scale_data (src/scaling.c:44): from here on P, A, q, l, u, x, z, y are the SCALED quantities, as
+            # in the reference's workspace; the reference's stock path factors the scaled KKT (src/osqp.c:167-216)
+            self.D, self.E, self.c, self.P, self.A, self.q = ruiz_scale(self.P, self.A, self.q, settings.scaling)
+            self.l, self.u = self.E * self.l, self.E * self.u
+            self.kkt = DenseKKT(self.P, self.A, settings.sigma)
         self.rho = min(max(settings.rho, RHO_MIN), RHO_MAX)
         self.rho_vec = set_rho_vec(self.l, self.u, self.rho)
         self.kkt.factor(self.rho_vec)
@@ -204,21 +217,21 @@ class Solver:
     def warm_start(self, x=None, y=None):
         self.s.warm_start = 1
         if x is not None:
-            self.x = np.array(x[: self.n], float)
+            self.x = np.array(x[: self.n], float) / self.D              # osqp.c:942-943
             self.z = self.A @ self.x
         if y is not None:
-            self.y = np.array(y[: self.m], float)
+            self.y = np.array(y[: self.m], float) / self.E * self.c     # osqp.c:944-945
 
     # osqp_update_bounds (src/osqp.c:784) -> update_rho_vec (src/auxil.c:103-145)
     def update_bounds(self, l, u):
-        self.l, self.u = np.array(l[: self.m], float), np.array(u[: self.m], float)
+        self.l, self.u = self.E * np.array(l[: self.m], float), self.E * np.array(u[: self.m], float)  # osqp.c:815-817
         new = set_rho_vec(self.l, self.u, self.rho)
         if np.any(new != self.rho_vec):
             self.rho_vec = new
             self.kkt.factor(self.rho_vec)
 
     def update_lin_cost(self, q):
-        self.q = np.array(q[: self.n], float)
+        self.q = self.c * self.D * np.array(q[: self.n], float)         # osqp.c:769-771
 
     # osqp_update_rho (src/osqp.c:1268-1319)
     def update_rho(self, rho_new):
@@ -226,12 +239,53 @@ class Solver:
         self.rho_vec = set_rho_vec(self.l, self.u, self.rho)
         self.kkt.factor(self.rho_vec)
 
-    def _residuals(self):
-        Ax, Px, Aty = self.A @ self.x, self.P @ self.x, self.A.T @ self.y
-        R = dict(pri=_inf(Ax - self.z), nz=_inf(self.z), nAx=_inf(Ax), dua=_inf(self.q + Px + Aty),
-                 nq=_inf(self.q), nAty=_inf(Aty), nPx=_inf(Px))
-        R["obj"] = 0.5 * float(self.x @ Px) + float(self.q @ self.x)
+    def _residuals(self, x=None, z=None, y=None):
+        # compute_pri_res / compute_dua_res and their tolerances' normalisers, unscaled as auxil.c:251-345 does
+        # (scaled_termination = 0); "s": the norms of the scaled vectors, which compute_rho_estimate reads
+        x, z, y = (self.x if x is None else x), (self.z if z is None else z), (self.y if y is None else y)
+        Ax, Px, Aty = self.A @ x, self.P @ x, self.A.T @ y
+        Ei, Di, ci = 1.0 / self.E, 1.0 / self.D, 1.0 / self.c
+        R = dict(pri=_inf(Ei * (Ax - z)), nz=_inf(Ei * z), nAx=_inf(Ei * Ax),
+                 dua=ci * _inf(Di * (self.q + Px + Aty)), nq=ci * _inf(Di * self.q), nAty=ci * _inf(Di * Aty),
+                 nPx=ci * _inf(Di * Px))
+        R["s"] = dict(pri=_inf(Ax - z), nz=_inf(z), nAx=_inf(Ax), dua=_inf(self.q + Px + Aty),
+                      nq=_inf(self.q), nAty=_inf(Aty), nPx=_inf(Px))
+        R["obj"] = ci * (0.5 * float(x @ Px) + float(self.q @ x))
         return R
+
+    def _polish(self, info):
+        """polish, src/polish.c:212-350, on the (scaled) workspace data.  Updates info and the iterates in place
+        when the polished point is accepted; returns status_polish (1 accepted, -1 rejected)."""
+        s, n = self.s, self.n
+        low = (self.z - self.l) < -self.y                                   # form_Ared :35-49
+        upp = ~low & ((self.u - self.z) < self.y)
+        il, iu = np.flatnonzero(low), np.flatnonzero(upp)
+        Ared = np.vstack([self.A[il], self.A[iu]]) if len(il) + len(iu) else np.zeros((0, n))
+        mr = Ared.shape[0]
+        K = np.block([[self.P, Ared.T], [Ared, np.zeros((mr, mr))]])
+        Kreg = K + np.diag(np.concatenate([np.full(n, s.delta), np.full(mr, -s.delta)]))   # kkt.c form_KKT, polish
+        b = np.concatenate([-self.q, self.l[il], self.u[iu]])                # form_rhs_red :103-118
+        lu = sla.lu_factor(Kreg)
+        zz = sla.lu_solve(lu, b)
+        for _ in range(int(s.polish_refine_iter)):                          # iterative_refinement :120-168
+            zz = zz + sla.lu_solve(lu, b - K @ zz)
+        x = zz[:n]
+        zp = self.A @ x
+        yp = np.zeros(self.m)                                               # get_ypol_from_yred :176-201
+        yp[il], yp[iu] = zz[n:n + len(il)], zz[n + len(il):]
+        t = zp + yp                                                         # project_normalcone, proj.c:16-29
+        zp = np.minimum(np.maximum(t, self.l), self.u)
+        yp = t - zp
+        R = self._residuals(x, zp, yp)
+        if self.m == 0:
+            R["pri"] = 0.0
+        ok = (R["pri"] < info["pri_res"] and R["dua"] < info["dua_res"]) or \
+             (R["pri"] < info["pri_res"] and info["dua_res"] < 1e-10) or \
+             (R["dua"] < info["dua_res"] and info["pri_res"] < 1e-10)       # :300-316
+        if ok:
+            info.update(obj=R["obj"], pri_res=R["pri"], dua_res=R["dua"])
+            self.x, self.z, self.y = x, zp, yp
+        return 1 if ok else -1
 
     def _prim_inf(self, dy, eps):        # src/auxil.c:364-427
         d = dy.copy()
@@ -241,23 +295,23 @@ class Solver:
         d[only_up] = np.minimum(d[only_up], 0.0)
         only_lo = lo_inf & ~up_inf
         d[only_lo] = np.maximum(d[only_lo], 0.0)
-        nrm = _inf(d)
+        nrm = _inf(self.E * d)
         if not nrm > eps:
             return False
         lhs = float(self.u @ np.maximum(d, 0.0) + self.l @ np.minimum(d, 0.0))
         if not lhs < -eps * nrm:
             return False
-        return _inf(self.A.T @ d) < eps * nrm
+        return _inf((self.A.T @ d) / self.D) < eps * nrm
 
     def _dual_inf(self, dx, eps):        # src/auxil.c:429-515
-        nrm = _inf(dx)
+        nrm = _inf(self.D * dx)
         if not nrm > eps:
             return False
-        if not float(self.q @ dx) < -eps * nrm:
+        if not float(self.q @ dx) < -self.c * eps * nrm:
             return False
-        if not _inf(self.P @ dx) < eps * nrm:
+        if not _inf((self.P @ dx) / self.D) < self.c * eps * nrm:
             return False
-        Adx = self.A @ dx
+        Adx = (self.A @ dx) / self.E
         thr = eps * nrm
         bad = ((self.u < OSQP_INFTY * MIN_SCALING) & (Adx > thr)) | ((self.l > -OSQP_INFTY * MIN_SCALING) & (Adx < -thr))
         return not bool(np.any(bad))
@@ -281,7 +335,8 @@ class Solver:
         return None
 
     @staticmethod
-    def _rho_estimate(R, rho):           # src/auxil.c:13-55
+    def _rho_estimate(R, rho):           # src/auxil.c:13-55 (on the scaled vectors)
+        R = R.get("s", R)
         pr = R["pri"] / (max(R["nz"], R["nAx"]) + 1e-10)
         dr = R["dua"] / (max(R["nq"], R["nAty"], R["nPx"]) + 1e-10)
         return min(max(rho * np.sqrt(pr / (dr + 1e-10)), RHO_MIN), RHO_MAX)
@@ -338,12 +393,43 @@ class Solver:
         if status == NON_CVX:
             obj = OSQP_NAN
         out = dict(status=status, iter=it, obj=obj, pri_res=R["pri"], dua_res=R["dua"],
-                   rho_updates=self.rho_updates, rho_estimate=self._rho_estimate(R, self.rho),
-                   x=np.full(n, OSQP_NAN) if no_sol else self.x.copy(),
-                   y=np.full(m, OSQP_NAN) if no_sol else self.y.copy())
+                   rho_updates=self.rho_updates, rho_estimate=self._rho_estimate(R, self.rho), status_polish=0)
+        if s.polish and status == SOLVED:                                   # osqp.c:589-591
+            out["status_polish"] = self._polish(out)
+        out.update(x=np.full(n, OSQP_NAN) if no_sol else self.D * self.x,                 # unscale_solution,
+                   y=np.full(m, OSQP_NAN) if no_sol else self.E * self.y / self.c)       # scaling.c:177-192
         if no_sol:   # store_solution cold-starts the iterates (src/auxil.c:539-563)
             self.x[:], self.z[:], self.y[:] = 0.0, 0.0, 0.0
         return out
+
+
+def _limit_scaling(v):
+    """src/scaling.c:7-14: norms below MIN_SCALING count as 1, above MAX_SCALING as MAX_SCALING."""
+    v = np.where(v < MIN_SCALING, 1.0, v)
+    return np.minimum(v, 1e4)
+
+
+def ruiz_scale(P, A, q, iters):
+    """scale_data, src/scaling.c:44-156.  P full symmetric.  Returns D, E, c and the scaled P, A, q."""
+    P, A, q = np.array(P, float), np.array(A, float), np.array(q, float)
+    n, m = P.shape[0], A.shape[0]
+    D, E, c = np.ones(n), np.ones(m), 1.0
+    for _ in range(int(iters)):
+        dn = np.abs(P).max(axis=0) if n else np.zeros(0)
+        if m:
+            dn = np.maximum(dn, np.abs(A).max(axis=0))
+            en = np.abs(A).max(axis=1)
+        else:
+            en = np.zeros(0)
+        dt, et = 1.0 / np.sqrt(_limit_scaling(dn)), 1.0 / np.sqrt(_limit_scaling(en))
+        P = dt[:, None] * P * dt[None, :]
+        A = et[:, None] * A * dt[None, :]
+        q = dt * q
+        D, E = D * dt, E * et
+        ct = max(float(np.abs(P).max(axis=0).mean()), float(_limit_scaling(np.array(_inf(q)))))
+        ct = 1.0 / float(_limit_scaling(np.array(ct)))
+        P, q, c = P * ct, q * ct, c * ct
+    return D, E, c, P, A, q
 
 
 def mpc_solver(model, N, q, l, u, settings: Settings, path="recursive"):
@@ -387,7 +473,8 @@ class OracleBatch:
         B, n, m = self.batch, *self.dims()
         out = dict(x=np.zeros((B, self.nmax)), y=np.zeros((B, self.mmax)))
         for key, dt in (("iter", np.int64), ("status", np.int64), ("obj", float), ("pri_res", float),
-                        ("dua_res", float), ("rho_updates", np.int64), ("rho_estimate", float)):
+                        ("dua_res", float), ("rho_updates", np.int64), ("rho_estimate", float),
+                        ("status_polish", np.int64)):
             out[key] = np.array([r[key] for r in self.last], dt)
         for k, r in enumerate(self.last):
             out["x"][k, :n], out["y"][k, :m] = r["x"], r["y"]

@@ -167,13 +167,15 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
   d_mval = nval; d_midx = nidx;
   Md.val = d_mval; Md.idx = d_midx; Md.nval = (int)mb.val.size();
   M = Mnew;
+  scale_stale = true;
   if (D.rec) return configure_stream();  // a P / A update may change which specialisation serves the model
   return 0;
 }
 
 // Which kernels serve the model, and the stage-record layout that goes with them.
 c_int Batch::configure_stream() {
-  streaming = !generic && stream_supported(M, N);
+  // Ruiz-scaled problems carry a step size per row and a sigma per variable: they run on the runtime-shape kernels
+  streaming = !generic && !scaled() && stream_supported(M, N);
   stream_record_dims(M, &D.qa, &D.PX, &D.PS, &D.bb, &D.bd, &D.PXX);
   D.RS = D.qa + D.PX + D.PS + kClsWords + 2 * D.bb;
   D.rec_stride = (long long)(Nmax + 1) * D.RS;
@@ -230,11 +232,11 @@ c_int validate_settings(const OSQPSettings *s) {
 
 // Preconditions of this path: rejected loudly, never silently diverging.
 static c_int validate_scope(const OSQPSettings *s) {
-  if (s->scaling != 0) {
-    fprintf(stderr, "ERROR in rldl: scaling must be 0 (the reference's recursive path factors the unscaled stage blocks)\n");
+  if (s->scaling != 0 && s->scaled_termination != 0) {
+    fprintf(stderr, "ERROR in rldl: scaled_termination = 1 together with scaling is not supported on this path\n");
     return 1;
   }
-  if (s->polish != 0) { fprintf(stderr, "ERROR in rldl: polish is not supported on this path\n"); return 1; }
+  if (s->polish != 0 && s->polish != 1) { fprintf(stderr, "ERROR in validate_settings: polish must be either 0 or 1\n"); return 1; }
   if (s->linsys_solver != QDLDL_SOLVER) { fprintf(stderr, "ERROR in rldl: linsys_solver must be QDLDL_SOLVER\n"); return 1; }
   return 0;
 }
@@ -307,6 +309,7 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(dalloc(&D.obj, bs)); CK(dalloc(&D.pri, bs)); CK(dalloc(&D.dua, bs)); CK(dalloc(&D.rho_est, bs));
   CK(dalloc(&D.rho_updates, bs)); CK(dalloc(&D.fact_flag, bs));
   CK(dalloc(&B->d_changed, bs));
+  if (B->scaled()) { CK(dalloc(&D.sD, bs * D.nmax)); CK(dalloc(&D.sE, bs * D.mmax)); CK(dalloc(&D.sC, bs)); }
   CK(dalloc(&D.sched, kSchedCounters));
   rc = B->configure_stream();
   if (rc) return rc;
@@ -341,7 +344,9 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
     }
     CK(cudaMemsetAsync(D.sched + 1, 0, sizeof(int), B->stream));
   }
-  // set_rho_vec (auxil.c:79) + full stage recursion (recursive_ldl.c:1139)
+  // scale_data (scaling.c:44) + set_rho_vec (auxil.c:79) + full stage recursion (recursive_ldl.c:1139)
+  rc = B->rescale();
+  if (rc) return rc;
   rc = B->retype(0, 3, false, false, true);
   if (rc) return rc;
   rc = B->factor(0, false);
@@ -358,11 +363,12 @@ void Batch::set_sizes() {
 
 Batch::~Batch() {
   cudaSetDevice(device);
-  double *dp[] = {D.q, D.l, D.u, D.rho_vec, D.x, D.z, D.y, D.dx, D.dy, D.Xinv, D.Sinv, D.yk, D.sk,
-                  D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec, d_l_alt, d_u_alt, d_latT};
+  double *dp[] = {D.sD, D.sE, D.sC, D.q, D.l, D.u, D.rho_vec, D.x, D.z, D.y, D.dx, D.dy, D.Xinv, D.Sinv, D.yk, D.sk,
+                  D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec, d_l_alt, d_u_alt, d_latT,
+                  d_polX, d_polS, d_polrho, d_polb, d_pols, d_polr};
   for (double *p : dp) if (p) cudaFree(p);
   if (D.iter) cudaFree(D.iter);
-  int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx, D.sched, D.sched_slots};
+  int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx, D.sched, D.sched_slots, d_polstat};
   for (int *p : ip) if (p) cudaFree(p);
   if (h_pin) cudaFreeHost(h_pin);
   if (ev0) cudaEventDestroy(ev0);
@@ -515,6 +521,44 @@ c_int Batch::solve() {
   float ms = 0;
   cudaEventElapsedTime(&ms, ev0, ev1);
   last_solve_ms = ms;
+  last_polish_ms = 0;
+  if (settings.polish) return polish();  // osqp.c:589-591: only the instances that ended OSQP_SOLVED
+  return 0;
+}
+
+// polish (src/polish.c:212-350) for every solved instance: a second stage factor with sigma = delta and
+// rho = 1/delta on the guessed active rows, iterative refinement, acceptance test — all on the device (k_polish).
+c_int Batch::polish() {
+  const size_t bs = (size_t)batch, ld = (size_t)D.nmax + D.mmax;
+  if (!d_polX) {
+    CK(dalloc(&d_polX, bs * D.xstride)); CK(dalloc(&d_polS, bs * D.sstride)); CK(dalloc(&d_polrho, bs * D.mmax));
+    CK(dalloc(&d_polb, bs * ld)); CK(dalloc(&d_pols, bs * ld)); CK(dalloc(&d_polr, bs * ld));
+    CK(dalloc(&d_polstat, bs));
+  }
+  BatchDev P = D;
+  P.Xinv = d_polX; P.Sinv = d_polS; P.rho_vec = d_polrho;
+  CK(cudaEventRecord(ev0, stream));
+  CK(launch_polish(M, D, P, S, settings.delta, (int)settings.polish_refine_iter, d_polb, d_pols, d_polr, d_polstat,
+                   stream));
+  launches++;
+  CK(cudaEventRecord(ev1, stream));
+  CK(cudaStreamSynchronize(stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, ev0, ev1);
+  last_polish_ms = ms;
+  return 0;
+}
+
+c_int Batch::get_polish(c_int *status_polish) {
+  CK(cudaSetDevice(device));
+  if (!d_polstat) {  // no polish has run on this handle
+    for (int i = 0; i < batch; i++) status_polish[i] = 0;
+    return 0;
+  }
+  std::vector<int> sp(batch);
+  CK(cudaMemcpyAsync(sp.data(), d_polstat, batch * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  for (int i = 0; i < batch; i++) status_polish[i] = sp[i];
   return 0;
 }
 
@@ -539,6 +583,27 @@ c_int Batch::retype(int k0, int parts, bool only_parked, bool want_flags, bool a
     CK(launch_set_rho_vec(D, all_rows ? D.mmax : D.m, (want_flags && !streaming) ? d_changed : nullptr, stream));
     launches++;
   }
+  return 0;
+}
+
+// scale_data (src/scaling.c:44-156) for every instance, from the resident model, the current horizon and the
+// current q; a no-op when settings.scaling == 0.
+c_int Batch::rescale() {
+  scale_stale = false;
+  if (!scaled()) return 0;
+  CK(launch_ruiz(M, D, (int)settings.scaling, stream));
+  launches++;
+  return 0;
+}
+
+c_int Batch::fetch_scaling(int inst, c_float *Dv, c_float *Ev, c_float *c) {
+  if (!scaled()) return 1;
+  CK(cudaSetDevice(device));
+  const size_t cnt = inst < 0 ? (size_t)batch : 1, first = inst < 0 ? 0 : (size_t)inst;  // inst < 0: the whole batch
+  CK(cudaMemcpyAsync(Dv, D.sD + first * D.nmax, cnt * D.nmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  CK(cudaMemcpyAsync(Ev, D.sE + first * D.mmax, cnt * D.mmax * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  CK(cudaMemcpyAsync(c, D.sC + first, cnt * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
   return 0;
 }
 
@@ -645,6 +710,15 @@ c_int Batch::update_horizon(c_int Nnew) {
   const int k0 = std::min((int)Nnew, N);  // first stage whose pivots change
   N = (int)Nnew;
   set_sizes();
+  if (scaled()) {
+    // the equilibration of the new horizon differs everywhere (what a fresh setup at the new horizon computes —
+    // the reference's recursive path has no defined behaviour here): full recursion
+    c_int rc = rescale();
+    if (rc) return rc;
+    rc = retype(0, 3, false, false);
+    if (rc) return rc;
+    return factor(0, false);
+  }
   c_int rc = retype(k0, 3, false, false);  // the terminal stage moved: its q, rows and bounds change
   if (rc) return rc;
   return factor(k0, false);
@@ -662,7 +736,10 @@ c_int Batch::update_rho(const c_float *rho) {
 
 c_int Batch::refactor() {
   CK(cudaSetDevice(device));
-  c_int rc = retype(0, 3, false, false);
+  c_int rc = 0;
+  if (scale_stale) rc = rescale();  // P / A changed: the reference unscales, updates and scales again (osqp.c:1033-1051)
+  if (rc) return rc;
+  rc = retype(0, 3, false, false);
   if (rc) return rc;
   return factor(0, false);
 }
@@ -741,9 +818,11 @@ c_int Batch::update_settings(const OSQPSettings *s) {
   if (validate_settings(s)) return 1;
   if (validate_scope(s)) return 1;
   const double old_rho = settings.rho, old_sigma = settings.sigma;
+  const c_int old_scaling = settings.scaling;
   settings = *s;
   settings.rho = old_rho;  // rho changes go through update_rho
   settings.sigma = old_sigma;
+  settings.scaling = old_scaling;  // fixed at setup, as in the reference (no osqp_update_scaling)
   push_settings();
   return 0;
 }

@@ -31,6 +31,12 @@ struct Batch {
   double *d_stage = nullptr;
   double *d_latT = nullptr;  // per-CTA T_k blocks of the latency-mode kernel
   double *d_l_alt = nullptr, *d_u_alt = nullptr;  // landing buffers of validated bound updates
+  // polish (settings.polish): second factor, its step sizes, three work vectors per instance, outcome
+  double *d_polX = nullptr, *d_polS = nullptr, *d_polrho = nullptr, *d_polb = nullptr, *d_pols = nullptr, *d_polr = nullptr;
+  int *d_polstat = nullptr;
+  double last_polish_ms = 0;
+  c_int polish();
+  c_int get_polish(c_int *status_polish);
   size_t stage_cap = 0;
   double *h_pin = nullptr;
   cudaStream_t stream = nullptr;
@@ -46,6 +52,10 @@ struct Batch {
                       const c_float *l, const c_float *u, const c_float *rho, bool generic);
   ~Batch();
 
+  bool scaled() const { return settings.scaling > 0; }
+  bool scale_stale = false;  // the model changed since the last equilibration
+  c_int rescale();
+  c_int fetch_scaling(int inst, c_float *Dv, c_float *Ev, c_float *c);
   c_int configure_stream();
   size_t rec_cap = 0;       // doubles allocated for D.rec
   bool slots_full = false;  // D.sched_slots sized for the scheduler

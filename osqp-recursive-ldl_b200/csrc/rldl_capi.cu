@@ -57,6 +57,7 @@ struct PrivSolver {
 };
 
 PrivSolver *priv(OSQPWorkspace *w) { return reinterpret_cast<PrivSolver *>(w->linsys_solver); }
+void mirror_scaling(OSQPWorkspace *w);
 
 void set_status(OSQPInfo *info, c_int v) {
   // update_status, src/auxil.c:654-682
@@ -215,6 +216,7 @@ void finish_setup(OSQPWorkspace *w, PrivSolver *p, double t0) {
     w->settings->adaptive_rho_interval = w->settings->check_termination ? 4 * w->settings->check_termination : 100;
   p->batch->settings.adaptive_rho_interval = w->settings->adaptive_rho_interval;
   p->batch->push_settings();
+  mirror_scaling(w);
 }
 
 void tic_update(OSQPWorkspace *w) {
@@ -280,15 +282,34 @@ c_int horizon_update(OSQPWorkspace *work, OSQPDataRLDL *r, c_int N) {
   work->data->n = N * (r->nx + r->nu);
   work->data->m = N * (r->nx + r->ny) + r->nt;
   r->N = N;
+  mirror_scaling(work);
   return 0;
 }
 
 void sync_settings(OSQPWorkspace *w) {
   Batch *B = priv(w)->batch;
   const double rho = B->settings.rho, sigma = B->settings.sigma;
+  const c_int scaling = B->settings.scaling;
   B->settings = *w->settings;
-  B->settings.rho = rho; B->settings.sigma = sigma;
+  B->settings.rho = rho; B->settings.sigma = sigma; B->settings.scaling = scaling;
   B->push_settings();
+}
+
+// Host mirror of the equilibration (work->scaling, reference include/types.h:44-52): D, E, c of the instance as
+// the device computed them.  The data mirrors (work->data) stay unscaled — the kernels never form scaled data.
+void mirror_scaling(OSQPWorkspace *w) {
+  Batch *B = priv(w)->batch;
+  if (!B->scaled()) return;
+  if (!w->scaling) {
+    w->scaling = zalloc<OSQPScaling>(1);
+    w->scaling->D = zalloc<c_float>(B->nmax); w->scaling->Dinv = zalloc<c_float>(B->nmax);
+    w->scaling->E = zalloc<c_float>(B->mmax); w->scaling->Einv = zalloc<c_float>(B->mmax);
+  }
+  OSQPScaling *sc = w->scaling;
+  if (B->fetch_scaling(0, sc->D, sc->E, &sc->c)) return;
+  sc->cinv = 1.0 / sc->c;
+  for (int i = 0; i < B->nmax; i++) sc->Dinv[i] = 1.0 / sc->D[i];
+  for (int i = 0; i < B->mmax; i++) sc->Einv[i] = 1.0 / sc->E[i];
 }
 
 }  // namespace
@@ -420,7 +441,14 @@ c_int osqp_solve(OSQPWorkspace *work) {
                      status == OSQP_DUAL_INFEASIBLE || status == OSQP_DUAL_INFEASIBLE_INACCURATE || status == OSQP_NON_CVX;
   for (c_int i = 0; i < n; i++) work->solution->x[i] = nosol ? OSQP_NAN : work->x[i];
   for (c_int i = 0; i < m; i++) work->solution->y[i] = nosol ? OSQP_NAN : work->y[i];
-  info->solve_time = now_s() - t0;
+  info->status_polish = 0; info->polish_time = 0.0;
+  if (work->settings->polish) {  // polish (src/polish.c) ran inside the solve for a solved instance
+    c_int sp = 0;
+    if (B->get_polish(&sp)) return 1;
+    info->status_polish = sp;
+    info->polish_time = 1e-3 * B->last_polish_ms;
+  }
+  info->solve_time = now_s() - t0 - info->polish_time;
   info->run_time = (work->first_run ? info->setup_time : info->update_time) + info->solve_time + info->polish_time;
   if (work->first_run) work->first_run = 0;
   work->clear_update_time = 1;
@@ -443,6 +471,7 @@ c_int osqp_cleanup(OSQPWorkspace *w) {
   free(w->Ax); free(w->Px); free(w->Aty); free(w->delta_y); free(w->Atdelta_y);
   free(w->delta_x); free(w->Pdelta_x); free(w->Adelta_x);
   if (w->solution) { free(w->solution->x); free(w->solution->y); free(w->solution); }
+  if (w->scaling) { free(w->scaling->D); free(w->scaling->Dinv); free(w->scaling->E); free(w->scaling->Einv); free(w->scaling); }
   free(w->info); free(w->timer); free(w->settings);
   free(w);
   return 0;
@@ -674,6 +703,7 @@ static c_int update_PA_common(OSQPWorkspace *work, const c_float *Px, const c_in
     stage_blocks_from_global(work, true);
   }
   c_int rc = rebuild_model(work);
+  if (!rc) mirror_scaling(work);
   reset_info(work->info);
   toc_update(work);
   return rc;
@@ -719,9 +749,9 @@ SETTER(time_limit, c_float, time_limit, v < 0., "time_limit must be nonnegative"
 c_int osqp_update_polish(OSQPWorkspace *work, c_int polish_new) {
   if (!work) return osqp_error(OSQP_WORKSPACE_NOT_INIT_ERROR);
   if (polish_new != 0 && polish_new != 1) { fprintf(stderr, "ERROR in osqp_update_polish: polish should be either 0 or 1\n"); return 1; }
-  if (polish_new == 1) { fprintf(stderr, "ERROR in osqp_update_polish: polish is not supported on this path\n"); return 1; }
-  work->settings->polish = 0;
+  work->settings->polish = polish_new;
   work->info->polish_time = 0.0;
+  sync_settings(work);
   return 0;
 }
 
@@ -782,6 +812,16 @@ c_int rldl_batch_get_info(RLDLBatch *h, c_int *iter, c_int *status_val, c_float 
                           c_float *dua_res, c_int *rho_updates, c_float *rho_estimate) {
   HB(h);
   return h->b->get_info(iter, status_val, obj_val, pri_res, dua_res, rho_updates, rho_estimate);
+}
+c_int rldl_batch_get_polish(RLDLBatch *h, c_int *status_polish) {
+  HB(h);
+  if (!status_polish) return 1;
+  return h->b->get_polish(status_polish);
+}
+c_int rldl_batch_get_scaling(RLDLBatch *h, c_float *D, c_float *E, c_float *c) {
+  HB(h);
+  if (!D || !E || !c) return 1;
+  return h->b->fetch_scaling(-1, D, E, c);
 }
 c_int rldl_batch_update_settings(RLDLBatch *h, const OSQPSettings *s) { HB(h); return h->b->update_settings(s); }
 void rldl_batch_dims(const RLDLBatch *h, c_int *n, c_int *m, c_int *N, c_int *batch) {

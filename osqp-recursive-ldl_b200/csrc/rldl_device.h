@@ -70,6 +70,11 @@ struct BatchDev {
   double *obj, *pri, *dua, *rho_est;
   int *rho_updates;
   int *fact_flag;          // 0 ok, >0 = 1 + stage of the first non-positive pivot
+  // Ruiz equilibration of the reference (src/scaling.c:44-156), per instance: sD[nmax] variable scaling D,
+  // sE[mmax] constraint scaling E, sC cost scaling c; all null when settings.scaling == 0.  The kernels never
+  // form scaled data: the scaled ADMM iteration is the unscaled one with per-variable sigma_i = sigma / (c D_i^2)
+  // and per-row rho_j = rho_class(E_j l_j, E_j u_j) E_j^2 / c, which is what rho_vec then holds.
+  double *sD, *sE, *sC;
   // Streaming layout (rldl_stream.cu): one record per (instance, stage), RS doubles:
   //   [ q_k (qa) | Xinv_k packed (PX) | Sinv_k packed (PS) | row classes (kClsWords) | l_k (bb) | u_k (bb) ]
   // packed = lower triangle, column-major, of the a x a / nx x nx symmetric pivot inverse;

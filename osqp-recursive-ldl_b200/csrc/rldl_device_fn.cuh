@@ -19,7 +19,7 @@
 namespace rldl {
 
 static constexpr double kInfty = 1e30;
-static constexpr double kMinScaling = 1e-4;
+static constexpr double kMinScaling = 1e-4, kMaxScaling = 1e4;
 static constexpr double kInfBound = kInfty * kMinScaling;  // 1e26, auxil.c:85
 static constexpr double kRhoMin = 1e-6, kRhoMax = 1e6, kRhoEq = 1e3, kRhoTol = 1e-4;
 static constexpr double kOsqpNan = (double)0x7fc00000UL;  // constants.h:95 (sic)
@@ -81,6 +81,21 @@ __device__ __forceinline__ double row_rho(double l, double u, double rho) {
   return rho;
 }
 
+// The same with the Ruiz scaling of the instance (B.sE != null): the reference types the SCALED bounds
+// (src/osqp.c:815-817 then auxil.c:103-145) and iterates on scaled data; in unscaled variables that is the step size
+// rho_class * E_r^2 / c on row r.  ri = flat index of the row (inst * mmax + r).
+__device__ __forceinline__ double row_rho_eff(const BatchDev &B, int inst, size_t ri, double rho) {
+  if (!B.sE) return row_rho(B.l[ri], B.u[ri], rho);
+  const double e = B.sE[ri];
+  return row_rho(e * B.l[ri], e * B.u[ri], rho) * e * e / B.sC[inst];
+}
+// per-variable sigma of the unscaled form of the scaled iteration: sigma / (c D_i^2); vi = inst * nmax + i
+__device__ __forceinline__ double var_sigma(const BatchDev &B, int inst, size_t vi, double sigma) {
+  if (!B.sD) return sigma;
+  const double d = B.sD[vi];
+  return sigma / (B.sC[inst] * d * d);
+}
+
 // ---------------------------------------------------------------------------
 // In-place inversion of a dim x dim SPD matrix held in shared memory
 // (Gauss-Jordan without pivoting, lane i owns column i => conflict-free).
@@ -135,10 +150,13 @@ __device__ int factor_instance(const ModelDev &M, const BatchDev &B, double sigm
     const int np = term ? nt : ny;
     const int roff = k * b;
     for (int r = lane; r < np; r += G) rp[r] = rv[roff + r];
-    // G = Q + sigma I
+    // G = Q + sigma I  (sigma per variable under Ruiz scaling; the phantom variables of stage 0 keep sigma)
+    const int xoff_f = (N == 0) ? 0 : k * a - nx, ilo_f = (k == 0 && !term) ? nx : 0;
     for (int e = lane; e < dim * dim; e += G) {
       const int i = e / dim, j = e - i * dim;
-      Gm[e] = __ldg(M.val + sc.Q + e) + (i == j ? sigma : 0.0);
+      double v = __ldg(M.val + sc.Q + e);
+      if (i == j) v += (i >= ilo_f) ? var_sigma(B, inst, (size_t)inst * B.nmax + xoff_f + i, sigma) : sigma;
+      Gm[e] = v;
     }
     __syncwarp(gm);
     // G += C' diag(rho_p) C   (lane i owns memory column i; symmetric update)
@@ -234,7 +252,7 @@ __device__ void kkt_sweep(const ModelDev &M, const BatchDev &B, const SettingsDe
     const int xoff = (N == 0) ? 0 : k * a - nx, roff = k * b, ilo = (k == 0 && !term) ? nx : 0;
     for (int i = lane; i < dim; i += G) {
       double gv = 0.0;
-      if (i >= ilo) gv = KKT ? rb[xoff + i] : sigma * x[xoff + i] - q[xoff + i];
+      if (i >= ilo) gv = KKT ? rb[xoff + i] : var_sigma(B, inst, vo + xoff + i, sigma) * x[xoff + i] - q[xoff + i];
       sm.g[i] = gv;
     }
     for (int r = lane; r < np; r += G) {
@@ -384,13 +402,20 @@ struct Resid {
   double pri, dua, nz, nAx, nq, nAty, nPx, obj;
 };
 
-// update_info (auxil.c:567-632): residuals, their normalisers and the objective.
+// update_info (auxil.c:567-632): residuals, their normalisers and the objective — always of the UNSCALED problem
+// (scaled_termination = 0: auxil.c:251, 263, 314, 327 unscale them).  Under Ruiz scaling `scaled`, when given,
+// receives the same seven norms of the scaled problem (||E (Ax - z)||, ||c D (Px + q + A'y)||, ...): the rho
+// estimate reads those (compute_rho_estimate works on the scaled vectors, auxil.c:13-55).
 template <int G>
 __device__ Resid compute_residuals(const ModelDev &M, const BatchDev &B, int inst, int lane, unsigned gm,
-                                   const Scratch &sm) {
+                                   const Scratch &sm, Resid *scaled = nullptr) {
   const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
   const double *q = B.q + vo, *x = B.x + vo, *z = B.z + ro, *y = B.y + ro;
   double pri = 0, nz = 0, nAx = 0, dua = 0, nq = 0, nAty = 0, nPx = 0, oq = 0, oP = 0;
+  const bool ws = scaled != nullptr && B.sD != nullptr;
+  const double *sD = ws ? B.sD + vo : nullptr, *sE = ws ? B.sE + ro : nullptr;
+  const double sc = ws ? B.sC[inst] : 1.0;
+  double s_pri = 0, s_nz = 0, s_nAx = 0, s_dua = 0, s_nq = 0, s_nAty = 0, s_nPx = 0;
   product_sweep<G>(
       M, B, lane, gm, sm, x, y,
       [&](int ri, double ax) {
@@ -398,6 +423,10 @@ __device__ Resid compute_residuals(const ModelDev &M, const BatchDev &B, int ins
         pri = fmax(pri, fabs(ax - zz));
         nz = fmax(nz, fabs(zz));
         nAx = fmax(nAx, fabs(ax));
+        if (ws) {
+          const double e = sE[ri];
+          s_pri = fmax(s_pri, e * fabs(ax - zz)); s_nz = fmax(s_nz, e * fabs(zz)); s_nAx = fmax(s_nAx, e * fabs(ax));
+        }
       },
       [&](int xi, double xval, double px, double aty) {
         const double qv = q[xi];
@@ -407,11 +436,24 @@ __device__ Resid compute_residuals(const ModelDev &M, const BatchDev &B, int ins
         nPx = fmax(nPx, fabs(px));
         oq = fma(qv, xval, oq);
         oP = fma(xval, px, oP);
+        if (ws) {
+          const double w = sc * sD[xi];
+          s_dua = fmax(s_dua, w * fabs((qv + px) + aty)); s_nq = fmax(s_nq, w * fabs(qv));
+          s_nAty = fmax(s_nAty, w * fabs(aty)); s_nPx = fmax(s_nPx, w * fabs(px));
+        }
       });
   Resid r;
   r.pri = grp_max<G>(pri, gm); r.nz = grp_max<G>(nz, gm); r.nAx = grp_max<G>(nAx, gm);
   r.dua = grp_max<G>(dua, gm); r.nq = grp_max<G>(nq, gm); r.nAty = grp_max<G>(nAty, gm); r.nPx = grp_max<G>(nPx, gm);
   r.obj = 0.5 * grp_sum<G>(oP, gm) + grp_sum<G>(oq, gm);
+  if (scaled) {
+    *scaled = r;
+    if (ws) {
+      scaled->pri = grp_max<G>(s_pri, gm); scaled->nz = grp_max<G>(s_nz, gm); scaled->nAx = grp_max<G>(s_nAx, gm);
+      scaled->dua = grp_max<G>(s_dua, gm); scaled->nq = grp_max<G>(s_nq, gm); scaled->nAty = grp_max<G>(s_nAty, gm);
+      scaled->nPx = grp_max<G>(s_nPx, gm);
+    }
+  }
   return r;
 }
 
@@ -422,12 +464,17 @@ __device__ int primal_infeasible(const ModelDev &M, const BatchDev &B, int inst,
   const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
   const double *l = B.l + ro, *u = B.u + ro;
   double *dy = B.dy + ro;
+  // Under Ruiz scaling the reference tests the finiteness of the SCALED bounds and ||E dy_scaled|| = c ||dy||
+  // against eps; the other two conditions are invariant (the factors cancel).
+  const double *sE = B.sE ? B.sE + ro : nullptr;
+  const double cs = B.sE ? B.sC[inst] : 1.0;
   double nrm = 0.0;
   for (int r = lane; r < m; r += G) {
     double d = dy[r];
-    if (u[r] > kInfBound) {
-      d = (l[r] < -kInfBound) ? 0.0 : fmin(d, 0.0);
-    } else if (l[r] < -kInfBound) {
+    const double e = sE ? sE[r] : 1.0;
+    if (e * u[r] > kInfBound) {
+      d = (e * l[r] < -kInfBound) ? 0.0 : fmin(d, 0.0);
+    } else if (e * l[r] < -kInfBound) {
       d = fmax(d, 0.0);
     }
     dy[r] = d;
@@ -435,7 +482,7 @@ __device__ int primal_infeasible(const ModelDev &M, const BatchDev &B, int inst,
   }
   nrm = grp_max<G>(nrm, gm);
   __syncwarp(gm);
-  if (!(nrm > eps)) return 0;
+  if (!(cs * nrm > eps)) return 0;
   double lhs = 0.0;
   for (int r = lane; r < m; r += G) {
     const double d = dy[r];
@@ -469,10 +516,12 @@ __device__ int dual_infeasible(const ModelDev &M, const BatchDev &B, int inst, i
   double nPdx = 0.0;
   int viol = 0;
   const double thr = eps * nrm;
+  const double *sE = B.sE ? B.sE + ro : nullptr;  // finiteness of the scaled bounds (auxil.c:496-499)
   product_sweep<G>(
       M, B, lane, gm, sm, dx, B.dy + ro /*unused values*/,
       [&](int ri, double adx) {
-        if ((u[ri] < kInfBound && adx > thr) || (l[ri] > -kInfBound && adx < -thr)) viol = 1;
+        const double e = sE ? sE[ri] : 1.0;
+        if ((e * u[ri] < kInfBound && adx > thr) || (e * l[ri] > -kInfBound && adx < -thr)) viol = 1;
       },
       [&](int, double, double px, double) { nPdx = fmax(nPdx, fabs(px)); });
   nPdx = grp_max<G>(nPdx, gm);

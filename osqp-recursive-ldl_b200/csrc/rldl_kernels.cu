@@ -32,7 +32,7 @@ __global__ void k_set_rho_vec(BatchDev B, int m, int *changed) {
   double rho = fmin(fmax(B.rho[warp], kRhoMin), kRhoMax);
   int ch = 0;
   for (int r = lane; r < B.mmax; r += 32) {
-    const double nv = row_rho(B.l[off + r], B.u[off + r], rho);
+    const double nv = row_rho_eff(B, warp, off + r, rho);
     if (r < m && nv != B.rho_vec[off + r]) ch = 1;
     B.rho_vec[off + r] = nv;
   }
@@ -42,6 +42,105 @@ __global__ void k_set_rho_vec(BatchDev B, int m, int *changed) {
     if (changed) changed[warp] = ch;
     if (B.status[warp] == kStatusParkedRho) B.status[warp] = -10;  // parked for this refresh: resumable again
   }
+}
+
+// ---------------------------------------------------------------------------
+// Ruiz equilibration (reference src/scaling.c:44-156, scale_data), one warp per instance, on the stage
+// structure: `iters` rounds of  D <- D / sqrt(||KKT column||_inf), E <- E / sqrt(||KKT row||_inf)  followed by the
+// cost normalisation c <- c / max(mean_j ||P column j||_inf, ||q||_inf).  The scaled matrices are never formed:
+// entry (i,j) of the current scaled P is c D_i P_ij D_j, of the scaled A it is E_r A_rj D_j.  Norms below 1e-4
+// count as 1, above 1e4 as 1e4 (limit_scaling, scaling.c:7-14).  dx / dy serve as the D_temp / E_temp of the
+// reference (free at setup and update time).  Rows and variables beyond the current horizon keep scaling 1.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double limit_scaling(double v) {
+  v = v < kMinScaling ? 1.0 : v;
+  return v > kMaxScaling ? kMaxScaling : v;
+}
+
+__global__ void k_ruiz(ModelDev M, BatchDev B, int iters) {
+  const int inst = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (inst >= B.batch) return;
+  const int nx = M.nx, a = M.a, b = M.b, ny = M.ny, nt = M.nt, N = B.N;
+  const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
+  double *D = B.sD + vo, *E = B.sE + ro, *dD = B.dx + vo, *dE = B.dy + ro;
+  const double *q = B.q + vo;
+  for (int i = lane; i < B.nmax; i += 32) D[i] = 1.0;
+  for (int r = lane; r < B.mmax; r += 32) E[r] = 1.0;
+  double c = 1.0;
+  __syncwarp();
+  // ||column i of the stage cost block||_inf weighted by D (without the c D_i factor)
+  auto pcol = [&](const StageClass &sc, int dim, int ilo, int xoff, int i) {
+    double pn = 0.0;
+    for (int j = ilo; j < dim; j++) pn = fmax(pn, fabs(__ldg(M.val + sc.Q + j * dim + i)) * D[xoff + j]);
+    return pn;
+  };
+  for (int t = 0; t < iters; t++) {
+    for (int k = 0; k <= N; k++) {
+      const bool term = (k == N);
+      const StageClass &sc = M.sc[term ? 2 : (k == 0 ? 0 : 1)];
+      const int dim = term ? nx : a, np = term ? nt : ny;
+      const int xoff = (N == 0) ? 0 : k * a - nx, roff = k * b, ilo = (k == 0 && !term) ? nx : 0;
+      for (int i = lane; i < dim; i += 32) {
+        if (i < ilo) continue;
+        const double pn = c * pcol(sc, dim, ilo, xoff, i);
+        double an = 0.0;
+        for (int e = 0; e < sc.Ct.width; e++)
+          an = fmax(an, fabs(__ldg(M.val + sc.Ct.off + i * sc.Ct.width + e)) * E[roff + __ldg(M.idx + sc.Ct.off + i * sc.Ct.width + e)]);
+        if (!term)
+          for (int e = 0; e < sc.Ft.width; e++)
+            an = fmax(an, fabs(__ldg(M.val + sc.Ft.off + i * sc.Ft.width + e)) *
+                              E[roff + ny + __ldg(M.idx + sc.Ft.off + i * sc.Ft.width + e)]);
+        if (k > 0 && i < nx) an = fmax(an, E[roff - b + ny + i]);  // the -I of stage k-1's dynamics rows
+        dD[xoff + i] = 1.0 / sqrt(limit_scaling(D[xoff + i] * fmax(pn, an)));
+      }
+      for (int r = lane; r < np; r += 32) {
+        double rn = 0.0;
+        for (int e = 0; e < sc.C.width; e++) {
+          const int j = __ldg(M.idx + sc.C.off + r * sc.C.width + e);
+          if (j >= ilo) rn = fmax(rn, fabs(__ldg(M.val + sc.C.off + r * sc.C.width + e)) * D[xoff + j]);
+        }
+        dE[roff + r] = 1.0 / sqrt(limit_scaling(E[roff + r] * rn));
+      }
+      if (!term)
+        for (int r = lane; r < nx; r += 32) {
+          double rn = D[xoff + a + r];  // the -I on x_{k+1}
+          for (int e = 0; e < sc.F.width; e++) {
+            const int j = __ldg(M.idx + sc.F.off + r * sc.F.width + e);
+            if (j >= ilo) rn = fmax(rn, fabs(__ldg(M.val + sc.F.off + r * sc.F.width + e)) * D[xoff + j]);
+          }
+          dE[roff + ny + r] = 1.0 / sqrt(limit_scaling(E[roff + ny + r] * rn));
+        }
+    }
+    __syncwarp();
+    for (int i = lane; i < B.n; i += 32) D[i] *= dD[i];
+    for (int r = lane; r < B.m; r += 32) E[r] *= dE[r];
+    __syncwarp();
+    // cost normalisation (scaling.c:111-138) with the new D and the c of the earlier rounds
+    double sum = 0.0, qn = 0.0;
+    for (int k = 0; k <= N; k++) {
+      const bool term = (k == N);
+      const StageClass &sc = M.sc[term ? 2 : (k == 0 ? 0 : 1)];
+      const int dim = term ? nx : a;
+      const int xoff = (N == 0) ? 0 : k * a - nx, ilo = (k == 0 && !term) ? nx : 0;
+      for (int i = lane; i < dim; i += 32) {
+        if (i < ilo) continue;
+        sum += c * D[xoff + i] * pcol(sc, dim, ilo, xoff, i);
+        qn = fmax(qn, c * fabs(D[xoff + i] * q[xoff + i]));
+      }
+    }
+    sum = grp_sum<32>(sum, FULL);
+    qn = grp_max<32>(qn, FULL);
+    const double ct = limit_scaling(fmax(sum / (double)B.n, limit_scaling(qn)));
+    c *= 1.0 / ct;
+    __syncwarp();
+  }
+  if (lane == 0) B.sC[inst] = c;
+}
+
+cudaError_t launch_ruiz(const ModelDev &M, const BatchDev &B, int iters, cudaStream_t st) {
+  const int threads = 128, wpb = threads / 32;
+  k_ruiz<<<(B.batch + wpb - 1) / wpb, threads, 0, st>>>(M, B, iters);
+  return cudaGetLastError();
 }
 
 size_t factor_smem_doubles(int a, int nx, int ny, int nt) {
@@ -104,7 +203,7 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
   int status = -10, rho_updates = 0, can_check = 0, iter;
   bool timed_out = false;
   double obj = 0.0, rho_est = rho;
-  Resid R = {0, 0, 0, 0, 0, 0, 0, 0};
+  Resid R = {0, 0, 0, 0, 0, 0, 0, 0}, Rs = R;  // Rs: the norms of the scaled problem (rho estimate under Ruiz scaling)
   for (iter = 1; iter <= S.max_iter; iter++) {
     can_check = S.check_termination && (iter % S.check_termination == 0);
     const bool time_due = time_check_due(S, iter, can_check);
@@ -112,19 +211,18 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
     kkt_sweep<32, false>(M, B, S, inst, lane, FULL, sm, nullptr, store_delta);
     __syncwarp();
     if (can_check) {
-      R = compute_residuals<32>(M, B, inst, lane, FULL, sm);
+      R = compute_residuals<32>(M, B, inst, lane, FULL, sm, &Rs);
       obj = R.obj;
       if (check_termination<32>(M, B, S, inst, lane, FULL, sm, R, 0, &status, &obj)) break;
     }
     if (S.adaptive_rho && S.adaptive_rho_interval && (iter % S.adaptive_rho_interval == 0)) {
-      if (!can_check) { R = compute_residuals<32>(M, B, inst, lane, FULL, sm); obj = R.obj; }
-      const double rn = rho_estimate(R, rho);
+      if (!can_check) { R = compute_residuals<32>(M, B, inst, lane, FULL, sm, &Rs); obj = R.obj; }
+      const double rn = rho_estimate(Rs, rho);
       rho_est = rn;
       if (rn > rho * S.adaptive_rho_tolerance || rn < rho / S.adaptive_rho_tolerance) {
         // osqp_update_rho (osqp.c:1268-1319): retype-free rho_vec rewrite + full refactor
         rho = fmin(fmax(rn, kRhoMin), kRhoMax);
-        for (int r = lane; r < B.mmax; r += 32)
-          B.rho_vec[ro + r] = row_rho(B.l[ro + r], B.u[ro + r], rho);
+        for (int r = lane; r < B.mmax; r += 32) B.rho_vec[ro + r] = row_rho_eff(B, inst, ro + r, rho);
         __syncwarp();
         const int flag = factor_instance<32>(M, B, S.sigma, inst, lane, FULL, 0, G, W, Sm, rp);
         rho_updates++;
@@ -140,7 +238,7 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
   int it_done = (iter > S.max_iter) ? S.max_iter : iter;
   if (status == -10) {
     if (!can_check) {  // osqp.c:524-546
-      R = compute_residuals<32>(M, B, inst, lane, FULL, sm);
+      R = compute_residuals<32>(M, B, inst, lane, FULL, sm, &Rs);
       obj = R.obj;
       check_termination<32>(M, B, S, inst, lane, FULL, sm, R, 0, &status, &obj);
     }
@@ -150,7 +248,7 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
   }
   const bool has_sol = !(status == -3 || status == 3 || status == -4 || status == 4 || status == -7);
   if (has_sol && status != -10) obj = R.obj;
-  rho_est = rho_estimate(R, rho);
+  rho_est = rho_estimate(Rs, rho);
   if (!has_sol) {
     // store_solution (auxil.c:527-563): normalise the certificate, cold-start the iterates
     if (status == -3 || status == 3) {
@@ -178,6 +276,133 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
     B.rho_updates[inst] += rho_updates;
     B.rho[inst] = rho;
   }
+}
+
+// ---------------------------------------------------------------------------
+// Polish (reference src/polish.c:212-350), one warp per instance, for the instances that ended OSQP_SOLVED.
+// The reduced KKT system of the guessed active set
+//     [ P + delta I   Ared' ] [x]   [ -q            ]
+//     [ Ared        -delta I ] [nu] = [ l_low ; u_upp ]
+// is the stage-ordered KKT with sigma = delta, rho = 1/delta on the active rows and the inactive rows removed
+// (path rows: rho = 0, they drop out of C' rho C; dynamics rows: 1/rho = 1e200, their row and column of
+// S_k^-1 vanish), so it is factored by the same stage recursion into a second factor (P.Xinv / P.Sinv) and solved
+// by the same block substitution; polish_refine_iter rounds of iterative refinement against the unregularised
+// products (polish.c:120-168) remove the delta error.  Then z = A x, the duals of the active rows, the normal-cone
+// projection (proj.c:16-29), the residuals of the polished point and the acceptance test (polish.c:300-330).
+// Under Ruiz scaling the reference does all of this on scaled data; in unscaled variables that is
+// sigma_i = delta / (c D_i^2), rho_j = E_j^2 / (c delta), the activity tests w_j (z_j - l_j) < -y_j and
+// w_j (u_j - z_j) < y_j with w_j = E_j^2 / c, and the projection z' = clip(z + y / w, l, u), y' = w (z + y / w - z').
+// P = the batch with Xinv / Sinv / rho_vec pointing at the polish buffers; pb, ps, pr: [batch][nmax + mmax]
+// work vectors (rhs b; solution [x ; nu]; refinement vector, then the polished z).
+// ---------------------------------------------------------------------------
+__global__ void k_polish(ModelDev M, BatchDev B, BatchDev P, SettingsDev S, double delta, int refine_iter,
+                         double *pb, double *ps, double *pr, int *status_polish) {
+  extern __shared__ double smem[];
+  const int wpb = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int inst = blockIdx.x * wpb + wid;
+  if (inst >= B.batch) return;
+  if (B.status[inst] != 1) {  // polish only follows OSQP_SOLVED (osqp.c:590-591)
+    if (lane == 0) status_polish[inst] = 0;
+    return;
+  }
+  int vm = M.a;
+  if (M.ny > vm) vm = M.ny;
+  if (M.nt > vm) vm = M.nt;
+  if (M.nx > vm) vm = M.nx;
+  int fvm = M.ny > M.nt ? M.ny : M.nt;
+  if (M.nx > fvm) fvm = M.nx;
+  const size_t per = 8 * (size_t)vm + (size_t)M.a * M.a + (size_t)M.a * M.nx + (size_t)M.nx * M.nx + fvm;
+  double *base = smem + per * wid;
+  const Scratch sm = make_scratch(base, vm);
+  double *G = base + 8 * vm, *W = G + M.a * M.a, *Sm = W + M.a * M.nx, *rp = Sm + M.nx * M.nx;
+  const int n = B.n, m = B.m, ld = B.nmax + B.mmax, ny = M.ny, b = M.b, N = B.N;
+  const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
+  const double *q = B.q + vo, *l = B.l + ro, *u = B.u + ro;
+  double *x = B.x + vo, *z = B.z + ro, *y = B.y + ro;
+  double *bb = pb + (size_t)inst * ld, *sol = ps + (size_t)inst * ld, *res = pr + (size_t)inst * ld;
+  double *prho = P.rho_vec + ro;
+  const double cs = B.sE ? B.sC[inst] : 1.0;
+  auto wgt = [&](int r) -> double { return B.sE ? B.sE[ro + r] * B.sE[ro + r] / cs : 1.0; };
+  auto is_dyn = [&](int r) -> bool { const int k = r / b; return k < N && (r - k * b) >= ny; };
+  // ---- active set (form_Ared, polish.c:20-49), reduced rhs (form_rhs_red :103-118), step sizes ----
+  for (int i = lane; i < n; i += 32) bb[i] = -q[i];
+  for (int r = lane; r < m; r += 32) {
+    const double w = wgt(r);
+    double rhs = 0.0, rho = is_dyn(r) ? 1e-200 : 0.0;
+    if (w * (z[r] - l[r]) < -y[r]) { rhs = l[r]; rho = w / delta; }
+    else if (w * (u[r] - z[r]) < y[r]) { rhs = u[r]; rho = w / delta; }
+    bb[n + r] = rhs;
+    prho[r] = rho;
+  }
+  __syncwarp();
+  // ---- factor the reduced KKT by the stage recursion ----
+  if (factor_instance<32>(M, P, delta, inst, lane, FULL, 0, G, W, Sm, rp)) {
+    if (lane == 0) status_polish[inst] = -1;
+    return;
+  }
+  // v <- K_reg^-1 v = [x ; nu], nu = 0 on the inactive rows.  The block substitution returns z~ = rhs + nu / rho
+  // on the rows (qdldl_interface.c:572-579); nu = rho (z~ - rhs).
+  double *rowc = B.dy + ro;  // scratch (the deltas are not needed after OSQP_SOLVED)
+  auto solve = [&](double *v) {
+    for (int r = lane; r < m; r += 32) rowc[r] = v[n + r];
+    __syncwarp();
+    kkt_sweep<32, true>(M, P, S, inst, lane, FULL, sm, v, false);
+    __syncwarp();
+    for (int r = lane; r < m; r += 32) {
+      const double rho = prho[r];
+      v[n + r] = rho > 1e-100 ? rho * (v[n + r] - rowc[r]) : 0.0;
+    }
+    __syncwarp();
+  };
+  for (int i = lane; i < n + m; i += 32) sol[i] = bb[i];
+  __syncwarp();
+  solve(sol);
+  // ---- iterative refinement (polish.c:120-168): z += K_reg^-1 (b - K z), K = [P Ared'; Ared 0] ----
+  for (int it = 0; it < refine_iter; it++) {
+    product_sweep<32>(
+        M, B, lane, FULL, sm, sol, sol + n,
+        [&](int ri, double ax) { res[n + ri] = prho[ri] > 1e-100 ? bb[n + ri] - ax : 0.0; },
+        [&](int xi, double, double px, double aty) { res[xi] = (bb[xi] - px) - aty; });
+    __syncwarp();
+    solve(res);
+    for (int i = lane; i < n + m; i += 32) sol[i] += res[i];
+    __syncwarp();
+  }
+  // ---- polished point: x, z = A x, y (get_ypol_from_yred), normal-cone projection, residuals ----
+  double *pz = res + n;   // polished z (the refinement vector is free now)
+  double *py = sol + n;   // polished y, in place over nu
+  double pri = 0.0, dua = 0.0, oq = 0.0, oP = 0.0;
+  product_sweep<32>(
+      M, B, lane, FULL, sm, sol, py, [&](int ri, double ax) { pz[ri] = ax; }, [&](int, double, double, double) {});
+  __syncwarp();
+  for (int r = lane; r < m; r += 32) {  // project_normalcone (proj.c:16-29) on the scaled pair
+    const double w = wgt(r);
+    const double t = pz[r] + py[r] / w;
+    const double zn = fmin(fmax(t, l[r]), u[r]);
+    py[r] = w * (t - zn);
+    pz[r] = zn;
+  }
+  __syncwarp();
+  product_sweep<32>(
+      M, B, lane, FULL, sm, sol, py,
+      [&](int ri, double ax) { pri = fmax(pri, fabs(ax - pz[ri])); },
+      [&](int xi, double xval, double px, double aty) {
+        const double qv = q[xi];
+        dua = fmax(dua, fabs((qv + px) + aty));
+        oq = fma(qv, xval, oq);
+        oP = fma(xval, px, oP);
+      });
+  pri = grp_max<32>(pri, FULL); dua = grp_max<32>(dua, FULL);
+  const double obj = 0.5 * grp_sum<32>(oP, FULL) + grp_sum<32>(oq, FULL);
+  if (m == 0) pri = 0.0;
+  const double ipri = B.pri[inst], idua = B.dua[inst];
+  const bool ok = (pri < ipri && dua < idua) || (pri < ipri && idua < 1e-10) || (dua < idua && ipri < 1e-10);
+  if (ok) {
+    for (int i = lane; i < n; i += 32) x[i] = sol[i];
+    for (int r = lane; r < m; r += 32) { z[r] = pz[r]; y[r] = py[r]; }
+    if (lane == 0) { B.obj[inst] = obj; B.pri[inst] = pri; B.dua[inst] = dua; }
+  }
+  if (lane == 0) status_polish[inst] = ok ? 1 : -1;
 }
 
 __global__ void k_kkt_solve(ModelDev M, BatchDev B, SettingsDev S, double *rhs, int ld) {
@@ -312,6 +537,19 @@ cudaError_t launch_admm(const ModelDev &M, const BatchDev &B, const SettingsDev 
   cudaError_t e = cudaFuncSetAttribute(k_admm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm);
   if (e != cudaSuccess) return e;
   k_admm<<<(B.batch + wpb - 1) / wpb, wpb * 32, shm, st>>>(M, B, S, warm_start);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_polish(const ModelDev &M, const BatchDev &B, const BatchDev &P, const SettingsDev &S, double delta,
+                          int refine_iter, double *pb, double *ps, double *pr, int *status_polish, cudaStream_t st) {
+  const size_t per = admm_smem_doubles(M.a, M.nx, M.ny, M.nt) * sizeof(double);
+  if (per > 220 * 1024) return cudaErrorInvalidValue;
+  int wpb = pick_wpb(per);
+  if (wpb > 2) wpb = 2;
+  const size_t shm = per * wpb;
+  cudaError_t e = cudaFuncSetAttribute(k_polish, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm);
+  if (e != cudaSuccess) return e;
+  k_polish<<<(B.batch + wpb - 1) / wpb, wpb * 32, shm, st>>>(M, B, P, S, delta, refine_iter, pb, ps, pr, status_polish);
   return cudaGetLastError();
 }
 

@@ -6,11 +6,14 @@
 namespace rldl {
 size_t factor_smem_doubles(int a, int nx, int ny, int nt);
 size_t admm_smem_doubles(int a, int nx, int ny, int nt);
+cudaError_t launch_ruiz(const ModelDev &M, const BatchDev &B, int iters, cudaStream_t st);
 cudaError_t launch_set_rho_vec(const BatchDev &B, int m, int *changed, cudaStream_t st);
 cudaError_t launch_factor(const ModelDev &M, const BatchDev &B, double sigma, int k0,
                           const int *only_flagged, cudaStream_t st);
 cudaError_t launch_admm(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                         cudaStream_t st);
+cudaError_t launch_polish(const ModelDev &M, const BatchDev &B, const BatchDev &P, const SettingsDev &S, double delta,
+                          int refine_iter, double *pb, double *ps, double *pr, int *status_polish, cudaStream_t st);
 cudaError_t launch_kkt_solve(const ModelDev &M, const BatchDev &B, const SettingsDev &S, double *rhs,
                              int ld, cudaStream_t st);
 cudaError_t launch_warm_start_z(const ModelDev &M, const BatchDev &B, cudaStream_t st);

@@ -67,3 +67,22 @@ def compare(out, ref, n, m, tag=""):
         if max(ex, ey, eo) > REL_TOL:
             bad.append((k, "x", ex, "y", ey, "obj", eo))
     return bad
+
+
+def scaled_problem(name, batch, seed=1234, Nmax=None):
+    """A problem whose Ruiz equilibration (reference src/scaling.c) is not the identity: the BASELINE random
+    models have unit KKT column norms, so their cost / input matrices are rescaled here; every instance gets its
+    own linear cost so that the cost scaling c differs inside a batch."""
+    cfg = mpc.CONFIGS[name]
+    mdl = mpc.make_model(cfg)
+    if cfg["model"] != "quadcopter":
+        mdl.Q = 40.0 * mdl.Q
+        mdl.R = 0.02 * mdl.R
+        mdl.B = 0.2 * mdl.B
+    N = cfg["N"]
+    x0 = mpc.sample_x0(mdl, batch, seed)
+    q, l, u = mdl.vectors(x0, N, Nmax)
+    rng = np.random.default_rng(seed + 1)
+    n = N * (mdl.nx + mdl.nu)
+    q[:, :n] += rng.standard_normal((batch, 1)) ** 2 * 3.0 * rng.standard_normal((batch, n))
+    return mdl, N, x0, q, l, u

@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 for p in (ROOT, os.path.join(ROOT, "osqp-recursive-ldl_b200"), os.path.join(ROOT, "tests")):
     sys.path.insert(0, p)
 
-from common import problem, ref_run, settings_dict  # noqa: E402
+from common import problem, ref_run, scaled_problem, settings_dict  # noqa: E402
 from rldl_b200 import mpc  # noqa: E402
 
 
@@ -109,7 +109,45 @@ def updates(name, batch):
     save(f"updates_{name}", **kw)
 
 
+def scaled(name, batch):
+    """Ruiz scaling (settings.scaling = 10, the OSQP default) on the reference's STOCK path (its recursive path
+    scales the global P / A but factors the unscaled stage blocks): the equilibration itself
+    (work->scaling D, E, c), a cold solve, and a solve with adaptive rho from rho = 1e-3."""
+    mdl, N, x0, q, l, u = scaled_problem(name, batch)
+    res = ref_run(mdl, N, N, q, l, u, [("solve",), ("get",), ("get_scaling",), ("dims",)], path="stock", scaling=10)
+    r, (D, E, c), (n, m) = res[1], res[2], res[3]
+    rho = np.full(batch, 1e-3)
+    ra = ref_run(mdl, N, N, q, l, u, [("solve",), ("get",)], path="stock", rho=rho, scaling=10, adaptive_rho=1,
+                 adaptive_rho_interval=25, adaptive_rho_tolerance=1.5)[1]
+    save(f"scaled_{name}", batch=batch, seed=1234, n=n, m=m, D=D[:, :n], E=E[:, :m], c=c, status=r["status"],
+         iter=r["iter"], obj=r["obj"], x=r["x"][:, :n], y=r["y"][:, :m], rho_a=rho, status_a=ra["status"],
+         iter_a=ra["iter"], obj_a=ra["obj"], rho_updates_a=ra["rho_updates"], x_a=ra["x"][:, :n], y_a=ra["y"][:, :m])
+
+
+POLISH = {"C1": (16, problem, dict(polish=1, eps_abs=3e-2, eps_rel=3e-2)),
+          "C3": (8, problem, dict(polish=1, eps_abs=3e-2, eps_rel=3e-2)),
+          "C4": (8, scaled_problem, dict(polish=1, eps_abs=1e-2, eps_rel=1e-2, scaling=10))}
+
+
+def polished(name):
+    """polish = 1 (src/polish.c) on the reference's stock path with tolerances loose enough that the guessed active
+    set is sometimes wrong: accepted (status_polish 1), rejected (-1) and not attempted (0) all occur."""
+    batch, prob, kw = POLISH[name]
+    mdl, N, x0, q, l, u = prob(name, batch)
+    res = ref_run(mdl, N, N, q, l, u, [("solve",), ("get",), ("get_polish",), ("dims",)], path="stock", **kw)
+    r, sp, (n, m) = res[1], res[2], res[3]
+    save(f"polish_{name}", batch=batch, seed=1234, n=n, m=m, status=r["status"], iter=r["iter"], obj=r["obj"],
+         status_polish=sp, pri_res=r["pri_res"], dua_res=r["dua_res"], x=r["x"][:, :n], y=r["y"][:, :m])
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "polish":
+        for nm in POLISH:
+            polished(nm)
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "scaled":
+        scaled("C1", 6); scaled("C3", 4); scaled("C4", 4)
+        sys.exit(0)
     cold("C1", 16)
     cold("C3", 6)
     cold("C4", 6)

@@ -163,3 +163,52 @@ def test_oracle_matches_live_reference_both_paths():
         ob.solve()
         n, m = ob.dims()
         assert not compare(ob.get(), ref, n, m), path
+
+
+@pytest.mark.parametrize("name,take", [("C1", [0, 1, 5]), ("C3", [1])])
+def test_oracle_ruiz_scaling_matches_golden(name, take):
+    """settings.scaling = 10: the restated scale_data (src/scaling.c:44-156) gives the reference's D, E, c to the
+    last bit, and the scaled ADMM loop with unscaled termination (src/auxil.c:251-515) the same status,
+    iteration count, rho updates, x, y, obj — cold and with adaptive rho (golden: reference stock path)."""
+    from common import scaled_problem
+    g = gold(f"scaled_{name}")
+    mdl, N, x0, q, l, u = scaled_problem(name, int(g["batch"]))
+    n, m = int(g["n"]), int(g["m"])
+    for tag, kw, rho in (("", dict(scaling=10), None),
+                         ("_a", dict(scaling=10, adaptive_rho=1, adaptive_rho_interval=25, adaptive_rho_tolerance=1.5),
+                          g["rho_a"])):
+        ob = O.OracleBatch(mdl, N, N, q[take], l[take], u[take], settings_dict(**kw), path="stock",
+                           rho=None if rho is None else rho[take])
+        for j, k in enumerate(take):
+            assert np.array_equal(ob.sv[j].D, g["D"][k]) and np.array_equal(ob.sv[j].E, g["E"][k])
+            assert ob.sv[j].c == g["c"][k]
+        ob.solve()
+        out = ob.get()
+        ref = dict(status=g["status" + tag][take], iter=g["iter" + tag][take], obj=g["obj" + tag][take],
+                   x=np.pad(g["x" + tag][take], ((0, 0), (0, q.shape[1] - n))),
+                   y=np.pad(g["y" + tag][take], ((0, 0), (0, l.shape[1] - m))))
+        assert not compare(out, ref, n, m), tag
+        if tag:
+            assert (out["rho_updates"] == g["rho_updates_a"][take]).all()
+
+
+@pytest.mark.parametrize("name,take", [("C1", list(range(16))), ("C3", [0, 1, 5])])
+def test_oracle_polish_matches_golden(name, take):
+    """polish = 1: the restated polish (src/polish.c:212-350 — active-set guess, reduced KKT with delta
+    regularisation, iterative refinement, normal-cone projection, acceptance test) reproduces the reference's
+    status_polish (accepted and rejected cases) and its polished x, y, obj."""
+    import sys
+    sys.path.insert(0, GOLD)
+    from make_golden import POLISH
+    g = gold(f"polish_{name}")
+    batch, prob, kw = POLISH[name]
+    mdl, N, x0, q, l, u = prob(name, batch)
+    n, m = int(g["n"]), int(g["m"])
+    ob = O.OracleBatch(mdl, N, N, q[take], l[take], u[take], settings_dict(**kw), path="stock")
+    ob.solve()
+    out = ob.get()
+    assert (out["status_polish"] == g["status_polish"][take]).all()
+    assert set(g["status_polish"].tolist()) >= {1, -1}
+    ref = dict(status=g["status"][take], iter=g["iter"][take], obj=g["obj"][take],
+               x=np.pad(g["x"][take], ((0, 0), (0, q.shape[1] - n))), y=np.pad(g["y"][take], ((0, 0), (0, l.shape[1] - m))))
+    assert not compare(out, ref, n, m)
