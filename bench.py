@@ -11,8 +11,8 @@ One step = the hot path over the whole batch: full stage-wise KKT factorisation
   value  : instances solved per second, data resident in HBM (CUDA events on the
            library's launching stream, max over ranks)
   e2e    : same through the host-buffer API: rldl_batch_update_bounds(l,u) +
-           rldl_batch_update_lin_cost(q) from pinned host memory, refactor, solve,
-           rldl_batch_get_solution(x,y) + rldl_batch_get_info back to pinned host memory
+           rldl_batch_update_lin_cost(q) from pinned host memory, refactor,
+           rldl_batch_solve_to_host(x, y, info) into pinned host memory
 --impl reference times the UNMODIFIED reference (oracle/_ref: osqp_setup_recursive +
 osqp_solve_recursive) on the host cores over a bounded sample of the same instances.
 """
@@ -291,10 +291,10 @@ def main_b200(args):
         assert lib.rldl_batch_update_bounds(gb.h, P(l_h), P(u_h)) == 0
         assert lib.rldl_batch_update_lin_cost(gb.h, P(q_h)) == 0
         assert gb.refactor() == 0
-        assert gb.solve() == 0
-        assert lib.rldl_batch_get_solution(gb.h, P(x_h), P(y_h)) == 0
-        assert lib.rldl_batch_get_info(gb.h, *[P(info_h[k]) for k in
-                                               ("iter", "status", "obj", "pri", "dua", "rho_updates", "rho_est")]) == 0
+        # fused solve-and-deliver: x, y and info of every instance land in the pinned host arrays as the instance
+        # finishes (device-initiated writes over PCIe), i.e. the D2H transfer is inside the solve
+        assert lib.rldl_batch_solve_to_host(gb.h, P(x_h), P(y_h), *[P(info_h[k]) for k in
+                                            ("iter", "status", "obj", "pri", "dua", "rho_updates", "rho_est")]) == 0
 
     def timed(fn, steps):
         barrier()

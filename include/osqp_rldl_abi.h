@@ -414,6 +414,16 @@ c_int rldl_batch_refactor(RLDLBatch *b);
 /* one KKT solve per instance: rhs [batch][n+m] (current sizes) is overwritten with
  * [x_tilde ; z_tilde] — the batched form of linsys_solver->solve */
 c_int rldl_batch_kkt_solve(RLDLBatch *b, c_float *rhs);
+/* Fused solve-and-deliver: rldl_batch_solve + rldl_batch_get_solution + rldl_batch_get_info in one call (array
+ * layout as in those two; status_val is required, the others may be NULL).  When every array given is PINNED host
+ * memory (cudaHostAlloc / cudaHostRegister), the kernels write each instance's x, y (OSQP_NAN for the statuses
+ * without a solution, auxil.c:539-542) and info to the host the moment the instance finishes, so the device-to-host
+ * transfer runs behind the rest of the solve instead of after it; pageable arrays, or settings.polish = 1 (polish
+ * revises the results after the ADMM kernels), take the ordinary copies after the solve.  Only entries [0, n) of
+ * each row of x and [0, m) of y are written. */
+c_int rldl_batch_solve_to_host(RLDLBatch *b, c_float *x, c_float *y, c_int *iter, c_int *status_val,
+                               c_float *obj_val, c_float *pri_res, c_float *dua_res, c_int *rho_updates,
+                               c_float *rho_estimate);
 /* gather: x [batch][nmax], y [batch][mmax] (any pointer may be NULL) */
 c_int rldl_batch_get_solution(RLDLBatch *b, c_float *x, c_float *y);
 c_int rldl_batch_get_info(RLDLBatch *b, c_int *iter, c_int *status_val, c_float *obj_val,

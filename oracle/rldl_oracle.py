@@ -516,7 +516,9 @@ class OracleBatch:
         n, m = P.shape[0], A.shape[0]
         for k, s in enumerate(self.sv):
             xo, zo, yo = s.x, s.z, s.y
+            assert not s.s.scaling, "horizon changes are restated for the unscaled recursive path only"
             s.P, s.A, s.n, s.m = P, A, n, m
+            s.P0, s.A0, s.D, s.E = P, A, np.ones(n), np.ones(m)
             s.q, s.l, s.u = self.q[k, :n].copy(), self.l[k, :m].copy(), self.u[k, :m].copy()
             s.rho_vec = set_rho_vec(s.l, s.u, s.rho)
             if isinstance(s.kkt, StageKKT):

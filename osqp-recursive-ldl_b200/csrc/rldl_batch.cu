@@ -760,6 +760,48 @@ c_int Batch::kkt_solve(c_float *rhs) {
   return 0;
 }
 
+// Device-visible address of a host array iff it is pinned (cudaHostAlloc / cudaHostRegister); null otherwise.
+template <class T>
+static T *pinned_dev_ptr(T *host) {
+  if (!host) return nullptr;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  if (at.type != cudaMemoryTypeHost || !at.devicePointer) return nullptr;
+  return static_cast<T *>(at.devicePointer);
+}
+
+// Fused solve-and-deliver: rldl_batch_solve + rldl_batch_get_solution + rldl_batch_get_info in one call.  When every
+// output array is pinned host memory the kernels write each instance's results to the host as soon as the instance
+// finishes (BatchDev::hx ...), so the device-to-host transfer (1.16 GB at C5) runs behind the solve; pageable
+// arrays — or polish, which revises results after the ADMM kernels — take the plain copies after the solve.
+c_int Batch::solve_to_host(c_float *x, c_float *y, c_int *iter, c_int *status, c_float *obj, c_float *pri, c_float *dua,
+                           c_int *rho_updates, c_float *rho_est) {
+  CK(cudaSetDevice(device));
+  if (!status) return 1;
+  BatchDev H = D;
+  H.hx = pinned_dev_ptr(x); H.hy = pinned_dev_ptr(y);
+  H.h_iter = pinned_dev_ptr(iter); H.h_status = pinned_dev_ptr(status); H.h_rho_updates = pinned_dev_ptr(rho_updates);
+  H.h_obj = pinned_dev_ptr(obj); H.h_pri = pinned_dev_ptr(pri); H.h_dua = pinned_dev_ptr(dua);
+  H.h_rho_est = pinned_dev_ptr(rho_est);
+  const bool direct = !settings.polish && (!x || H.hx) && (!y || H.hy) && (!iter || H.h_iter) && H.h_status &&
+                      (!rho_updates || H.h_rho_updates) && (!obj || H.h_obj) && (!pri || H.h_pri) &&
+                      (!dua || H.h_dua) && (!rho_est || H.h_rho_est);
+  if (!direct) {
+    c_int rc = solve();
+    if (rc) return rc;
+    rc = get_solution(x, y);
+    if (rc) return rc;
+    return get_info(iter, status, obj, pri, dua, rho_updates, rho_est);
+  }
+  const BatchDev keep = D;
+  D = H;
+  const c_int rc = solve();  // ends with a stream synchronisation: every delivery has landed
+  D.hx = keep.hx; D.hy = keep.hy; D.h_iter = keep.h_iter; D.h_status = keep.h_status;
+  D.h_rho_updates = keep.h_rho_updates; D.h_obj = keep.h_obj; D.h_pri = keep.h_pri; D.h_dua = keep.h_dua;
+  D.h_rho_est = keep.h_rho_est;
+  return rc;
+}
+
 static bool no_solution(int st) {
   return st == OSQP_PRIMAL_INFEASIBLE || st == OSQP_PRIMAL_INFEASIBLE_INACCURATE ||
          st == OSQP_DUAL_INFEASIBLE || st == OSQP_DUAL_INFEASIBLE_INACCURATE || st == OSQP_NON_CVX;

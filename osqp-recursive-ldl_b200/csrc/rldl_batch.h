@@ -84,6 +84,8 @@ struct Batch {
   c_int update_rho(const c_float *rho);
   c_int refactor();
   c_int kkt_solve(c_float *rhs);
+  c_int solve_to_host(c_float *x, c_float *y, c_int *iter, c_int *status, c_float *obj, c_float *pri, c_float *dua,
+                      c_int *rho_updates, c_float *rho_est);
   c_int get_solution(c_float *x, c_float *y);
   c_int get_info(c_int *iter, c_int *status, c_float *obj, c_float *pri, c_float *dua,
                  c_int *rho_updates, c_float *rho_est);

@@ -774,6 +774,11 @@ c_int rldl_batch_setup(RLDLBatch **out, const OSQPDataRLDL *model, const OSQPSet
 }
 #define HB(h) if (!(h) || !(h)->b) return osqp_error(OSQP_WORKSPACE_NOT_INIT_ERROR)
 c_int rldl_batch_solve(RLDLBatch *h) { HB(h); return h->b->solve(); }
+c_int rldl_batch_solve_to_host(RLDLBatch *h, c_float *x, c_float *y, c_int *iter, c_int *status_val, c_float *obj_val,
+                               c_float *pri_res, c_float *dua_res, c_int *rho_updates, c_float *rho_estimate) {
+  HB(h);
+  return h->b->solve_to_host(x, y, iter, status_val, obj_val, pri_res, dua_res, rho_updates, rho_estimate);
+}
 c_int rldl_batch_update_model(RLDLBatch *h, const OSQPDataRLDL *model) {
   HB(h);
   if (!model) return osqp_error(OSQP_DATA_VALIDATION_ERROR);

@@ -75,6 +75,12 @@ struct BatchDev {
   // form scaled data: the scaled ADMM iteration is the unscaled one with per-variable sigma_i = sigma / (c D_i^2)
   // and per-row rho_j = rho_class(E_j l_j, E_j u_j) E_j^2 / c, which is what rho_vec then holds.
   double *sD, *sE, *sC;
+  // Fused solve-and-deliver (rldl_batch_solve_to_host): device-accessible addresses of the caller's PINNED host
+  // arrays, or null.  The group / CTA that finishes an instance writes its x, y (OSQP_NAN when the status carries
+  // no solution) and info scalars straight to host memory, so the device-to-host transfer of a batch runs behind
+  // the rest of the solve instead of after it.  Layout as rldl_batch_get_solution / rldl_batch_get_info.
+  double *hx, *hy, *h_obj, *h_pri, *h_dua, *h_rho_est;
+  long long *h_iter, *h_status, *h_rho_updates;
   // Streaming layout (rldl_stream.cu): one record per (instance, stage), RS doubles:
   //   [ q_k (qa) | Xinv_k packed (PX) | Sinv_k packed (PS) | row classes (kClsWords) | l_k (bb) | u_k (bb) ]
   // packed = lower triangle, column-major, of the a x a / nx x nx symmetric pivot inverse;

@@ -585,6 +585,29 @@ __device__ __forceinline__ bool time_check_due(const SettingsDev &S, int iter, b
   return S.time_limit_ns > 0 && (can_check || (!S.check_termination && iter % 25 == 0));
 }
 
+// store_solution (auxil.c:527-563) + the info scalars of a finished instance, written straight to the caller's pinned
+// host arrays (BatchDev::hx ...) by `nthr` cooperating threads (tid = 0 .. nthr-1) that can all see the final
+// iterates in global memory.  No-op unless the solve was started through rldl_batch_solve_to_host.
+__device__ __forceinline__ void deliver_to_host(const BatchDev &B, int inst, int tid, int nthr, int n, int m, int status,
+                                                long long iter, double obj, double pri, double dua, double rho_est) {
+  if (!B.h_status) return;
+  const bool has_sol = !(status == -3 || status == 3 || status == -4 || status == 4 || status == -7);
+  const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
+  if (B.hx)
+    for (int i = tid; i < n; i += nthr) B.hx[vo + i] = has_sol ? __ldcg(B.x + vo + i) : kOsqpNan;
+  if (B.hy)
+    for (int r = tid; r < m; r += nthr) B.hy[ro + r] = has_sol ? __ldcg(B.y + ro + r) : kOsqpNan;
+  if (tid == 0) {
+    B.h_status[inst] = status;
+    if (B.h_iter) B.h_iter[inst] = iter;
+    if (B.h_obj) B.h_obj[inst] = obj;
+    if (B.h_pri) B.h_pri[inst] = pri;
+    if (B.h_dua) B.h_dua[inst] = dua;
+    if (B.h_rho_est) B.h_rho_est[inst] = rho_est;
+    if (B.h_rho_updates) B.h_rho_updates[inst] = B.rho_updates[inst];
+  }
+}
+
 // compute_rho_estimate (auxil.c:13-55)
 __device__ __forceinline__ double rho_estimate(const Resid &R, double rho) {
   const double pr = R.pri / (fmax(R.nz, R.nAx) + 1e-10);

@@ -192,6 +192,7 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
   const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
   if (B.fact_flag[inst]) {  // failed factorisation: report non-convex, like a diverged solve
     if (lane == 0) { B.status[inst] = -7; B.iter[inst] = 0; B.obj[inst] = kOsqpNan; }
+    deliver_to_host(B, inst, lane, 32, n, m, -7, 0, kOsqpNan, 0.0, 0.0, 0.0);
     return;
   }
   if (!warm_start) {
@@ -276,6 +277,8 @@ __global__ void k_admm(ModelDev M, BatchDev B, SettingsDev S, int warm_start) {
     B.rho_updates[inst] += rho_updates;
     B.rho[inst] = rho;
   }
+  __syncwarp();
+  deliver_to_host(B, inst, lane, 32, n, m, status, it_done, obj, R.pri, R.dua, rho_est);
 }
 
 // ---------------------------------------------------------------------------

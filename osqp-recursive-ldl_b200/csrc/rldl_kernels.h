@@ -36,7 +36,7 @@ struct StreamTuning {
   int ring_depth = 0;   // stage records in flight per lane group (default 2)
   int sched_s0 = -1;    // iterations a fresh instance runs before it may yield (default check_termination; 0 = scheduler off)
   int ctas_per_sm = 0;  // resident CTAs per SM (default 4 with the latency-mode hand-off, 3 without)
-  int l2_hints = 0;     // bit 0: stage records evict_first; bit 1: forward intermediates evict_last / evict_first
+  int l2_hints = 1;     // bit 0: stage records evict_first; bit 1: forward intermediates evict_last / evict_first
 };
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
                                int resume, int park_below, const StreamTuning &tune, cudaStream_t st);

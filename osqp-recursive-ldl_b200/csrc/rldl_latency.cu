@@ -296,6 +296,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
           if (!resume || B.status[i] == -10) {
             B.status[i] = -7; B.iter[i] = 0; B.obj[i] = kOsqpNan;
             atomicSub(B.sched + kSchedUnfinished, 1);
+            deliver_to_host(B, i, 0, 1, n, m, -7, 0, kOsqpNan, 0.0, 0.0, 0.0);
           }
           continue;
         }
@@ -803,12 +804,15 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
           // parked for the batched re-factorisation, resumed afterwards
           if (gl == 0) { B.iter[inst] = iter; B.status[inst] = kStatusParkedRho; }
         }
-        if (gl == 0) ctl[1] = (done || rho_changed) ? 1 : 0;
+        if (gl == 0) ctl[1] = done ? 2 : (rho_changed ? 1 : 0);
       }
       __syncthreads();
       PT(5);
       if (ctl[1]) break;
     }
+    if (ctl[1] == 2 && B.h_status)  // fused solve-and-deliver: the whole CTA copies the finished instance out
+      deliver_to_host(B, inst, threadIdx.x, blockDim.x, n, m, __ldcg(B.status + inst), __ldcg(B.iter + inst),
+                      __ldcg(B.obj + inst), __ldcg(B.pri + inst), __ldcg(B.dua + inst), __ldcg(B.rho_est + inst));
 #ifdef RLDL_LAT_PROFILE
     if (threadIdx.x == 0 && blockIdx.x == 0)
       printf("lat profile inst %d iters %d: cycles/iter A %lld B %lld C %lld D %lld E %lld epi %lld  (T waits in B+D %lld)\n", inst, iter,

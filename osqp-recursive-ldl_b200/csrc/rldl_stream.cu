@@ -340,10 +340,12 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       if (i >= 0) {
         bool skip = false;
         if (B.fact_flag[i]) {  // failed factorisation: report non-convex, like a diverged solve
-          if (gl == 0 && (!resume || __ldcg(B.status + i) == -10)) {
+          const bool report = !resume || __ldcg(B.status + i) == -10;
+          if (gl == 0 && report) {
             B.status[i] = -7; B.iter[i] = 0; B.obj[i] = kOsqpNan;
             atomicSub(B.sched + kSchedUnfinished, 1);
           }
+          if (report) deliver_to_host(B, i, gl, G, n, m, -7, 0, kOsqpNan, 0.0, 0.0, 0.0);
           skip = true;
         } else if (resume && __ldcg(B.status + i) != -10) {
           skip = true;  // finished in an earlier launch of this solve
@@ -617,6 +619,10 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           B.dua[inst] = R.dua;
           B.rho_est[inst] = rho_est;
           atomicSub(B.sched + kSchedUnfinished, 1);
+        }
+        if (B.h_status) {  // fused solve-and-deliver: this instance's results go to the host now
+          __syncwarp(gm);
+          deliver_to_host(B, inst, gl, G, n, m, status, iter, obj, R.pri, R.dua, rho_est);
         }
         drain();
         have = start_next();

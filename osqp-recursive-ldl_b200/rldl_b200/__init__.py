@@ -109,7 +109,7 @@ osqp_update_polish osqp_update_polish_refine_iter osqp_update_verbose osqp_updat
 osqp_setup_recursive osqp_solve_recursive osqp_update_recursive osqp_setup_combine_recursive
 osqp_solve_combine_recursive osqp_update_Z_horizon osqp_update_X_horizon
 osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions cleanup_rldl
-rldl_batch_setup rldl_batch_solve rldl_batch_update_bounds rldl_batch_partial_update_bounds
+rldl_batch_setup rldl_batch_solve rldl_batch_solve_to_host rldl_batch_update_bounds rldl_batch_partial_update_bounds
 rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
 rldl_batch_refactor rldl_batch_update_model rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_get_solution rldl_batch_get_info
 rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel rldl_batch_set_tuning rldl_batch_get_scaling rldl_batch_get_polish
@@ -163,6 +163,7 @@ def lib():
         "get_L_dimensions": [C.POINTER(OSQPWorkspace), C.POINTER(c_int), C.POINTER(c_int), C.POINTER(c_int)],
         "rldl_batch_setup": [C.POINTER(vp), C.POINTER(OSQPDataRLDL), C.POINTER(OSQPSettings)] + [c_int] * 7 + [vp] * 4,
         "rldl_batch_solve": [vp],
+        "rldl_batch_solve_to_host": [vp] * 10,
         "rldl_batch_update_bounds": [vp, vp, vp],
         "rldl_batch_partial_update_bounds": [vp, c_int, c_int, vp, vp],
         "rldl_batch_update_lin_cost": [vp, vp],
@@ -264,6 +265,12 @@ class Batch:
 
     def solve(self):
         return lib().rldl_batch_solve(self.h)
+
+    def solve_to_host(self, out):
+        """rldl_batch_solve_to_host into the arrays of `out` (keys as get(); pinned arrays are written by the
+        kernels while the solve runs, pageable ones by copies after it)."""
+        return lib().rldl_batch_solve_to_host(self.h, *[_p(out[k]) for k in (
+            "x", "y", "iter", "status", "obj", "pri_res", "dua_res", "rho_updates", "rho_estimate")])
 
     def get(self):
         B = self.batch

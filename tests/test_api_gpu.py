@@ -301,7 +301,7 @@ def test_setup_validation_errors():
     assert L.osqp_update_max_iter(w, 0) == 1 and L.osqp_update_max_iter(w, 10) == 0
     assert L.osqp_update_eps_abs(w, -1.0) == 1 and L.osqp_update_eps_rel(w, -1.0) == 1
     assert L.osqp_update_check_termination(w, -1) == 1
-    assert L.osqp_update_polish(w, 1) == 1 and L.osqp_update_polish(w, 0) == 0
+    assert L.osqp_update_polish(w, 2) == 1 and L.osqp_update_polish(w, 1) == 0 and L.osqp_update_polish(w, 0) == 0
     # max_iter = 10 with check_termination = 25: stops at 10 with "maximum iterations reached" (-2)
     L.osqp_update_warm_start(w, 0)
     assert L.osqp_update_eps_abs(w, 1e-14) == 0 and L.osqp_update_eps_rel(w, 1e-14) == 0
@@ -337,3 +337,58 @@ def test_batch_update_model_matches_fresh_setup():
         assert a.solve() == 0
         assert not compare(a.get(), b.get(), n, m)
         a.free(); b.free()
+
+
+def test_model_updates_and_combine_shrink_pinned_to_the_reference():
+    """The sub-paths round 1 only checked against the product's own fresh setup, now against the UNMODIFIED
+    reference's stock path (the same mathematics; the recursive workspace of the reference has no
+    KKT to update, F1, and its combine-variant tail shrink diverges, F8):
+      (1) osqp_update_P_A on a recursive workspace  vs  the reference's own osqp_update_P_A (src/osqp.c:1166-1266)
+          with the same value arrays on a stock workspace, then osqp_update_lin_cost / osqp_update_bounds;
+      (2) rldl_batch_update_model (the batched form)  vs  the same reference run;
+      (3) osqp_update_Z_horizon(-2) after osqp_setup_combine_recursive(15 + 5)  vs  a reference stock setup at
+          N = 18."""
+    N, batch = 12, 6
+    m1, m2 = mpc.random_model(4, 2, seed=31), mpc.random_model(4, 2, seed=32)
+    x0 = mpc.sample_x0(m1, batch, 9)
+    q, l, u = m1.vectors(x0, N)
+    q2, l2, u2 = m2.vectors(x0, N)
+    q2 = q2 + 0.1 * np.random.default_rng(2).standard_normal(q2.shape)
+    Px2, Ax2 = ref_run(m2, N, N, q2, l2, u2, [("get_PA",)], path="stock")[0]
+    ops = [("solve",), ("update_PA", Px2, Ax2), ("update_lin_cost", q2), ("update_bounds", l2, u2), ("solve",), ("get",)]
+    res = ref_run(m1, N, N, q, l, u, ops, path="stock")
+    assert res[1] == 0
+    want = res[5]
+    n, m = N * 6, N * 10 + 4
+    # (1) scalar entry point, instance by instance
+    for k in range(2):
+        a = Scalar(m1, N, N, q[k], l[k], u[k], gpu_settings())
+        assert a.rc == 0 and a.solve() == 0
+        assert a.csc_values("P").shape == Px2.shape and a.csc_values("A").shape == Ax2.shape
+        assert a.L.osqp_update_P_A(a.w, Px2.ctypes.data, None, len(Px2), Ax2.ctypes.data, None, len(Ax2)) == 0
+        assert a.L.osqp_update_lin_cost(a.w, np.ascontiguousarray(q2[k]).ctypes.data) == 0
+        assert a.L.osqp_update_bounds(a.w, np.ascontiguousarray(l2[k]).ctypes.data,
+                                      np.ascontiguousarray(u2[k]).ctypes.data) == 0
+        assert a.solve() == 0
+        bad = compare(a.out(), {key: v[k:k + 1] for key, v in want.items()}, n, m)
+        assert not bad, (k, bad)
+        a.free()
+    # (2) batched
+    gb = R.Batch(m1, N, N, q, l, u, gpu_settings())
+    assert gb.solve() == 0 and gb.update_model(m2) == 0
+    assert gb.update_lin_cost(q2) == 0 and gb.update_bounds(l2, u2) == 0 and gb.solve() == 0
+    bad = compare(gb.get(), want, n, m)
+    gb.free()
+    assert not bad, bad[:3]
+    # (3) combine variant: tail shrink
+    mdl, Nc, x0c, qc, lc, uc = problem("C1", 1, Nmax=22)
+    ws = Scalar(mdl, 20, 22, qc[0], lc[0], uc[0], gpu_settings(), combine=(15, 5))
+    assert ws.rc == 0 and ws.solve() == 0
+    ws.L.osqp_update_warm_start(ws.w, 0)
+    assert ws.L.osqp_update_Z_horizon(ws.w, C.byref(ws.d), -2) == 0 and ws.solve() == 0
+    q18, l18, u18 = mdl.vectors(x0c[:1], 18)
+    ref18 = ref_run(mdl, 18, 18, q18, l18, u18, [("solve",), ("get",), ("dims",)], path="stock")
+    assert ws.dims() == tuple(ref18[2])
+    bad = compare(ws.out(), ref18[1], *ref18[2])
+    ws.free()
+    assert not bad, bad

@@ -196,3 +196,54 @@ def test_c5_every_instance_against_the_reference_fixture(capsys):
     with capsys.disabled():
         print(f"C5 solved twice: {flips} instances with a different status / iteration count, max |dx| {dx:.2e}")
     assert flips == 0 and dx < 1e-9
+
+
+def test_c3_closed_loop_as_configured():
+    """BASELINE config C3 as stated: quadcopter nx=12 nu=4 N=50, batch 4 096, T=20 closed-loop steps — solve, apply
+    u0, x0 <- A x0 + B u0, device-side shifted warm start (rldl_batch_warm_start_shift), stage-0
+    rldl_batch_partial_update_bounds, horizon shrink every 5th step (tail re-factorisation from the saved S_k) and
+    grow back at the last step.  64 sampled instances are replayed on the unmodified reference with the GPU's own
+    feedback (identical problem data at every step; reference: osqp_update_recursive, osqp_update_bounds,
+    osqp_warm_start — src/recursive_ldl.c:1973-2016, 119-201) and every step is compared."""
+    from oracle import scenarios
+    cfg = mpc.CONFIGS["C3"]
+    mdl, N0, batch, T = mpc.make_model(cfg), cfg["N"], 4096, 20
+    nx, nu, ny = mdl.nx, mdl.nu, mdl.ny
+    x0 = mpc.sample_x0(mdl, batch, 4321)
+    q, l, u = mdl.vectors(x0, N0, N0 + 1)
+    idx = np.sort(np.random.default_rng(11).choice(batch, 64, replace=False))
+    gb = R.Batch(mdl, N0, N0 + 1, q, l, u, gpu_settings(warm_start=1))
+    N, xcur, steps, fb = N0, x0.copy(), [], []
+    for t in range(T):
+        assert gb.solve() == 0
+        r = gb.get()
+        n, m, _, _ = gb.dims()
+        assert np.isin(r["status"], (1, 2, -2)).all() and (r["status"] == 1).mean() > 0.999, \
+            (t, np.unique(r["status"], return_counts=True))
+        steps.append(dict(N=N, n=n, m=m, iter=r["iter"][idx].copy(), status=r["status"][idx].copy(),
+                          obj=r["obj"][idx].copy(), x=r["x"][idx, :n].copy(), y=r["y"][idx, :m].copy()))
+        if t + 1 == T:
+            break
+        u0 = r["x"][:, :nu]
+        fb.append(u0[idx].copy())
+        xcur = xcur @ mdl.A.T + u0 @ mdl.B.T
+        assert gb.warm_start_shift() == 0
+        Nnew = N - 1 if (t + 1) % 5 == 0 else N
+        if t + 2 == T:
+            Nnew = N0
+        if Nnew != N:
+            assert gb.update_horizon(Nnew) == 0
+            N = Nnew
+        dyn0 = np.ascontiguousarray(-(xcur @ mdl.A.T))
+        assert gb.partial_update_bounds(ny, ny + nx, dyn0, dyn0) == 0
+    gb.free()
+    assert [s["N"] for s in steps] == [50] * 5 + [49] * 5 + [48] * 5 + [47] * 4 + [50]
+    ref = ref_run(mdl, N0, N0 + 1, q[idx], l[idx], u[idx], [("receding", x0[idx], T, 5, fb)], warm_start=1)[0]
+    mism = 0
+    for t, (s, rr) in enumerate(zip(steps, ref)):
+        assert s["N"] == rr["N"]
+        out = dict(status=s["status"], iter=s["iter"], obj=s["obj"], x=s["x"], y=s["y"])
+        bad = compare(out, dict(status=rr["status"], iter=rr["iter"], obj=rr["obj"], x=rr["x"], y=rr["y"]), s["n"], s["m"])
+        mism += len(bad)
+        assert not bad, (t, bad[:3])
+    assert mism == 0

@@ -165,3 +165,37 @@ def test_other_specialised_shapes_match_reference(nx, nu, monkeypatch):
         bad = compare(gb.get(), ref, n, m)
         assert not bad, (nx, nu, below, bad[:5])
         gb.free()
+
+
+@pytest.mark.parametrize("name,batch,below,kernel", [("C1", 3000, 1024, 0), ("C1", 500, 100000, 0), ("C3", 300, 100, 0),
+                                                     ("C1", 64, 0, 1)],
+                         ids=["stream+tail", "latency", "C3 hand-off", "generic"])
+@pytest.mark.parametrize("pinned", [True, False])
+def test_solve_to_host_delivers_what_get_returns(name, batch, below, kernel, pinned):
+    """rldl_batch_solve_to_host: the kernels write every finished instance to PINNED host arrays themselves
+    (pageable arrays: copies after the solve); bitwise what rldl_batch_get_solution / _get_info return, including
+    OSQP_NAN rows for an instance without a solution."""
+    import torch
+    mdl, N, x0, q, l, u = problem(name, batch)
+    b = mdl.nx + mdl.ny
+    l[1, b:b + mdl.nx] = 10.0; u[1, b:b + mdl.nx] = 11.0      # instance 1: primal infeasible
+    gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+    assert gb.select_kernel(kernel) == 0
+    gb.set_tuning(lat_below=below)
+    shapes = dict(x=q.shape, y=l.shape, iter=batch, status=batch, obj=batch, pri_res=batch, dua_res=batch,
+                  rho_updates=batch, rho_estimate=batch)
+    ints = ("iter", "status", "rho_updates")
+    tens = {k: torch.full(shp if isinstance(shp, tuple) else (shp,), -77, dtype=torch.int64 if k in ints else torch.float64)
+            for k, shp in shapes.items()}
+    if pinned:
+        tens = {k: t.pin_memory() for k, t in tens.items()}
+    out = {k: t.numpy() for k, t in tens.items()}
+    assert gb.solve_to_host(out) == 0
+    want = gb.get()
+    n, m, _, _ = gb.dims()
+    gb.free()
+    assert want["status"][1] in (-3, 3) and (want["status"] == 1).sum() >= batch - 2
+    for k in ("iter", "status", "obj", "pri_res", "dua_res", "rho_updates", "rho_estimate"):
+        assert np.array_equal(out[k], want[k]), k
+    assert np.array_equal(out["x"][:, :n], want["x"][:, :n]) and np.array_equal(out["y"][:, :m], want["y"][:, :m])
+    assert (out["x"][1, :n] == float(0x7fc00000)).all()
