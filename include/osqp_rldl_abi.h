@@ -463,6 +463,11 @@ c_int rldl_batch_select_kernel(RLDLBatch *b, c_int which);
  *   "sched_s0"    iterations a fresh instance runs before it may be pre-empted (default check_termination;
  *                 0 = device priority scheduler off)
  *   "ctas_per_sm" resident CTAs per SM of the streaming kernel (default 4, 3 without the hand-off)
+ *   "l2_hints"    bit 0: stage records are streamed with an L2 evict-first policy (default 1)
+ *   "lat_lane"    latency-mode CTAs that run BESIDE the streaming kernel towards the end of a launch and take over
+ *                 its most-unconverged instances, whose chains would otherwise bound the tail (default 8, 0 = off)
+ *   "lat_retire_below"  unfinished instances at which the streaming CTAs on the lane's SMs retire
+ *                 (default 6 x lat_below)
  * value = -1 restores the default.  Returns 0, or 1 for an unknown name / invalid value. */
 c_int rldl_batch_set_tuning(RLDLBatch *b, const char *name, c_int value);
 /* the CUDA stream (cudaStream_t) every launch and copy of this handle is issued on, so a

@@ -190,7 +190,7 @@ c_int Batch::configure_stream() {
   if (streaming && !slots_full) {
     if (D.sched_slots) cudaFree(D.sched_slots);
     D.sched_slots = nullptr;
-    CK(dalloc(&D.sched_slots, (size_t)kSchedBuckets * bs));
+    CK(dalloc(&D.sched_slots, (size_t)kSchedRings * bs));
     slots_full = true;
   } else if (!D.sched_slots) {
     CK(dalloc(&D.sched_slots, 1));
@@ -313,8 +313,15 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(dalloc(&D.sched, kSchedCounters));
   rc = B->configure_stream();
   if (rc) return rc;
-  CK(cudaStreamCreateWithFlags(&B->stream, cudaStreamNonBlocking));
+  {
+    int lo = 0, hi = 0;  // lowest / highest priority (numerically greatest / least)
+    CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CK(cudaStreamCreateWithPriority(&B->stream, cudaStreamNonBlocking, hi));
+    CK(cudaStreamCreateWithPriority(&B->stream2, cudaStreamNonBlocking, lo));
+  }
   CK(cudaEventCreate(&B->ev0)); CK(cudaEventCreate(&B->ev1));
+  CK(cudaEventCreateWithFlags(&B->ev_reset, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&B->ev_lane, cudaEventDisableTiming));
   B->set_sizes();
   B->push_settings();
   // per-instance data
@@ -373,6 +380,9 @@ Batch::~Batch() {
   if (h_pin) cudaFreeHost(h_pin);
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
+  if (ev_reset) cudaEventDestroy(ev_reset);
+  if (ev_lane) cudaEventDestroy(ev_lane);
+  if (stream2) cudaStreamDestroy(stream2);
   if (stream) cudaStreamDestroy(stream);
 }
 
@@ -484,20 +494,38 @@ c_int Batch::solve() {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     const size_t lat_smem = latency_smem_bytes(M, N);
     const bool lat_ok = lat_below > 0 && lat_smem != (size_t)-1 && lat_smem <= 227 * 1024;
-    if (lat_ok && !d_latT) CK(cudaMalloc(&d_latT, (size_t)sms * latency_t_blocks(Nmax) * nx * (nx + 2) * sizeof(double)));
+    const int lane = lat_ok ? std::min(std::max(lat_lane, 0), 32) : 0;
+    const size_t t_per_cta = (size_t)latency_t_blocks(Nmax) * nx * (nx + 2);
+    if (lat_ok && !d_latT) CK(cudaMalloc(&d_latT, (size_t)(sms + 32) * t_per_cta * sizeof(double)));
     int unfinished = batch, resume = 0;
     CK(cudaMemcpyAsync(D.sched + kSchedUnfinished, &unfinished, sizeof(int), cudaMemcpyHostToDevice, stream));
     for (;;) {
       const bool run_stream = !lat_ok || unfinished > lat_below;
+      // the lane only pays when the launch is long enough for the streaming CTAs to retire well before its end
+      const bool run_lane = run_stream && lane > 0 && unfinished >= 4 * lat_below;
       if (run_stream) {
-        CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, lat_ok ? lat_below : 0, tune, stream));
+        int s_ctas = 0;
+        const int retire = lat_retire_below > 0 ? lat_retire_below : 6 * lat_below;
+        CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, lat_ok ? lat_below : 0, tune,
+                              run_lane ? lane : 0, retire, run_lane ? ev_reset : nullptr, &s_ctas, stream));
         launches++;
+        if (run_lane) {
+          // latency-mode CTAs beside the streaming kernel: pending until its CTAs on SMs 0..lane-1 retire, then fed
+          // with the most-unconverged instances by the streaming groups (their chains would bound the tail)
+          CK(cudaStreamWaitEvent(stream2, ev_reset, 0));
+          CK(launch_admm_latency(M, D, S, (int)settings.warm_start, 1, d_latT + (size_t)sms * t_per_cta, lane, 0, 2,
+                                 s_ctas, stream2));
+          CK(cudaEventRecord(ev_lane, stream2));
+          CK(launch_set_tail_flag(D, stream));  // after the streaming kernel: nobody waits for a hand-over any more
+          launches += 2;
+        }
       }
       if (lat_ok) {
         CK(launch_admm_latency(M, D, S, (int)settings.warm_start, (resume || run_stream) ? 1 : 0, d_latT,
-                               std::min(sms, batch), run_stream ? 0 : 1, run_stream ? 1 : 0, stream));
+                               std::min(sms, batch), run_stream ? 0 : 1, run_stream ? 1 : 0, 0, stream));
         launches++;
       }
+      if (run_lane) CK(cudaStreamWaitEvent(stream, ev_lane, 0));
       if (!settings.adaptive_rho) break;
       int cnt[2] = {0, 0};
       CK(cudaMemcpyAsync(&cnt[0], D.sched + 1, sizeof(int), cudaMemcpyDeviceToHost, stream));

@@ -15,6 +15,11 @@ struct Batch {
   int kernel_choice = 0;   // 0 auto, 1 force the generic (runtime-shape) ADMM kernel
   int lat_below = 1024;    // hand-off threshold: unfinished instances at which the latency-mode kernel takes over (0: never)
   StreamTuning tune;       // launch knobs of the streaming kernel (rldl_batch_set_tuning)
+  // concurrent latency-mode lane: lat_lane CTAs of the latency-mode kernel run beside the streaming kernel on the SMs
+  // its CTAs vacate once at most lat_retire_below instances are unfinished (0 = 6 x lat_below); lat_lane = 0: off
+  int lat_lane = 8, lat_retire_below = 0;
+  cudaStream_t stream2 = nullptr;  // the lane's stream (lower priority than `stream`)
+  cudaEvent_t ev_reset = nullptr, ev_lane = nullptr;
   bool streaming = false;  // shapes the streaming kernels cover (rldl_stream.cu)
   bool need_unpacked = false;   // a generic-kernel consumer wants Xinv/Sinv unpacked as well as the records
   bool unpacked_valid = false;  // D.Xinv / D.Sinv match the current factorisation

@@ -862,7 +862,9 @@ c_int rldl_batch_set_tuning(RLDLBatch *h, const char *name, c_int value) {
   else if (!strcmp(name, "ring_depth")) B->tune.ring_depth = (int)value < 0 ? 0 : (int)value;
   else if (!strcmp(name, "sched_s0")) B->tune.sched_s0 = (int)value;
   else if (!strcmp(name, "ctas_per_sm")) B->tune.ctas_per_sm = (int)value < 0 ? 0 : (int)value;
-  else if (!strcmp(name, "l2_hints")) B->tune.l2_hints = (int)value < 0 ? 0 : (int)value;
+  else if (!strcmp(name, "l2_hints")) B->tune.l2_hints = (int)value < 0 ? 1 : (int)value;
+  else if (!strcmp(name, "lat_lane")) B->lat_lane = (int)value < 0 ? 8 : (int)value;
+  else if (!strcmp(name, "lat_retire_below")) B->lat_retire_below = (int)value < 0 ? 0 : (int)value;
   else return 1;
   return 0;
 }

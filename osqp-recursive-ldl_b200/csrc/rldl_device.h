@@ -92,7 +92,8 @@ struct BatchDev {
   long long rec_stride;    // (Nmax+1)*RS doubles per instance
   // Device work scheduler of the persistent ADMM kernel (rldl_stream.cu):
   //   sched[0] fresh-instance counter, sched[1] instances parked for a rho refactorisation,
-  //   sched[2 .. 2+kSchedBuckets) bucket heads, sched[2+kSchedBuckets .. 2+2*kSchedBuckets) bucket tails;
+  //   sched[2 .. 2+kSchedRings) ring heads, sched[2+kSchedRings .. 2+2*kSchedRings) ring tails (rings 0..31: the
+  //   priority buckets; ring kSchedLQ: instances handed to the latency-mode CTAs that run beside the streaming kernel);
   //   sched_slots[b*batch + (index mod batch)] = suspended instance, -1 = empty.
   int *sched;
   int *sched_slots;
@@ -102,9 +103,14 @@ constexpr int kClsWords = 2;  // 64-bit words of 2-bit row classes per stage rec
 constexpr int kSchedBuckets = 32;  // priority buckets: floor(2*log2(residual / tolerance)), clamped
 // sched[kSchedUnfinished]: instances of the current solve not yet finished (kept across the launches of
 // one solve: streaming launch, latency-mode launch, adaptive-rho resume rounds); kSchedCounters = array size
-constexpr int kSchedUnfinished = 2 + 2 * kSchedBuckets;
+constexpr int kSchedLQ = kSchedBuckets;         // ring of instances handed over to the concurrent latency-mode CTAs
+constexpr int kSchedRings = kSchedBuckets + 1;
+constexpr int kSchedUnfinished = 2 + 2 * kSchedRings;
 constexpr int kSchedT0 = kSchedUnfinished + 2;  // 64-bit %globaltimer value at the start of the current solve
-constexpr int kSchedCounters = kSchedT0 + 2;
+// concurrent latency-mode lane: latency-mode CTAs waiting for an instance, the urgency bucket an instance
+// must have to be handed over (decaying maximum), streaming CTAs started, "the streaming kernel has hit its tail / ended"
+constexpr int kSchedLWant = kSchedT0 + 2, kSchedTop = kSchedT0 + 3, kSchedStarted = kSchedT0 + 4, kSchedTailFlag = kSchedT0 + 5;
+constexpr int kSchedCounters = kSchedT0 + 6;
 
 constexpr int STATUS_FACTOR_ERROR = -7;  // reported as OSQP_NON_CVX
 // device-internal: instance parked by an adaptive-rho update until its factor has been refreshed (never

@@ -38,13 +38,18 @@ struct StreamTuning {
   int ctas_per_sm = 0;  // resident CTAs per SM (default 4 with the latency-mode hand-off, 3 without)
   int l2_hints = 1;     // bit 0: stage records evict_first; bit 1: forward intermediates evict_last / evict_first
 };
+// k_l > 0: the CTAs on SMs 0 .. k_l-1 retire once at most retire_below instances are unfinished (concurrent
+// latency-mode lane); reset_done (optional) is recorded after the scheduler reset and before the kernel; grid_out
+// (optional) receives the number of CTAs launched
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                               int resume, int park_below, const StreamTuning &tune, cudaStream_t st);
+                               int resume, int park_below, const StreamTuning &tune, int k_l, int retire_below,
+                               cudaEvent_t reset_done, int *grid_out, cudaStream_t st);
+cudaError_t launch_set_tail_flag(const BatchDev &B, cudaStream_t st);
 // latency-mode kernel (rldl_latency.cu): one instance per CTA, factor resident in shared memory
 int latency_t_blocks(int Nmax);  // nx x (nx+2) blocks of global scratch per CTA of the latency-mode kernel
 size_t latency_smem_bytes(const ModelDev &M, int N);  // (size_t)-1 if the shape is not in the table
 cudaError_t launch_admm_latency(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                int resume, double *Tg, int ctas, int reset_parked, int from_buckets,
+                                int resume, double *Tg, int ctas, int reset_parked, int claim_mode, int stream_ctas,
                                 cudaStream_t st);
 cudaError_t launch_factor_stream(const ModelDev &M, const BatchDev &B, double sigma, int k0,
                                  const int *only_flagged, int write_unpacked, cudaStream_t st);

@@ -68,7 +68,7 @@ struct LatLayout {  // shared-memory layout (doubles) of k_admm_cta for horizon 
 
 template <class SH>
 __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDev B, SettingsDev S, int warm_start,
-                                                              int resume, double *Tg, int from_buckets) {
+                                                              int resume, double *Tg, int claim_mode, int stream_ctas) {
   constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, NT = SH::NT, CW = SH::CW, G = SH::G, NYT = SH::NYT,
                 ROWS = SH::ROWS, RS = SH::RS, BQ = SH::B, AE = SH::AE, NXE = SH::NXE, NG = LatLayout<SH>::NG;
   extern __shared__ __align__(16) double smem[];
@@ -275,16 +275,40 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
 
   for (;;) {
     // ---------------- claim an instance ----------------
-    // from_buckets: the tail of a streaming launch — every unfinished instance sits suspended in its priority
-    // bucket; the most-unconverged ones (the longest remaining chains) are resumed first.
+    // claim_mode 1: the tail of a streaming launch — first the instances handed over to the latency-mode lane that
+    //   nobody took, then every suspended instance, most-unconverged first (the longest remaining chains start first).
+    // claim_mode 2: a CTA of the concurrent lane, launched beside the streaming kernel: it waits for hand-overs
+    //   (kSchedLWant announces it, the streaming groups answer through ring kSchedLQ); once the streaming kernel has
+    //   hit its tail it behaves like mode 1.  A CTA that became resident before every streaming CTA had started
+    //   would keep an SM from the streaming kernel for the whole launch: it leaves at once.
     // otherwise: the fresh counter, with the same resume rules as the streaming kernel.
-    if (threadIdx.x == 0 && from_buckets) {
+    if (threadIdx.x == 0 && claim_mode) {
       int i = -1;
-      for (int b = kSchedBuckets - 1; b >= 0 && i < 0; b--)
-        while (ld_volatile(B.sched + 2 + kSchedBuckets + b) > ld_volatile(B.sched + 2 + b)) {
-          i = sched_pop(B, b);
-          if (i >= 0) break;
+      if (claim_mode == 2 && ld_volatile(B.sched + kSchedStarted) < stream_ctas && !ld_volatile(B.sched + kSchedTailFlag)) {
+        i = -1;
+      } else {
+        if (sched_ring_nonempty(B, kSchedLQ)) i = sched_pop(B, kSchedLQ);
+        if (i < 0 && claim_mode == 2 && !ld_volatile(B.sched + kSchedTailFlag)) {
+          atomicAdd(B.sched + kSchedLWant, 1);
+          for (int spins = 1;; spins++) {
+            if (sched_ring_nonempty(B, kSchedLQ) && (i = sched_pop(B, kSchedLQ)) >= 0) break;
+            if (ld_volatile(B.sched + kSchedUnfinished) <= 0 || ld_volatile(B.sched + kSchedTailFlag)) break;
+            __nanosleep(2000);
+            if ((spins & 7) == 0) {  // nobody qualified for a while: lower the hand-over threshold by one bucket
+              const int t = ld_volatile(B.sched + kSchedTop);
+              if (t < kSchedBuckets - 3) atomicCAS(B.sched + kSchedTop, t, t + 1);
+            }
+          }
+          if (i < 0) {  // leaving without a hand-over: take the announcement back if it is still there
+            int w = ld_volatile(B.sched + kSchedLWant);
+            while (w > 0 && atomicCAS(B.sched + kSchedLWant, w, w - 1) != w) w = ld_volatile(B.sched + kSchedLWant);
+          }
         }
+        if (i < 0 && (claim_mode == 1 || ld_volatile(B.sched + kSchedTailFlag))) {
+          if (sched_ring_nonempty(B, kSchedLQ)) i = sched_pop(B, kSchedLQ);
+          if (i < 0) i = sched_pop_best(B);
+        }
+      }
       if (i >= 0) __threadfence();  // order the loads of the iterates after the hand-over
       ctl[0] = i;
     } else if (threadIdx.x == 0) {
@@ -830,16 +854,18 @@ static size_t latency_smem_t(int N) {
 
 template <class SH>
 static cudaError_t launch_latency_t(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                    int resume, double *Tg, int ctas, int reset_parked, int from_buckets,
+                                    int resume, double *Tg, int ctas, int reset_parked, int claim_mode, int stream_ctas,
                                     cudaStream_t st) {
   const size_t shm = latency_smem_t<SH>(B.N);
   auto kern = k_admm_cta<SH>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm);
   if (e != cudaSuccess) return e;
   // fresh counter; the parked-for-rho counter only if no streaming launch of this round has counted into it
-  e = cudaMemsetAsync(B.sched, 0, (reset_parked ? 2 : 1) * sizeof(int), st);
-  if (e != cudaSuccess) return e;
-  kern<<<(unsigned)ctas, kLatThreads, shm, st>>>(M, B, S, warm_start, resume, Tg, from_buckets);
+  if (claim_mode != 2) {  // (the concurrent lane shares the scheduler state of the running streaming kernel)
+    e = cudaMemsetAsync(B.sched, 0, (reset_parked ? 2 : 1) * sizeof(int), st);
+    if (e != cudaSuccess) return e;
+  }
+  kern<<<(unsigned)ctas, kLatThreads, shm, st>>>(M, B, S, warm_start, resume, Tg, claim_mode, stream_ctas);
   return cudaGetLastError();
 }
 
@@ -855,13 +881,13 @@ size_t latency_smem_bytes(const ModelDev &M, int N) {
 }
 
 cudaError_t launch_admm_latency(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                int resume, double *Tg, int ctas, int reset_parked, int from_buckets,
+                                int resume, double *Tg, int ctas, int reset_parked, int claim_mode, int stream_ctas,
                                 cudaStream_t st) {
   const int cw = max_c_width(M);
 #define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                    \
   if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))         \
     return launch_latency_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, Tg, ctas, reset_parked, \
-                                                                 from_buckets, st);
+                                                                 claim_mode, stream_ctas, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;

@@ -85,40 +85,67 @@ __global__ void __launch_bounds__(256) k_vec_records(BatchDev B, int k0, int par
   const double rho = fmin(fmax(B.rho[inst], kRhoMin), kRhoMax);
   double *rec = B.rec + (size_t)inst * B.rec_stride;
   int ch = 0;
-#pragma unroll 2
-  for (int k = k0 + wid; k <= N; k += nw) {
-    const bool term = (k == N);
-    double *rk = rec + (size_t)k * RS;
-    if (parts & 1) {
-      const int dim = term ? NX : A, ilo = (k == 0 && !term) ? NX : 0, xoff = k * A - NX;
-      for (int o = lane; o < SH::QA; o += 32) rk[o] = (o >= ilo && o < dim) ? B.q[vo + xoff + o] : 0.0;
-    }
-    if (parts & 2) {
+  // Each warp takes its stages U at a time: all loads of the U stages are issued before the first dependent
+  // instruction (the stores of one stage may alias the loads of the next as far as the compiler knows, so a plain
+  // loop runs one DRAM round trip per stage and leaves the memory system idle)
+  constexpr int U = 4, W = (SH::BB + 31) / 32;
+  static_assert(W <= kClsWords, "class words");
+  for (int kb = k0 + wid; kb <= N; kb += U * nw) {
+    double lv[U][W], uv[U][W], qv[U];
+    unsigned long long old[U][W];
+#pragma unroll
+    for (int j = 0; j < U; j++) {
+      const int k = kb + j * nw;
+      const bool on = k <= N, term = (k == N);
       const int rows = term ? NT : BQ;
+      const int dim = term ? NX : A, ilo = (k == 0 && !term) ? NX : 0, xoff = k * A - NX;
+      qv[j] = 0.0;
+      if (on && (parts & 1) && lane >= ilo && lane < dim) qv[j] = __ldcs(B.q + vo + xoff + lane);
 #pragma unroll
-      for (int w = 0; w < kClsWords; w++) {
-        if (32 * w >= SH::BB) break;
+      for (int w = 0; w < W; w++) {
         const int r = 32 * w + lane;
-        double lv = 0.0, uv = 0.0;
-        int c = 0;
-        if (r < rows) {
-          const size_t ri = ro + (size_t)k * BQ + r;
-          lv = B.l[ri]; uv = B.u[ri];
-          c = (lv < -kInfBound && uv > kInfBound) ? 2 : ((uv - lv < kRhoTol) ? 1 : 0);
-          B.rho_vec[ri] = c == 2 ? kRhoMin : (c == 1 ? kRhoEq * rho : rho);
+        lv[j][w] = uv[j][w] = 0.0; old[j][w] = 0ull;
+        if (on && (parts & 2)) {
+          if (r < rows) {
+            const size_t ri = ro + (size_t)k * BQ + r;
+            lv[j][w] = __ldcs(B.l + ri); uv[j][w] = __ldcs(B.u + ri);
+          }
+          if (lane == 0) old[j][w] = (unsigned long long)__double_as_longlong(rec[(size_t)k * RS + SH::CLS + w]);
         }
-        const unsigned long long wv = spread_bits(__ballot_sync(FULL, c == 1)) |
-                                      (spread_bits(__ballot_sync(FULL, c == 2)) << 1);
-        if (lane == 0) {
-          const unsigned long long old = (unsigned long long)__double_as_longlong(rk[SH::CLS + w]);
-          if (old != wv) ch = 1;
-          rk[SH::CLS + w] = __longlong_as_double((long long)wv);
-        }
-        if (r < SH::BB) { rk[SH::LO + r] = lv; rk[SH::UP + r] = uv; }
       }
+    }
 #pragma unroll
-      for (int w = (SH::BB + 31) / 32; w < kClsWords; w++)
-        if (lane == 0) rk[SH::CLS + w] = 0.0;
+    for (int j = 0; j < U; j++) {
+      const int k = kb + j * nw;
+      if (k > N) break;
+      const bool term = (k == N);
+      double *rk = rec + (size_t)k * RS;
+      if (parts & 1) {
+        static_assert(SH::QA <= 32, "q part of a record fits one warp pass");
+        if (lane < SH::QA) rk[lane] = qv[j];
+      }
+      if (parts & 2) {
+        const int rows = term ? NT : BQ;
+#pragma unroll
+        for (int w = 0; w < W; w++) {
+          const int r = 32 * w + lane;
+          int c = 0;
+          if (r < rows) {
+            c = (lv[j][w] < -kInfBound && uv[j][w] > kInfBound) ? 2 : ((uv[j][w] - lv[j][w] < kRhoTol) ? 1 : 0);
+            B.rho_vec[ro + (size_t)k * BQ + r] = c == 2 ? kRhoMin : (c == 1 ? kRhoEq * rho : rho);
+          }
+          const unsigned long long wv = spread_bits(__ballot_sync(FULL, c == 1)) |
+                                        (spread_bits(__ballot_sync(FULL, c == 2)) << 1);
+          if (lane == 0) {
+            if (old[j][w] != wv) ch = 1;
+            rk[SH::CLS + w] = __longlong_as_double((long long)wv);
+          }
+          if (r < SH::BB) { rk[SH::LO + r] = lv[j][w]; rk[SH::UP + r] = uv[j][w]; }
+        }
+#pragma unroll
+        for (int w = W; w < kClsWords; w++)
+          if (lane == 0) rk[SH::CLS + w] = 0.0;
+      }
     }
   }
   if (parts & 2) {
@@ -177,7 +204,7 @@ template <int G>
 __device__ __forceinline__ int sched_best(const BatchDev &B, int gl, unsigned gm) {
   int best = -1;
   for (int b = gl; b < kSchedBuckets; b += G)
-    if (ld_volatile(B.sched + 2 + kSchedBuckets + b) > ld_volatile(B.sched + 2 + b)) best = b;
+    if (sched_ring_nonempty(B, b)) best = b;
 #pragma unroll
   for (int o = G / 2; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(gm, best, o));
   return best;
@@ -192,7 +219,8 @@ __device__ __forceinline__ int sched_best(const BatchDev &B, int gl, unsigned gm
 // ---------------------------------------------------------------------------
 template <class SH>
 __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, SettingsDev S, int warm_start, int D,
-                                                        int resume, int s0, int park_below, int l2_hints) {
+                                                        int resume, int s0, int park_below, int l2_hints, int k_l,
+                                                        int retire_below) {
   constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, NT = SH::NT, CW = SH::CW, G = SH::G, NYT = SH::NYT,
                 ROWS = SH::ROWS, RS = SH::RS, BQ = SH::B;
   extern __shared__ __align__(16) double smem[];
@@ -253,6 +281,12 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
   const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
+  // Concurrent latency-mode lane (k_l > 0): towards the end of the launch the CTAs on SMs 0 .. k_l-1 retire and
+  // latency-mode CTAs (k_admm_cta, launched beside this kernel and pending until an SM is free) take those SMs; the
+  // streaming groups hand them their most-unconverged instances, whose chains would otherwise bound the tail.
+  unsigned smid = 0;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  if (threadIdx.x == 0 && k_l > 0) atomicAdd(B.sched + kSchedStarted, 1);
 
   // lane constants of the diagonal-packed mat-vecs
   Wraps<SH> wr;
@@ -328,9 +362,17 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     }
     return t != 0;
   };
+  auto retiring = [&]() -> bool {  // this SM goes to a latency-mode CTA
+    int t = 0;
+    if (k_l > 0 && (int)smid < k_l) {
+      if (gl == 0) t = ld_volatile(B.sched) >= B.batch && ld_volatile(B.sched + kSchedUnfinished) <= retire_below;
+      t = __shfl_sync(gm, t, 0, G);
+    }
+    return t != 0;
+  };
   auto acquire = [&](int above, bool *fresh) -> int {
     for (;;) {
-      if (tail_reached()) return -1;
+      if (tail_reached() || retiring()) return -1;
       int i = -1;
       if (gl == 0 && ld_volatile(B.sched) < B.batch) {
         i = atomicAdd(B.sched, 1);
@@ -632,10 +674,14 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         if (gl == 0) { B.iter[inst] = iter; B.status[inst] = kStatusParkedRho; }
         drain();
         have = start_next();
-      } else if (can_check && tail_reached()) {
+      } else if (can_check && (tail_reached() || retiring())) {
         // suspended as it stands (status stays OSQP_UNSOLVED) into its priority bucket: the latency-mode kernel
-        // resumes the suspended instances most-unconverged first (the longest remaining chains start first)
-        if (gl == 0) B.iter[inst] = iter;
+        // resumes the suspended instances most-unconverged first (the longest remaining chains start first);
+        // a retiring SM's instances are picked up by the other groups like any suspended instance
+        if (gl == 0) {
+          B.iter[inst] = iter;
+          if (k_l > 0 && tail_reached()) atomicExch(B.sched + kSchedTailFlag, 1);
+        }
         __threadfence();
         __syncwarp(gm);
         if (gl == 0) sched_push(B, urgency_bucket(S, R), inst);
@@ -647,6 +693,31 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         if (sched_on && can_check) {
           // urgency of this instance: distance from its tolerances (auxil.c:259-288, 323-362)
           myb = urgency_bucket(S, R);
+          if (k_l > 0) {
+            // hand-over to a waiting latency-mode CTA: only the most-unconverged instances qualify (kSchedTop is a
+            // decaying maximum of the buckets seen at the checks; the waiting CTAs lower it until someone qualifies)
+            int give = 0;
+            if (gl == 0) {
+              // kSchedTop holds (kSchedBuckets - 1 - threshold), so that an all-zero reset means "top bucket only"
+              const int inv = kSchedBuckets - 1 - myb;
+              atomicMin(B.sched + kSchedTop, inv);
+              if (myb >= 2 && ld_volatile(B.sched + kSchedLWant) > 0 && inv <= ld_volatile(B.sched + kSchedTop)) {
+                if (atomicSub(B.sched + kSchedLWant, 1) > 0) give = 1;
+                else atomicAdd(B.sched + kSchedLWant, 1);
+              }
+            }
+            give = __shfl_sync(gm, give, 0, G);
+            if (give) {
+              if (gl == 0) B.iter[inst] = iter;
+              __threadfence();  // this lane's iterate stores precede the hand-over
+              __syncwarp(gm);
+              if (gl == 0) sched_push(B, kSchedLQ, inst);
+              drain();
+              have = start_next();
+              __syncwarp();
+              continue;
+            }
+          }
           int fresh_left = 0;
           if (gl == 0) fresh_left = ld_volatile(B.sched) < B.batch;
           fresh_left = __shfl_sync(gm, fresh_left, 0, G);
@@ -672,7 +743,8 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
 // ------------------------------- launcher --------------------------------
 template <class SH>
 static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                                   int resume, int park_below, const StreamTuning &tune, cudaStream_t st) {
+                                   int resume, int park_below, const StreamTuning &tune, int k_l, int retire_below,
+                                   cudaEvent_t reset_done, int *grid_out, cudaStream_t st) {
   const int threads = 128, groups = (threads / 32) * SH::GPW;
   int D = tune.ring_depth > 1 ? tune.ring_depth : 2;  // two stage steps of look-ahead cover the HBM latency
   if (D > 2 * (B.N + 1)) D = 2 * (B.N + 1);
@@ -698,12 +770,23 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   const long long need = ((long long)B.batch + groups - 1) / groups;
   if (grid > need) grid = need;
   // scheduler state: counters to 0, every ring slot to -1 (empty)
-  e = cudaMemsetAsync(B.sched, 0, (2 + 2 * kSchedBuckets) * sizeof(int), st);
+  e = cudaMemsetAsync(B.sched, 0, (2 + 2 * kSchedRings) * sizeof(int), st);
   if (e != cudaSuccess) return e;
   // (instances suspended for the latency-mode kernel may be left in the rings of an earlier launch)
-  e = cudaMemsetAsync(B.sched_slots, 0xff, (size_t)kSchedBuckets * B.batch * sizeof(int), st);
+  e = cudaMemsetAsync(B.sched_slots, 0xff, (size_t)kSchedRings * B.batch * sizeof(int), st);
   if (e != cudaSuccess) return e;
-  kern<<<(unsigned)grid, threads, shm, st>>>(M, B, S, warm_start, D, resume, s0, park_below, tune.l2_hints);
+  // concurrent latency-mode lane: waiting CTAs 0, hand-over threshold at the top bucket (stored inverted), CTAs
+  // started 0, tail flag 0
+  static_assert(kSchedTop == kSchedLWant + 1 && kSchedStarted == kSchedLWant + 2 && kSchedTailFlag == kSchedLWant + 3, "layout");
+  e = cudaMemsetAsync(B.sched + kSchedLWant, 0, 4 * sizeof(int), st);
+  if (e != cudaSuccess) return e;
+  if (reset_done) {  // the concurrent latency-mode launch waits for this, not for the kernel
+    e = cudaEventRecord(reset_done, st);
+    if (e != cudaSuccess) return e;
+  }
+  if (grid_out) *grid_out = (int)grid;
+  kern<<<(unsigned)grid, threads, shm, st>>>(M, B, S, warm_start, D, resume, s0, park_below, tune.l2_hints, k_l,
+                                             retire_below);
   return cudaGetLastError();
 }
 
@@ -1050,14 +1133,23 @@ bool stream_supported(const ModelDev &M, int N) {
 }
 
 cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const SettingsDev &S, int warm_start,
-                               int resume, int park_below, const StreamTuning &tune, cudaStream_t st) {
+                               int resume, int park_below, const StreamTuning &tune, int k_l, int retire_below,
+                               cudaEvent_t reset_done, int *grid_out, cudaStream_t st) {
   const int cw = max_c_width(M);
 #define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                                          \
   if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))      \
-    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, park_below, tune, st);
+    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, park_below, tune, k_l, \
+                                                                retire_below, reset_done, grid_out, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;
+}
+
+__global__ void k_set_tail_flag(int *sched) { atomicExch(sched + kSchedTailFlag, 1); }
+// stream-ordered "the streaming kernel has ended": latency-mode CTAs still waiting for a hand-over stop waiting
+cudaError_t launch_set_tail_flag(const BatchDev &B, cudaStream_t st) {
+  k_set_tail_flag<<<1, 1, 0, st>>>(B.sched);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_vec_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,

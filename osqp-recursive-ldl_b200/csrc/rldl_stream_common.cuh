@@ -70,13 +70,13 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ int ld_volatile(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
 
 __device__ __forceinline__ void sched_push(const BatchDev &B, int b, int inst) {
-  const int idx = atomicAdd(B.sched + 2 + kSchedBuckets + b, 1);
+  const int idx = atomicAdd(B.sched + 2 + kSchedRings + b, 1);
   int *sl = B.sched_slots + (size_t)b * B.batch + (idx % B.batch);
   while (atomicCAS(sl, -1, inst) != -1) __nanosleep(32);
 }
 __device__ __forceinline__ int sched_pop(const BatchDev &B, int b) {
   int *head = B.sched + 2 + b;
-  const int *tail = B.sched + 2 + kSchedBuckets + b;
+  const int *tail = B.sched + 2 + kSchedRings + b;
   for (;;) {
     const int h = ld_volatile(head), t = ld_volatile(tail);
     if (h >= t) return -1;
@@ -88,6 +88,19 @@ __device__ __forceinline__ int sched_pop(const BatchDev &B, int b) {
     }
   }
 }
+__device__ __forceinline__ bool sched_ring_nonempty(const BatchDev &B, int b) {
+  return ld_volatile(B.sched + 2 + kSchedRings + b) > ld_volatile(B.sched + 2 + b);
+}
+// the most urgent suspended instance (thread-level; -1 if every bucket is empty)
+__device__ __forceinline__ int sched_pop_best(const BatchDev &B) {
+  for (int b = kSchedBuckets - 1; b >= 0; b--)
+    while (sched_ring_nonempty(B, b)) {
+      const int i = sched_pop(B, b);
+      if (i >= 0) return i;
+    }
+  return -1;
+}
+
 // urgency of an instance at a termination check: how far it is from its tolerances (auxil.c:259-288, 323-362),
 // floor(2*log2(max(r_p/eps_p, r_d/eps_d))) clamped to the bucket range
 __device__ __forceinline__ int urgency_bucket(const SettingsDev &S, const Resid &R) {

@@ -10,7 +10,7 @@ import pytest
 
 import rldl_b200 as R
 import updates_script as US
-from common import gpu_settings, settings_dict, problem, compare
+from common import gpu_settings, settings_dict, problem, compare, ref_run
 from oracle import rldl_oracle as O
 from rldl_b200 import mpc
 
