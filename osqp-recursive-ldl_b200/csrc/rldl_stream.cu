@@ -595,7 +595,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         cur = nxt;
       }
       // ---- iteration epilogue: residuals, termination, rho adaptation (osqp.c:426-519, 524-567) ----
-      bool done = false, rho_changed = false;
+      bool done = false, rho_changed = false, at_tail = false;
       int status = -10;
       double obj = 0.0, rho_new = rho_in;
       Resid R = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -674,13 +674,13 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         if (gl == 0) { B.iter[inst] = iter; B.status[inst] = kStatusParkedRho; }
         drain();
         have = start_next();
-      } else if (can_check && (tail_reached() || retiring())) {
+      } else if (can_check && ((at_tail = tail_reached()) || retiring())) {
         // suspended as it stands (status stays OSQP_UNSOLVED) into its priority bucket: the latency-mode kernel
         // resumes the suspended instances most-unconverged first (the longest remaining chains start first);
         // a retiring SM's instances are picked up by the other groups like any suspended instance
         if (gl == 0) {
           B.iter[inst] = iter;
-          if (k_l > 0 && tail_reached()) atomicExch(B.sched + kSchedTailFlag, 1);
+          if (k_l > 0 && at_tail) atomicExch(B.sched + kSchedTailFlag, 1);
         }
         __threadfence();
         __syncwarp(gm);
@@ -688,7 +688,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         drain();
         have = false;
       } else {
-        bool yield = false;
+        bool yield = false, handed = false;
         int myb = 0;
         if (sched_on && can_check) {
           // urgency of this instance: distance from its tolerances (auxil.c:259-288, 323-362)
@@ -714,15 +714,16 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
               if (gl == 0) sched_push(B, kSchedLQ, inst);
               drain();
               have = start_next();
-              __syncwarp();
-              continue;
+              handed = true;
             }
           }
-          int fresh_left = 0;
-          if (gl == 0) fresh_left = ld_volatile(B.sched) < B.batch;
-          fresh_left = __shfl_sync(gm, fresh_left, 0, G);
-          if (fresh_left) yield = iter >= s0;
-          else yield = sched_best<G>(B, gl, gm) > myb;
+          if (!handed) {
+            int fresh_left = 0;
+            if (gl == 0) fresh_left = ld_volatile(B.sched) < B.batch;
+            fresh_left = __shfl_sync(gm, fresh_left, 0, G);
+            if (fresh_left) yield = iter >= s0;
+            else yield = sched_best<G>(B, gl, gm) > myb;
+          }
         }
         if (yield) {
           if (gl == 0) B.iter[inst] = iter;

@@ -14,7 +14,9 @@ N = cfg["N"]
 q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch, bench.SEED), N)
 s = dict(bench.SETTINGS); s["max_iter"] = mi
 gb = R.Batch(mdl, N, N, q, l, u, R.default_settings(**s))
+gb.set_tuning(**{knob: vals[0]})
 gb.solve()
+print('first solve done', flush=True)
 for rep in range(2):
     for v in vals:
         gb.set_tuning(**{knob: v})
