@@ -163,6 +163,168 @@ def main_reference(args):
 
 
 # ----------------------------------------------------------------------------
+# the other BASELINE.json configs (parity-test cases), measured once per bench run at N = 1 outside the
+# timed region: GPU throughput through the C ABI, the unmodified reference on a sample, and mismatch counts
+# ----------------------------------------------------------------------------
+def _ref(spec):
+    from oracle import ref_py
+    return ref_py.run_isolated(spec)
+
+
+def scenario_c1_scalar():
+    """configs[0]: one MPC QP (nx=4, nu=2, N=20) through the scalar entry points osqp_setup_recursive +
+    osqp_solve_recursive — batch-of-one latency on the GPU next to the reference on one host core."""
+    import ctypes as C
+    import rldl_b200 as R
+    from rldl_b200 import mpc
+    cfg = mpc.CONFIGS["C1"]
+    mdl, N = mpc.make_model(cfg), cfg["N"]
+    q, l, u = mdl.vectors(mpc.sample_x0(mdl, 1, SEED), N, N + 1)
+    L, DP = R.lib(), C.POINTER(C.c_double)
+    t_setup, t_solve, info = [], [], None
+    for _ in range(5):
+        sm = R.StageModel(mdl)
+        d = sm.data
+        qq, ll, uu = (np.ascontiguousarray(v[0]) for v in (q, l, u))
+        d.data.n, d.data.m = len(qq), len(ll)
+        d.data.q, d.data.l, d.data.u = (v.ctypes.data_as(DP) for v in (qq, ll, uu))
+        w = C.POINTER(R.OSQPWorkspace)()
+        st = R.default_settings(**SETTINGS)
+        t0 = time.perf_counter()
+        assert L.osqp_setup_recursive(C.byref(w), C.byref(d), C.byref(st), N + 1, N, mdl.nx, mdl.nu, mdl.ny, mdl.nt) == 0
+        t1 = time.perf_counter()
+        assert L.osqp_solve_recursive(w) == 0
+        t2 = time.perf_counter()
+        info = w.contents.info.contents
+        it, stv, obj = int(info.iter), int(info.status_val), float(info.obj_val)
+        L.osqp_cleanup(w)
+        t_setup.append(t1 - t0); t_solve.append(t2 - t1)
+    res = _ref(dict(model=mdl, N=N, Nmax=N + 1, q=q, l=l, u=u, settings=SETTINGS, path="recursive", nthreads=1,
+                    ops=[("solve",), ("get",)]))
+    r = res[1]
+    return {"config": "C1: nx=4 nu=2 N=20, one instance, scalar API (osqp_setup_recursive + osqp_solve_recursive)",
+            "gpu_setup_ms": 1e3 * min(t_setup), "gpu_solve_ms": 1e3 * min(t_solve),
+            "reference_setup_ms": 1e3 * float(r["setup_time"][0]), "reference_solve_ms": 1e3 * float(r["solve_time"][0]),
+            "iterations": it, "parity": {"compared": 1, "status_mismatch": int(stv != r["status"][0]),
+                                         "iter_mismatch": int(it != r["iter"][0]),
+                                         "max_rel_obj": abs(obj - r["obj"][0]) / max(abs(r["obj"][0]), 1e-12)},
+            "note": "a batch of one is launch- and latency-bound on a GPU (one 512-thread CTA); the path is built for batches"}
+
+
+def scenario_c2():
+    import rldl_b200 as R
+    from rldl_b200 import mpc
+    cfg = mpc.CONFIGS["C2"]
+    mdl, N, batch = mpc.make_model(cfg), cfg["N"], cfg["batch"]
+    x0 = mpc.sample_x0(mdl, batch, SEED)
+    q, l, u = mdl.vectors(x0, N)
+    gb = R.Batch(mdl, N, N, q, l, u, R.default_settings(**SETTINGS))
+    ts = []
+    for _ in range(5):
+        gb.refactor(); gb.solve(); ts.append(sum(gb.last_times()))
+    out = gb.get(); n, m, _, _ = gb.dims(); gb.free()
+    q1, l1, u1 = mdl.vectors(x0, N, N + 1)
+    res = _ref(dict(model=mdl, N=N, Nmax=N + 1, q=q1, l=l1, u=u1, settings=SETTINGS, path="recursive",
+                    ops=[("solve",), ("get",)]))
+    tt = res[-1]
+    return {"config": "C2: nx=4 nu=2 N=20, batch 1024, cold (factor + solve), device-resident",
+            "gpu_ms": min(ts), "gpu_solves_per_s": batch / (min(ts) * 1e-3), "mean_iter": float(out["iter"].mean()),
+            "reference_solves_per_s": batch / (tt["setup_wall"] + tt["solve_wall"][0]), "reference_threads": tt["nthreads"],
+            "parity": parity_counts(res[1], out, n, m)}
+
+
+def scenario_c3(sample=64):
+    import rldl_b200 as R
+    from rldl_b200 import mpc
+    cfg = mpc.CONFIGS["C3"]
+    mdl, N0, batch, T = mpc.make_model(cfg), cfg["N"], cfg["batch"], 20
+    nx, nu, ny = mdl.nx, mdl.nu, mdl.ny
+    x0 = mpc.sample_x0(mdl, batch, 4321)
+    q, l, u = mdl.vectors(x0, N0, N0 + 1)
+    idx = np.sort(np.random.default_rng(11).choice(batch, sample, replace=False))
+    st = dict(SETTINGS); st["warm_start"] = 1
+    gb = R.Batch(mdl, N0, N0 + 1, q, l, u, R.default_settings(**st))
+    N, xcur, steps, fb, k_ms = N0, x0.copy(), [], [], 0.0
+    t0 = time.perf_counter()
+    for t in range(T):
+        assert gb.solve() == 0
+        k_ms += gb.last_times()[1]
+        r = gb.get()
+        n, m, _, _ = gb.dims()
+        steps.append(dict(n=n, m=m, status=r["status"][idx].copy(), iter=r["iter"][idx].copy(), obj=r["obj"][idx].copy(),
+                          x=r["x"][idx, :n].copy(), y=r["y"][idx, :m].copy()))
+        if t + 1 == T:
+            break
+        u0 = r["x"][:, :nu]
+        fb.append(u0[idx].copy())
+        xcur = xcur @ mdl.A.T + u0 @ mdl.B.T
+        assert gb.warm_start_shift() == 0
+        Nnew = N - 1 if (t + 1) % 5 == 0 else N
+        if t + 2 == T:
+            Nnew = N0
+        if Nnew != N:
+            assert gb.update_horizon(Nnew) == 0
+            N = Nnew
+        dyn0 = np.ascontiguousarray(-(xcur @ mdl.A.T))
+        assert gb.partial_update_bounds(ny, ny + nx, dyn0, dyn0) == 0
+    wall = time.perf_counter() - t0
+    gb.free()
+    t0 = time.perf_counter()
+    ref = _ref(dict(model=mdl, N=N0, Nmax=N0 + 1, q=q[idx], l=l[idx], u=u[idx], settings=st, path="recursive",
+                    ops=[("receding", x0[idx], T, 5, fb)]))[0]
+    ref_wall = time.perf_counter() - t0
+    tot = {"compared": 0, "status_mismatch": 0, "iter_mismatch": 0, "max_rel_x": 0.0, "max_rel_y": 0.0, "max_rel_obj": 0.0}
+    for s, rr in zip(steps, ref):
+        pc = parity_counts(rr, s, s["n"], s["m"])
+        for k in ("compared", "status_mismatch", "iter_mismatch"):
+            tot[k] += pc[k]
+        for k in ("max_rel_x", "max_rel_y", "max_rel_obj"):
+            tot[k] = max(tot[k], pc[k])
+    return {"config": f"C3: quadcopter nx=12 nu=4 N=50, batch {batch}, receding horizon T={T}: device-shifted warm start, "
+                      f"stage-0 bound update, horizon shrink every 5th step + grow back",
+            "gpu_wall_s": wall, "gpu_solves_per_s": batch * T / wall, "admm_kernel_ms_total": k_ms,
+            "note": "GPU wall clock includes the host closed loop (x, y D2H every step, numpy plant update, bound H2D)",
+            "reference_solves_per_s": sample * T / ref_wall,
+            "reference_note": f"{sample} sampled instances replayed with the GPU's feedback; wall clock includes process start",
+            "parity": tot}
+
+
+def scenario_c4(sample=128):
+    import rldl_b200 as R
+    from rldl_b200 import mpc
+    cfg = mpc.CONFIGS["C4"]
+    mdl, N, batch = mpc.make_model(cfg), cfg["N"], cfg["batch"]
+    q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch, SEED), N)
+    rho = np.where(np.arange(batch) % 2 == 0, 1e-3, 10.0)
+    st = dict(SETTINGS); st.update(adaptive_rho=1, adaptive_rho_interval=25, adaptive_rho_tolerance=1.5)
+    ts = []
+    for _ in range(3):
+        gb = R.Batch(mdl, N, N, q, l, u, R.default_settings(**st), rho=rho)
+        t0 = time.perf_counter(); assert gb.solve() == 0; ts.append(time.perf_counter() - t0)
+        out = gb.get(); n, m, _, _ = gb.dims(); gb.free()
+    res = _ref(dict(model=mdl, N=N, Nmax=N, q=q[:sample], l=l[:sample], u=u[:sample], rho=rho[:sample], settings=st,
+                    path="stock", ops=[("solve",), ("get",)]))
+    tt = res[-1]
+    pc = parity_counts(res[1], {k: v[:sample] for k, v in out.items()}, n, m)
+    pc["rho_updates_mismatch"] = int((res[1]["rho_updates"] != out["rho_updates"][:sample]).sum())
+    return {"config": f"C4: nx=8 nu=3 N=100, batch {batch}, adaptive rho (interval 25, tolerance 1.5, rho0 in {{1e-3, 10}})",
+            "gpu_ms": 1e3 * min(ts), "gpu_solves_per_s": batch / min(ts), "mean_iter": float(out["iter"].mean()),
+            "mean_rho_updates": float(out["rho_updates"].mean()),
+            "reference_solves_per_s": sample / tt["solve_wall"][0], "reference_threads": tt["nthreads"],
+            "reference_path": "stock (rho updates segfault on the reference's recursive workspace, SURVEY F1)", "parity": pc}
+
+
+def run_scenarios():
+    out = {}
+    for name, fn in (("C1", scenario_c1_scalar), ("C2", scenario_c2), ("C3", scenario_c3), ("C4", scenario_c4)):
+        try:
+            out[name] = fn()
+        except Exception as e:  # a scenario must never take the bench line down
+            out[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    return out
+
+
+# ----------------------------------------------------------------------------
 # clocks sampling (B200_PROFILING.md recipe)
 # ----------------------------------------------------------------------------
 class ClockSampler:
@@ -336,6 +498,11 @@ def main_b200(args):
     # = sum over this rank's instances of iterations x bytes/iteration, over the
     # kernel's own CUDA-event duration measured inside the library on its launching stream
     admm_bytes, factor_bytes, _ = gb.counters()
+    nx_, nu_ = cfg["nx"], cfg["nu"]
+    a_ = nx_ + nu_
+    # multiply-adds of one stage of the recursion with block-diagonal pivots: sweep of X^xx and X^uu,
+    # W = Xinv F', S = F W, sweep of S; 2 flop each
+    gb_factor_flops = 2.0 * (N * ((nx_ ** 3 + nu_ ** 3) + (nx_ ** 3 + nu_ * nu_ * nx_) + a_ * nx_ * nx_ + nx_ ** 3) + nx_ ** 3 + nu_ ** 3)
     f_ms = float(np.mean([p[0] for p in parts])); s_ms = float(np.mean([p[1] for p in parts]))
     peaks = {}
     try:
@@ -344,24 +511,32 @@ def main_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = iter_sum * admm_bytes / (s_ms * 1e-3) / 1e9
-    # DRAM traffic of the same kernel from the committed ncu --set full capture
-    # (profiles/r01_stream_v7_ncu_full_uniform_c5_batch16384.txt: dram read 372.42 GB + write 66.51 GB for
-    # 1.6384 M instance-iterations x 235 872 algorithmic bytes with the block-diagonal pivot records;
-    # r01_stream_v5_...: 432.75 + 66.61 GB x 275 040 bytes with the full a x a block), scaled by the algorithmic
-    # bytes of this launch
+    # DRAM traffic of the same kernel: dram__bytes_read + dram__bytes_write of its committed `ncu --set full`
+    # capture at uniform load (profiles/r02_stream_ncu_full_uniform_c5_batch16384.txt: 383.68 + 65.95 GB for
+    # 1.6384 M instance-iterations x 235 872 algorithmic bytes = x1.163), scaled to this launch.  Only quoted for
+    # the shape and record layout the capture was taken on; null otherwise.
+    traffic = None
+    traffic_source = "no ncu capture for this shape / record layout"
     if abs(admm_bytes - 235872.0) < 1.0:
-        traffic_ratio = (372.419525e9 + 66.513596e9) / (16384 * 100 * 235872.0)
-    else:
-        traffic_ratio = (432.746847e9 + 66.611270e9) / (16384 * 100 * 275040.0)
+        traffic_ratio = (383.681287e9 + 65.951344e9) / (16384 * 100 * 235872.0)
+        traffic = traffic_ratio * iter_sum * admm_bytes
+        traffic_source = ("ncu dram__bytes_read+write of this kernel at batch 16384, uniform 100 iterations "
+                          "(x%.3f of algorithmic), scaled by this launch's instance-iterations" % traffic_ratio)
+    # FP64 peak of the box: tools/micro/dfma.cu, measured on this pool's B200 (profiles/r02_dfma_peak_b200.txt)
+    fp64_peak = 33988.7e9
+    flops_factor = float(gb_factor_flops) * mine
     roof = {"bound": "hbm", "kernel": "k_admm_stream (fused KKT solve + ADMM step + termination, whole solve loop; its tail is finished by k_admm_cta inside the same timed region)",
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
-            "traffic": traffic_ratio * iter_sum * admm_bytes,
-            "traffic_source": "ncu dram__bytes_read+write of this kernel at batch 16384, uniform 100 iterations (x%.3f of algorithmic), scaled" % traffic_ratio,
+            "traffic": traffic, "traffic_source": traffic_source,
             "launch_ms": s_ms, "algorithmic_bytes_per_launch": iter_sum * admm_bytes,
-            "factor_kernel": {"kernel": "k_factor_stream (stage recursion, ~10 flop/B: shared-memory data pipe 70 %, FP64 pipe 27 %, profiles/r01_factor_v6_ncu_full_c5_batch16384.txt)",
+            "note": "iterations finished by the latency-mode kernel (factor resident in shared memory) are counted at the streaming kernel's bytes; they are about 1 % of a single-GPU step",
+            "factor_kernel": {"kernel": "k_factor_stream (stage recursion, FP64 / shared-memory bound: ~7 flop/B; profiles/r02_factor_ncu_full_c5_batch16384.txt)",
                               "launch_ms": f_ms, "achieved": factor_bytes / (f_ms * 1e-3) / 1e9,
-                              "frac": factor_bytes / (f_ms * 1e-3) / 1e9 / peak}}
+                              "frac": factor_bytes / (f_ms * 1e-3) / 1e9 / peak,
+                              "fp64_gflops": flops_factor / (f_ms * 1e-3) / 1e9,
+                              "fp64_peak_gflops": fp64_peak / 1e9, "fp64_peak_source": "tools/micro/dfma.cu on B200 (profiles/r02_dfma_peak_b200.txt)",
+                              "fp64_frac": flops_factor / (f_ms * 1e-3) / fp64_peak}}
     mean_iter = allsum(iter_sum) / total
     gb.free()
 
@@ -390,6 +565,8 @@ def main_b200(args):
                                               f"each, {thr} pthreads, {secs:.2f} s wall, "
                                               f"mean {float(ref['iter'].mean()):.0f} ADMM iterations"}
             line["parity"] = parity_counts(ref, gpu, n_act, m_act)
+            if not args.no_scenarios:
+                line["scenarios"] = run_scenarios()
         print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
@@ -405,6 +582,7 @@ def main():
     ap.add_argument("--workload", default="C5")
     ap.add_argument("--batch", type=int, default=0, help="override the total batch (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-scenarios", action="store_true", help="skip the C1-C4 scenario measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)

@@ -470,6 +470,10 @@ c_int rldl_batch_select_kernel(RLDLBatch *b, c_int which);
  *                 (default 6 x lat_below)
  * value = -1 restores the default.  Returns 0, or 1 for an unknown name / invalid value. */
 c_int rldl_batch_set_tuning(RLDLBatch *b, const char *name, c_int value);
+/* statistics of the concurrent latency-mode lane in the last streaming launch (6 values): instances handed over,
+ * lane CTAs that left at once (resident before the streaming kernel had started), instances a lane CTA took from
+ * the hand-over ring / from the priority buckets, instances suspended by retiring SMs, lane CTA exits */
+c_int rldl_batch_lane_stats(RLDLBatch *b, c_int *stats);
 /* the CUDA stream (cudaStream_t) every launch and copy of this handle is issued on, so a
  * caller can bracket calls with its own events on the launching stream */
 void *rldl_batch_stream(const RLDLBatch *b);

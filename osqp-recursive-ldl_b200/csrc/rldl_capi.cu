@@ -868,6 +868,14 @@ c_int rldl_batch_set_tuning(RLDLBatch *h, const char *name, c_int value) {
   else return 1;
   return 0;
 }
+c_int rldl_batch_lane_stats(RLDLBatch *h, c_int *stats) {
+  HB(h);
+  int v[6] = {0, 0, 0, 0, 0, 0};
+  if (cudaSetDevice(h->b->device) != cudaSuccess ||
+      cudaMemcpy(v, h->b->D.sched + rldl::kSchedStats, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return 1;
+  for (int i = 0; i < 6; i++) stats[i] = v[i];
+  return 0;
+}
 void *rldl_batch_stream(const RLDLBatch *h) { return (h && h->b) ? (void *)h->b->stream : nullptr; }
 void rldl_batch_free(RLDLBatch *h) {
   if (!h) return;

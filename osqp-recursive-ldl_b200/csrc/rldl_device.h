@@ -110,7 +110,10 @@ constexpr int kSchedT0 = kSchedUnfinished + 2;  // 64-bit %globaltimer value at 
 // concurrent latency-mode lane: latency-mode CTAs waiting for an instance, the urgency bucket an instance
 // must have to be handed over (decaying maximum), streaming CTAs started, "the streaming kernel has hit its tail / ended"
 constexpr int kSchedLWant = kSchedT0 + 2, kSchedTop = kSchedT0 + 3, kSchedStarted = kSchedT0 + 4, kSchedTailFlag = kSchedT0 + 5;
-constexpr int kSchedCounters = kSchedT0 + 6;
+// lane statistics of the last streaming launch: hand-overs, lane CTAs that left early, instances a lane CTA took
+// from the hand-over ring / from the buckets, SMs that retired
+constexpr int kSchedStats = kSchedT0 + 6;
+constexpr int kSchedCounters = kSchedStats + 6;
 
 constexpr int STATUS_FACTOR_ERROR = -7;  // reported as OSQP_NON_CVX
 // device-internal: instance parked by an adaptive-rho update until its factor has been refreshed (never

@@ -284,8 +284,10 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     // otherwise: the fresh counter, with the same resume rules as the streaming kernel.
     if (threadIdx.x == 0 && claim_mode) {
       int i = -1;
+      bool from_ring = true;
       if (claim_mode == 2 && ld_volatile(B.sched + kSchedStarted) < stream_ctas && !ld_volatile(B.sched + kSchedTailFlag)) {
         i = -1;
+        atomicAdd(B.sched + kSchedStats + 1, 1);
       } else {
         if (sched_ring_nonempty(B, kSchedLQ)) i = sched_pop(B, kSchedLQ);
         if (i < 0 && claim_mode == 2 && !ld_volatile(B.sched + kSchedTailFlag)) {
@@ -306,10 +308,11 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         }
         if (i < 0 && (claim_mode == 1 || ld_volatile(B.sched + kSchedTailFlag))) {
           if (sched_ring_nonempty(B, kSchedLQ)) i = sched_pop(B, kSchedLQ);
-          if (i < 0) i = sched_pop_best(B);
+          if (i < 0) { i = sched_pop_best(B); from_ring = false; }
         }
       }
       if (i >= 0) __threadfence();  // order the loads of the iterates after the hand-over
+      if (claim_mode == 2) atomicAdd(B.sched + kSchedStats + (i >= 0 ? (from_ring ? 2 : 3) : 5), 1);
       ctl[0] = i;
     } else if (threadIdx.x == 0) {
       int i = -1;

@@ -681,6 +681,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         if (gl == 0) {
           B.iter[inst] = iter;
           if (k_l > 0 && at_tail) atomicExch(B.sched + kSchedTailFlag, 1);
+          if (k_l > 0 && !at_tail) atomicAdd(B.sched + kSchedStats + 4, 1);  // instances suspended by retiring SMs
         }
         __threadfence();
         __syncwarp(gm);
@@ -711,7 +712,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
               if (gl == 0) B.iter[inst] = iter;
               __threadfence();  // this lane's iterate stores precede the hand-over
               __syncwarp(gm);
-              if (gl == 0) sched_push(B, kSchedLQ, inst);
+              if (gl == 0) { sched_push(B, kSchedLQ, inst); atomicAdd(B.sched + kSchedStats, 1); }
               drain();
               have = start_next();
               handed = true;
@@ -779,7 +780,7 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   // concurrent latency-mode lane: waiting CTAs 0, hand-over threshold at the top bucket (stored inverted), CTAs
   // started 0, tail flag 0
   static_assert(kSchedTop == kSchedLWant + 1 && kSchedStarted == kSchedLWant + 2 && kSchedTailFlag == kSchedLWant + 3, "layout");
-  e = cudaMemsetAsync(B.sched + kSchedLWant, 0, 4 * sizeof(int), st);
+  e = cudaMemsetAsync(B.sched + kSchedLWant, 0, (4 + 6) * sizeof(int), st);
   if (e != cudaSuccess) return e;
   if (reset_done) {  // the concurrent latency-mode launch waits for this, not for the kernel
     e = cudaEventRecord(reset_done, st);

@@ -194,8 +194,10 @@ def test_solve_to_host_delivers_what_get_returns(name, batch, below, kernel, pin
     want = gb.get()
     n, m, _, _ = gb.dims()
     gb.free()
-    assert want["status"][1] in (-3, 3) and (want["status"] == 1).sum() >= batch - 2
+    assert want["status"][1] in (-3, 3, -2) and (want["status"] == 1).sum() >= batch - 2
+    assert name != "C1" or want["status"][1] == -3
     for k in ("iter", "status", "obj", "pri_res", "dua_res", "rho_updates", "rho_estimate"):
         assert np.array_equal(out[k], want[k]), k
     assert np.array_equal(out["x"][:, :n], want["x"][:, :n]) and np.array_equal(out["y"][:, :m], want["y"][:, :m])
-    assert (out["x"][1, :n] == float(0x7fc00000)).all()
+    if want["status"][1] in (-3, 3):
+        assert (out["x"][1, :n] == float(0x7fc00000)).all()

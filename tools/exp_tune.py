@@ -25,5 +25,5 @@ for rep in range(2):
             gb.refactor(); gb.solve(); ts.append(gb.last_times())
         it = gb.get()["iter"]
         print(f"{knob}={v} batch {batch} max_iter {mi}: factor ms {min(t[0] for t in ts):.2f} solve ms {[round(t[1], 1) for t in ts]} "
-              f"inst-iter/us {it.sum() / min(t[1] for t in ts) / 1e3:.2f}", flush=True)
+              f"inst-iter/us {it.sum() / min(t[1] for t in ts) / 1e3:.2f} lane {gb.lane_stats()}", flush=True)
 gb.free()
