@@ -474,6 +474,10 @@ c_int rldl_batch_set_tuning(RLDLBatch *b, const char *name, c_int value);
  * lane CTAs that left at once (resident before the streaming kernel had started), instances a lane CTA took from
  * the hand-over ring / from the priority buckets, instances suspended by retiring SMs, lane CTA exits */
 c_int rldl_batch_lane_stats(RLDLBatch *b, c_int *stats);
+/* finish-time trace of the last solve (after rldl_batch_set_tuning(b, "trace", 1)): per instance, milliseconds
+ * from the start of the solve to the moment it finished + 1e6 x the engine that finished it (1 streaming kernel,
+ * 2 latency-mode kernel).  Returns 1 if tracing was never switched on. */
+c_int rldl_batch_get_trace(RLDLBatch *b, c_float *t);
 /* the CUDA stream (cudaStream_t) every launch and copy of this handle is issued on, so a
  * caller can bracket calls with its own events on the launching stream */
 void *rldl_batch_stream(const RLDLBatch *b);

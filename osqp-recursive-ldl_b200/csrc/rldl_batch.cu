@@ -372,7 +372,7 @@ Batch::~Batch() {
   cudaSetDevice(device);
   double *dp[] = {D.sD, D.sE, D.sC, D.q, D.l, D.u, D.rho_vec, D.x, D.z, D.y, D.dx, D.dy, D.Xinv, D.Sinv, D.yk, D.sk,
                   D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec, d_l_alt, d_u_alt, d_latT,
-                  d_polX, d_polS, d_polrho, d_polb, d_pols, d_polr};
+                  d_polX, d_polS, d_polrho, d_polb, d_pols, d_polr, d_trace};
   for (double *p : dp) if (p) cudaFree(p);
   if (D.iter) cudaFree(D.iter);
   int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx, D.sched, D.sched_slots, d_polstat};
@@ -464,6 +464,8 @@ c_int Batch::solve() {
   if (settings.time_limit > 0.0) {
     const double left = settings.time_limit - time_spent_before_solve;
     S.time_limit_ns = left > 1e-9 ? (long long)(left * 1e9) : 1;
+  }
+  if (settings.time_limit > 0.0 || D.trace) {
     CK(launch_mark_time(D, stream));
     launches++;
   }
@@ -621,6 +623,18 @@ c_int Batch::rescale() {
   if (!scaled()) return 0;
   CK(launch_ruiz(M, D, (int)settings.scaling, stream));
   launches++;
+  return 0;
+}
+
+c_int Batch::set_trace(bool on) {
+  if (on && !d_trace) CK(dalloc(&d_trace, (size_t)batch));
+  D.trace = on ? d_trace : nullptr;
+  return 0;
+}
+c_int Batch::get_trace(c_float *t) {
+  if (!d_trace) return 1;
+  CK(cudaSetDevice(device));
+  CK(cudaMemcpy(t, d_trace, (size_t)batch * sizeof(double), cudaMemcpyDeviceToHost));
   return 0;
 }
 

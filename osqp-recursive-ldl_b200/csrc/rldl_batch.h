@@ -18,6 +18,9 @@ struct Batch {
   // concurrent latency-mode lane: lat_lane CTAs of the latency-mode kernel run beside the streaming kernel on the SMs
   // its CTAs vacate once at most lat_retire_below instances are unfinished (0 = 6 x lat_below); lat_lane = 0: off
   int lat_lane = 8, lat_retire_below = 0;
+  double *d_trace = nullptr;  // optional per-instance finish-time trace
+  c_int set_trace(bool on);
+  c_int get_trace(c_float *t);
   cudaStream_t stream2 = nullptr;  // the lane's stream (lower priority than `stream`)
   cudaEvent_t ev_reset = nullptr, ev_lane = nullptr;
   bool streaming = false;  // shapes the streaming kernels cover (rldl_stream.cu)

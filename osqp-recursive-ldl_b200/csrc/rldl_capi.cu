@@ -863,11 +863,13 @@ c_int rldl_batch_set_tuning(RLDLBatch *h, const char *name, c_int value) {
   else if (!strcmp(name, "sched_s0")) B->tune.sched_s0 = (int)value;
   else if (!strcmp(name, "ctas_per_sm")) B->tune.ctas_per_sm = (int)value < 0 ? 0 : (int)value;
   else if (!strcmp(name, "l2_hints")) B->tune.l2_hints = (int)value < 0 ? 1 : (int)value;
+  else if (!strcmp(name, "trace")) return B->set_trace(value > 0);
   else if (!strcmp(name, "lat_lane")) B->lat_lane = (int)value < 0 ? 8 : (int)value;
   else if (!strcmp(name, "lat_retire_below")) B->lat_retire_below = (int)value < 0 ? 0 : (int)value;
   else return 1;
   return 0;
 }
+c_int rldl_batch_get_trace(RLDLBatch *h, c_float *t) { HB(h); return t ? h->b->get_trace(t) : 1; }
 c_int rldl_batch_lane_stats(RLDLBatch *h, c_int *stats) {
   HB(h);
   int v[6] = {0, 0, 0, 0, 0, 0};

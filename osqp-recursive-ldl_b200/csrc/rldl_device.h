@@ -81,6 +81,9 @@ struct BatchDev {
   // the rest of the solve instead of after it.  Layout as rldl_batch_get_solution / rldl_batch_get_info.
   double *hx, *hy, *h_obj, *h_pri, *h_dua, *h_rho_est;
   long long *h_iter, *h_status, *h_rho_updates;
+  // optional trace (rldl_batch_set_tuning "trace"): per instance, milliseconds from the start of the solve to the
+  // moment the instance finished, plus 1e6 x the engine that finished it (1 streaming, 2 latency-mode, 3 runtime-shape)
+  double *trace;
   // Streaming layout (rldl_stream.cu): one record per (instance, stage), RS doubles:
   //   [ q_k (qa) | Xinv_k packed (PX) | Sinv_k packed (PS) | row classes (kClsWords) | l_k (bb) | u_k (bb) ]
   // packed = lower triangle, column-major, of the a x a / nx x nx symmetric pivot inverse;

@@ -585,6 +585,14 @@ __device__ __forceinline__ bool time_check_due(const SettingsDev &S, int iter, b
   return S.time_limit_ns > 0 && (can_check || (!S.check_termination && iter % 25 == 0));
 }
 
+__device__ __forceinline__ void trace_finish(const BatchDev &B, int inst, int engine) {
+  if (!B.trace) return;
+  unsigned long long now;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+  const unsigned long long t0 = *reinterpret_cast<const volatile unsigned long long *>(B.sched + kSchedT0);
+  B.trace[inst] = 1e-6 * (double)(long long)(now - t0) + 1e6 * engine;
+}
+
 // store_solution (auxil.c:527-563) + the info scalars of a finished instance, written straight to the caller's pinned
 // host arrays (BatchDev::hx ...) by `nthr` cooperating threads (tid = 0 .. nthr-1) that can all see the final
 // iterates in global memory.  No-op unless the solve was started through rldl_batch_solve_to_host.

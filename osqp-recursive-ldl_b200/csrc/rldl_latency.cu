@@ -826,6 +826,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
             B.dua[inst] = R.dua;
             B.rho_est[inst] = rho_est;
             atomicSub(B.sched + kSchedUnfinished, 1);
+            trace_finish(B, inst, 2);
           }
         } else if (rho_changed) {
           // parked for the batched re-factorisation, resumed afterwards

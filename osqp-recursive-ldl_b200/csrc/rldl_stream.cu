@@ -661,6 +661,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           B.dua[inst] = R.dua;
           B.rho_est[inst] = rho_est;
           atomicSub(B.sched + kSchedUnfinished, 1);
+          trace_finish(B, inst, 1);
         }
         if (B.h_status) {  // fused solve-and-deliver: this instance's results go to the host now
           __syncwarp(gm);
