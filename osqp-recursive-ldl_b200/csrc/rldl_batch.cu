@@ -309,6 +309,8 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(dalloc(&D.obj, bs)); CK(dalloc(&D.pri, bs)); CK(dalloc(&D.dua, bs)); CK(dalloc(&D.rho_est, bs));
   CK(dalloc(&D.rho_updates, bs)); CK(dalloc(&D.fact_flag, bs));
   CK(dalloc(&B->d_changed, bs));
+  CK(dalloc(&B->d_ratio, bs));
+  D.ratio_prev = B->d_ratio; D.sched_key = 1;
   if (B->scaled()) { CK(dalloc(&D.sD, bs * D.nmax)); CK(dalloc(&D.sE, bs * D.mmax)); CK(dalloc(&D.sC, bs)); }
   CK(dalloc(&D.sched, kSchedCounters));
   rc = B->configure_stream();
@@ -372,7 +374,7 @@ Batch::~Batch() {
   cudaSetDevice(device);
   double *dp[] = {D.sD, D.sE, D.sC, D.q, D.l, D.u, D.rho_vec, D.x, D.z, D.y, D.dx, D.dy, D.Xinv, D.Sinv, D.yk, D.sk,
                   D.rho, D.obj, D.pri, D.dua, D.rho_est, d_mval, d_stage, D.rec, d_l_alt, d_u_alt, d_latT,
-                  d_polX, d_polS, d_polrho, d_polb, d_pols, d_polr, d_trace};
+                  d_polX, d_polS, d_polrho, d_polb, d_pols, d_polr, d_trace, d_ratio};
   for (double *p : dp) if (p) cudaFree(p);
   if (D.iter) cudaFree(D.iter);
   int *ip[] = {D.status, D.rho_updates, D.fact_flag, d_changed, d_midx, D.sched, D.sched_slots, d_polstat};
@@ -496,9 +498,9 @@ c_int Batch::solve() {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     const size_t lat_smem = latency_smem_bytes(M, N);
     const bool lat_ok = lat_below > 0 && lat_smem != (size_t)-1 && lat_smem <= 227 * 1024;
-    const int lane = lat_ok ? std::min(std::max(lat_lane, 0), 32) : 0;
+    const int lane = lat_ok ? std::min(std::max(lat_lane, 0), sms - 8) : 0;
     const size_t t_per_cta = (size_t)latency_t_blocks(Nmax) * nx * (nx + 2);
-    if (lat_ok && !d_latT) CK(cudaMalloc(&d_latT, (size_t)(sms + 32) * t_per_cta * sizeof(double)));
+    if (lat_ok && !d_latT) CK(cudaMalloc(&d_latT, (size_t)(2 * sms) * t_per_cta * sizeof(double)));
     int unfinished = batch, resume = 0;
     CK(cudaMemcpyAsync(D.sched + kSchedUnfinished, &unfinished, sizeof(int), cudaMemcpyHostToDevice, stream));
     for (;;) {
@@ -508,7 +510,8 @@ c_int Batch::solve() {
       if (run_stream) {
         int s_ctas = 0;
         const int retire = lat_retire_below > 0 ? lat_retire_below : 6 * lat_below;
-        CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, lat_ok ? lat_below : 0, tune,
+        const int park = !lat_ok ? 0 : ((run_lane && lane_tail > 0) ? std::min(lat_below, lane_tail) : lat_below);
+        CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, park, tune,
                               run_lane ? lane : 0, retire, run_lane ? ev_reset : nullptr, &s_ctas, stream));
         launches++;
         if (run_lane) {

@@ -16,8 +16,10 @@ struct Batch {
   int lat_below = 1024;    // hand-off threshold: unfinished instances at which the latency-mode kernel takes over (0: never)
   StreamTuning tune;       // launch knobs of the streaming kernel (rldl_batch_set_tuning)
   // concurrent latency-mode lane: lat_lane CTAs of the latency-mode kernel run beside the streaming kernel on the SMs
-  // its CTAs vacate once at most lat_retire_below instances are unfinished (0 = 6 x lat_below); lat_lane = 0: off
-  int lat_lane = 8, lat_retire_below = 0;
+  // its CTAs vacate once at most lat_retire_below instances are unfinished; lane_tail (> 0) replaces lat_below as the
+  // streaming kernel's stop threshold while the lane runs; lat_lane = 0: off
+  int lat_lane = 8, lat_retire_below = 0, lane_tail = 0;  // (0: retire at 6 x lat_below; tail at lat_below)
+  double *d_ratio = nullptr;
   double *d_trace = nullptr;  // optional per-instance finish-time trace
   c_int set_trace(bool on);
   c_int get_trace(c_float *t);

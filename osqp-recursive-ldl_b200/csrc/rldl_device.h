@@ -84,6 +84,11 @@ struct BatchDev {
   // optional trace (rldl_batch_set_tuning "trace"): per instance, milliseconds from the start of the solve to the
   // moment the instance finished, plus 1e6 x the engine that finished it (1 streaming, 2 latency-mode, 3 runtime-shape)
   double *trace;
+  // max(r_p / eps_p, r_d / eps_d) of every instance at its previous termination check in the streaming kernel (0: none
+  // yet): with the current ratio it gives the convergence rate and from it the predicted remaining iterations, the
+  // urgency the device scheduler sorts by
+  double *ratio_prev;
+  int sched_key;  // 0: urgency = log of the distance from the tolerances (round 1); 1: log of the predicted remaining iterations
   // Streaming layout (rldl_stream.cu): one record per (instance, stage), RS doubles:
   //   [ q_k (qa) | Xinv_k packed (PX) | Sinv_k packed (PS) | row classes (kClsWords) | l_k (bb) | u_k (bb) ]
   // packed = lower triangle, column-major, of the a x a / nx x nx symmetric pivot inverse;

@@ -301,7 +301,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
               if (t < kSchedBuckets - 3) atomicCAS(B.sched + kSchedTop, t, t + 1);
             }
           }
-          if (i < 0) {  // leaving without a hand-over: take the announcement back if it is still there
+          if (i < 0 || !from_ring) {  // leaving without a hand-over: take the announcement back if it is still there
             int w = ld_volatile(B.sched + kSchedLWant);
             while (w > 0 && atomicCAS(B.sched + kSchedLWant, w, w - 1) != w) w = ld_volatile(B.sched + kSchedLWant);
           }

@@ -281,11 +281,13 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
   const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
-  // Concurrent latency-mode lane (k_l > 0): towards the end of the launch the CTAs on SMs 0 .. k_l-1 retire and
-  // latency-mode CTAs (k_admm_cta, launched beside this kernel and pending until an SM is free) take those SMs; the
-  // streaming groups hand them their most-unconverged instances, whose chains would otherwise bound the tail.
-  unsigned smid = 0;
+  // Concurrent latency-mode lane (k_l > 0): as the launch runs out of instances the CTAs on SMs 0 .. k_l-1 retire one
+  // SM after the other and latency-mode CTAs (k_admm_cta, launched beside this kernel and pending until an SM is
+  // free) take those SMs; the streaming groups hand them their most-unconverged instances, whose chains would
+  // otherwise bound the tail, and they also resume suspended instances, most-unconverged first.
+  unsigned smid = 0, nsmid = 0;
   asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  asm volatile("mov.u32 %0, %%nsmid;" : "=r"(nsmid));
   if (threadIdx.x == 0 && k_l > 0) atomicAdd(B.sched + kSchedStarted, 1);
 
   // lane constants of the diagonal-packed mat-vecs
@@ -365,6 +367,10 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   auto retiring = [&]() -> bool {  // this SM goes to a latency-mode CTA
     int t = 0;
     if (k_l > 0 && (int)smid < k_l) {
+      // (a progressive variant — one SM given up per 16 unfinished instances, up to 132 lane CTAs — was measured and
+      // rejected: a latency-mode CTA sustains 60 k instance-iterations/s against 127-155 k of a streaming SM, so SMs
+      // given up while the streaming kernel still has work lengthen it by more than the shorter tail returns:
+      // 8 192 instances 190 -> 209 ms, 16 384: 299 -> 334 ms; profiles/r02_i_lane_progressive_trace.txt)
       if (gl == 0) t = ld_volatile(B.sched) >= B.batch && ld_volatile(B.sched + kSchedUnfinished) <= retire_below;
       t = __shfl_sync(gm, t, 0, G);
     }
@@ -435,7 +441,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         for (int i2 = gl; i2 < n; i2 += G) x[i2] = 0.0;
         for (int r = gl; r < m; r += G) { z[r] = 0.0; y[r] = 0.0; }
       }
-      if (gl == 0) B.status[inst] = -10;
+      if (gl == 0) { B.status[inst] = -10; B.ratio_prev[inst] = 0.0; }
       iter = 0;
     } else {
       iter = (int)__ldcg(B.iter + inst);
@@ -686,7 +692,11 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         }
         __threadfence();
         __syncwarp(gm);
-        if (gl == 0) sched_push(B, urgency_bucket(S, R), inst);
+        if (gl == 0) {
+          const double ratio = urgency_ratio(S, R);
+          sched_push(B, urgency_bucket(S, ratio, B.ratio_prev[inst], B.sched_key), inst);
+          B.ratio_prev[inst] = ratio;
+        }
         drain();
         have = false;
       } else {
@@ -694,7 +704,14 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         int myb = 0;
         if (sched_on && can_check) {
           // urgency of this instance: distance from its tolerances (auxil.c:259-288, 323-362)
-          myb = urgency_bucket(S, R);
+          {
+            const double ratio = urgency_ratio(S, R);
+            if (gl == 0) {
+              myb = urgency_bucket(S, ratio, B.ratio_prev[inst], B.sched_key);
+              B.ratio_prev[inst] = ratio;  // (read again only after a hand-over of the instance, behind the fence)
+            }
+            myb = __shfl_sync(gm, myb, 0, G);
+          }
           if (k_l > 0) {
             // hand-over to a waiting latency-mode CTA: only the most-unconverged instances qualify (kSchedTop is a
             // decaying maximum of the buckets seen at the checks; the waiting CTAs lower it until someone qualifies)

@@ -101,13 +101,31 @@ __device__ __forceinline__ int sched_pop_best(const BatchDev &B) {
   return -1;
 }
 
-// urgency of an instance at a termination check: how far it is from its tolerances (auxil.c:259-288, 323-362),
-// floor(2*log2(max(r_p/eps_p, r_d/eps_d))) clamped to the bucket range
-__device__ __forceinline__ int urgency_bucket(const SettingsDev &S, const Resid &R) {
+// Urgency of an instance at a termination check.  `ratio` = how far it is from its tolerances (auxil.c:259-288,
+// 323-362), max(r_p/eps_p, r_d/eps_d).
+//  key 0: floor(2*log2(ratio)) — round 1.
+//  key 1: the predicted number of remaining iterations.  ADMM converges linearly once the active set has settled, so
+//         with the ratio of the previous check, `every` iterations ago, rate = ln(prev/ratio)/every and
+//         remaining = ln(ratio)/rate.  On the recorded residual trajectories of 2 048 C5 instances its rank
+//         correlation with the true remaining count is 0.94-0.99 from iteration 100 on (0.84-0.87 for key 0), and it
+//         names the few 3 000-iteration instances by iteration 200-300, which key 0 does not.  Bucket =
+//         floor(3*log2(remaining / every)), clamped; a first check (no previous ratio) assumes the ratio halves per
+//         check, a ratio that did not fall counts as max_iter.
+__device__ __forceinline__ double urgency_ratio(const SettingsDev &S, const Resid &R) {
   const double ep = S.eps_abs + S.eps_rel * fmax(R.nz, R.nAx);
   const double ed = S.eps_abs + S.eps_rel * fmax(fmax(R.nq, R.nAty), R.nPx);
-  const double ratio = fmax(R.pri / ep, R.dua / ed);
-  return ratio > 1.0 ? min(kSchedBuckets - 1, (int)(2.0 * log2(ratio))) : 0;
+  return fmax(R.pri / ep, R.dua / ed);
+}
+__device__ __forceinline__ int urgency_bucket(const SettingsDev &S, double ratio, double prev, int key) {
+  if (!(ratio > 1.0)) return 0;
+  if (key == 0) return min(kSchedBuckets - 1, (int)(2.0 * log2(ratio)));
+  const double every = S.check_termination > 0 ? (double)S.check_termination : 25.0;
+  double rem;
+  if (!(prev > 0.0)) rem = every * log2(ratio);
+  else if (prev > ratio * 1.0001) rem = every * log(ratio) / log(prev / ratio);
+  else rem = (double)S.max_iter;
+  rem = fmin(rem, (double)S.max_iter);
+  return rem > every ? min(kSchedBuckets - 1, (int)(3.0 * log2(rem / every))) : 0;
 }
 
 __host__ __device__ inline int even_up(int v) { return (v + 1) & ~1; }
