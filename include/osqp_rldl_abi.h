@@ -414,6 +414,17 @@ c_int rldl_batch_refactor(RLDLBatch *b);
 /* one KKT solve per instance: rhs [batch][n+m] (current sizes) is overwritten with
  * [x_tilde ; z_tilde] — the batched form of linsys_solver->solve */
 c_int rldl_batch_kkt_solve(RLDLBatch *b, c_float *rhs);
+/* Allocation-free KKT solve.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as rldl_batch_kkt_solve — rhs [batch][n+m] in, sol [batch][n+m] = [x_tilde ; z_tilde] out (host
+ * arrays, may alias) — but the right-hand sides are staged in a fixed 4 MiB device array inside the library
+ * instead of a cudaMalloc'ed buffer: the call path contains no cudaMalloc / cudaFree.  Limit: batch * (n + m) <=
+ * rldl_batch_max_static_doubles() (524 288); larger calls return 1 with a message and do nothing.  Every call on a
+ * device shares the one array (it keeps the last call's contents; nothing in it needs clearing): calls that overlap
+ * on the same GPU — other handles, other host threads — race and must be serialised by the caller.  Every GPU that
+ * loads the library holds the array until exit. */
+c_int rldl_batch_kkt_solve_static(RLDLBatch *b, const c_float *rhs, c_float *sol);
+c_int rldl_batch_max_static_doubles(void);
 /* Fused solve-and-deliver: rldl_batch_solve + rldl_batch_get_solution + rldl_batch_get_info in one call (array
  * layout as in those two; status_val is required, the others may be NULL).  When every array given is PINNED host
  * memory (cudaHostAlloc / cudaHostRegister), the kernels write each instance's x, y (OSQP_NAN for the statuses

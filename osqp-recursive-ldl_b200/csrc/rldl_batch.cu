@@ -847,6 +847,26 @@ c_int Batch::solve_to_host(c_float *x, c_float *y, c_int *iter, c_int *status, c
   return rc;
 }
 
+// rldl_batch_kkt_solve without any allocation on the call path: the right-hand sides are staged in the library's
+// fixed device scratch (rldl_kernels.cu) instead of the handle's grow-on-demand buffer.  The pivot inverses the
+// kernel reads were allocated at setup.  Returns 1 (and says why) when batch * (n + m) exceeds the scratch.
+c_int Batch::kkt_solve_static(const c_float *rhs, c_float *sol) {
+  CK(cudaSetDevice(device));
+  const int ld = D.n + D.m;
+  const size_t cnt = (size_t)batch * ld;
+  if (cnt > (size_t)kKktStaticDoubles) {
+    fprintf(stderr, "ERROR in rldl_batch_kkt_solve_static: batch * (n + m) = %zu doubles exceeds the fixed scratch of %d "
+                    "doubles; use rldl_batch_kkt_solve\n", cnt, kKktStaticDoubles);
+    return 1;
+  }
+  c_int rc = ensure_unpacked();  // kernel launches only (the unpacked factor buffers exist since setup)
+  if (rc) return rc;
+  CK(launch_kkt_solve_static(M, D, S, rhs, sol, cnt, ld, stream));
+  launches++;
+  CK(cudaStreamSynchronize(stream));
+  return 0;
+}
+
 static bool no_solution(int st) {
   return st == OSQP_PRIMAL_INFEASIBLE || st == OSQP_PRIMAL_INFEASIBLE_INACCURATE ||
          st == OSQP_DUAL_INFEASIBLE || st == OSQP_DUAL_INFEASIBLE_INACCURATE || st == OSQP_NON_CVX;

@@ -94,6 +94,7 @@ struct Batch {
   c_int update_rho(const c_float *rho);
   c_int refactor();
   c_int kkt_solve(c_float *rhs);
+  c_int kkt_solve_static(const c_float *rhs, c_float *sol);
   c_int solve_to_host(c_float *x, c_float *y, c_int *iter, c_int *status, c_float *obj, c_float *pri, c_float *dua,
                       c_int *rho_updates, c_float *rho_est);
   c_int get_solution(c_float *x, c_float *y);

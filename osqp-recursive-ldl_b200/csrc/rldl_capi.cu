@@ -812,6 +812,12 @@ c_int rldl_batch_update_horizon(RLDLBatch *h, c_int N) { HB(h); return h->b->upd
 c_int rldl_batch_update_rho(RLDLBatch *h, const c_float *rho) { HB(h); return h->b->update_rho(rho); }
 c_int rldl_batch_refactor(RLDLBatch *h) { HB(h); return h->b->refactor(); }
 c_int rldl_batch_kkt_solve(RLDLBatch *h, c_float *rhs) { HB(h); return h->b->kkt_solve(rhs); }
+c_int rldl_batch_kkt_solve_static(RLDLBatch *h, const c_float *rhs, c_float *sol) {
+  HB(h);
+  if (!rhs || !sol) return osqp_error(OSQP_DATA_VALIDATION_ERROR);
+  return h->b->kkt_solve_static(rhs, sol);
+}
+c_int rldl_batch_max_static_doubles(void) { return (c_int)rldl::kKktStaticDoubles; }
 c_int rldl_batch_get_solution(RLDLBatch *h, c_float *x, c_float *y) { HB(h); return h->b->get_solution(x, y); }
 c_int rldl_batch_get_info(RLDLBatch *h, c_int *iter, c_int *status_val, c_float *obj_val, c_float *pri_res,
                           c_float *dua_res, c_int *rho_updates, c_float *rho_estimate) {

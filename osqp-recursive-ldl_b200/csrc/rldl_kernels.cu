@@ -556,6 +556,48 @@ cudaError_t launch_polish(const ModelDev &M, const BatchDev &B, const BatchDev &
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------
+// Allocation-free KKT solve (rldl_batch_kkt_solve_static).  The existing entry point stages the right-hand sides in
+// a cudaMalloc'ed buffer that grows on demand; this variant stages them in a fixed file-scope device array, so the
+// call path contains no cudaMalloc / cudaFree.  Every GPU that loads the library holds the array (4 MiB) until exit.
+// All calls share it: it keeps the last call's contents, calls that overlap on the GPU race.  Nothing in it has to
+// start at zero — the kernel reads exactly the count doubles the call has just copied in.
+// In host code `g_kkt_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) double g_kkt_scratch[kKktStaticDoubles];
+
+static cudaError_t kkt_scratch_address(double **out) {
+  static double *addr[64] = {nullptr};  // per device; racing first calls write the same value
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (!addr[dev]) {
+    double *p = nullptr;
+    e = cudaGetSymbolAddress((void **)&p, g_kkt_scratch);
+    if (e != cudaSuccess) return e;
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return cudaSuccess;
+}
+
+// rhs_in / sol_out: host arrays of count = batch * ld doubles (ld = n + m); the caller has checked count against
+// kKktStaticDoubles.  Copies in, runs k_kkt_solve on the static scratch, copies out; stream-ordered, not synchronised.
+cudaError_t launch_kkt_solve_static(const ModelDev &M, const BatchDev &B, const SettingsDev &S, const double *rhs_in,
+                                    double *sol_out, size_t count, int ld, cudaStream_t st) {
+  if (count > (size_t)kKktStaticDoubles) return cudaErrorInvalidValue;
+  double *scratch = nullptr;
+  cudaError_t e = kkt_scratch_address(&scratch);
+  if (e != cudaSuccess) return e;
+  e = cudaMemcpyAsync(scratch, rhs_in, count * sizeof(double), cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) return e;
+  e = launch_kkt_solve(M, B, S, scratch, ld, st);
+  if (e != cudaSuccess) return e;
+  return cudaMemcpyAsync(sol_out, scratch, count * sizeof(double), cudaMemcpyDeviceToHost, st);
+}
+
 cudaError_t launch_kkt_solve(const ModelDev &M, const BatchDev &B, const SettingsDev &S, double *rhs,
                              int ld, cudaStream_t st) {
   int vm = M.a;

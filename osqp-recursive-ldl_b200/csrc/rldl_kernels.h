@@ -14,6 +14,10 @@ cudaError_t launch_admm(const ModelDev &M, const BatchDev &B, const SettingsDev 
                         cudaStream_t st);
 cudaError_t launch_polish(const ModelDev &M, const BatchDev &B, const BatchDev &P, const SettingsDev &S, double delta,
                           int refine_iter, double *pb, double *ps, double *pr, int *status_polish, cudaStream_t st);
+// allocation-free variant: right-hand sides staged in a fixed file-scope device array of kKktStaticDoubles doubles
+constexpr int kKktStaticDoubles = 512 * 1024;  // 4 MiB per GPU that loads the library
+cudaError_t launch_kkt_solve_static(const ModelDev &M, const BatchDev &B, const SettingsDev &S, const double *rhs_in,
+                                    double *sol_out, size_t count, int ld, cudaStream_t st);
 cudaError_t launch_kkt_solve(const ModelDev &M, const BatchDev &B, const SettingsDev &S, double *rhs,
                              int ld, cudaStream_t st);
 cudaError_t launch_warm_start_z(const ModelDev &M, const BatchDev &B, cudaStream_t st);

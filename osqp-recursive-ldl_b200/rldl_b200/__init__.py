@@ -111,7 +111,7 @@ osqp_solve_combine_recursive osqp_update_Z_horizon osqp_update_X_horizon
 osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions cleanup_rldl
 rldl_batch_setup rldl_batch_solve rldl_batch_solve_to_host rldl_batch_update_bounds rldl_batch_partial_update_bounds
 rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
-rldl_batch_refactor rldl_batch_update_model rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_get_solution rldl_batch_get_info
+rldl_batch_refactor rldl_batch_update_model rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_kkt_solve_static rldl_batch_max_static_doubles rldl_batch_get_solution rldl_batch_get_info
 rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel rldl_batch_set_tuning rldl_batch_lane_stats rldl_batch_get_trace rldl_batch_get_scaling rldl_batch_get_polish
 rldl_batch_free
 rldl_device_count rldl_set_device rldl_version
@@ -175,6 +175,7 @@ def lib():
         "rldl_batch_failed_factorisations": [vp, vp],
         "rldl_batch_update_model": [vp, vp],
         "rldl_batch_kkt_solve": [vp, vp],
+        "rldl_batch_kkt_solve_static": [vp, vp, vp],
         "rldl_batch_get_solution": [vp, vp, vp],
         "rldl_batch_get_info": [vp] * 8,
         "rldl_batch_update_settings": [vp, C.POINTER(OSQPSettings)],
@@ -196,6 +197,8 @@ def lib():
     L.rldl_batch_select_kernel.restype = c_int
     L.rldl_batch_set_tuning.argtypes = [vp, C.c_char_p, c_int]
     L.rldl_batch_set_tuning.restype = c_int
+    L.rldl_batch_max_static_doubles.argtypes = []
+    L.rldl_batch_max_static_doubles.restype = c_int
     L.rldl_batch_stream.argtypes = [vp]
     L.rldl_batch_stream.restype = vp
     for name in ("max_iter", "warm_start", "scaled_termination", "check_termination", "polish",
@@ -357,6 +360,12 @@ class Batch:
         if rc:
             raise RuntimeError(f"rldl_batch_kkt_solve failed with code {rc}")
         return rhs
+
+    def kkt_solve_static(self, rhs):
+        """rldl_batch_kkt_solve_static (no allocation on the call path); returns (rc, solution)."""
+        rhs = np.ascontiguousarray(rhs, np.float64)
+        sol = np.empty_like(rhs)
+        return lib().rldl_batch_kkt_solve_static(self.h, _p(rhs), _p(sol)), sol
 
     def last_times(self):
         f, s = C.c_double(), C.c_double()
