@@ -441,8 +441,9 @@ c_int osqp_solve(OSQPWorkspace *work) {
                      status == OSQP_DUAL_INFEASIBLE || status == OSQP_DUAL_INFEASIBLE_INACCURATE || status == OSQP_NON_CVX;
   for (c_int i = 0; i < n; i++) work->solution->x[i] = nosol ? OSQP_NAN : work->x[i];
   for (c_int i = 0; i < m; i++) work->solution->y[i] = nosol ? OSQP_NAN : work->y[i];
-  info->status_polish = 0; info->polish_time = 0.0;
-  if (work->settings->polish) {  // polish (src/polish.c) ran inside the solve for a solved instance
+  // polish (src/polish.c) ran inside the solve iff it is on and the instance ended OSQP_SOLVED (osqp.c:589-591);
+  // otherwise status_polish / polish_time keep their previous values, as in the reference
+  if (work->settings->polish && status == OSQP_SOLVED) {
     c_int sp = 0;
     if (B->get_polish(&sp)) return 1;
     info->status_polish = sp;

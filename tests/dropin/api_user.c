@@ -10,7 +10,10 @@
  *   part B — the combine variant on the C1-shaped MPC of mpc_model.h:
  *     osqp_setup_combine_recursive (head 15 + tail 3), osqp_solve_combine_recursive,
  *     osqp_update_Z_horizon (tail +2);
- *   part C — the reference's own unconstrained / non_cvx / primal_dual_infeasibility test problems.
+ *   part C — the reference's own unconstrained / non_cvx / primal_dual_infeasibility test problems;
+ *   part D — the settings osqp_set_default_settings leaves (Ruiz scaling = 10, adaptive rho; the automatic
+ *     wall-clock interval replaced by an explicit one so both sides are deterministic) and polish = 1 on the
+ *     basic_qp problem and on a badly scaled QP; osqp_update_polish; time_limit reached.
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -253,11 +256,96 @@ static int part_c(void) {
   return 0;
 }
 
+/* part D */
+static void report_polish(const char *tag, OSQPWorkspace *w) {
+  printf("POLISH %s status_polish %lld\n", tag, (long long)w->info->status_polish);
+}
+
+static int part_d(void) {
+  c_int rc;
+  OSQPWorkspace *w = NULL;
+  { /* basic_qp, defaults (scaling 10, adaptive rho, eps 1e-3) + polish */
+    c_float P_x[3] = {4.0, 1.0, 2.0};
+    c_int P_i[3] = {0, 0, 1}, P_p[3] = {0, 1, 3};
+    c_float q[2] = {1.0, 1.0};
+    c_float A_x[4] = {1.0, 1.0, 1.0, 1.0};
+    c_int A_i[4] = {0, 1, 0, 2}, A_p[3] = {0, 2, 4};
+    c_float l[3] = {1.0, 0.0, 0.0}, u[3] = {1.0, 0.7, 0.7};
+    OSQPData *data = (OSQPData *)calloc(1, sizeof(OSQPData));
+    data->n = 2;
+    data->m = 3;
+    data->P = csc_matrix(2, 2, 3, P_x, P_i, P_p);
+    data->q = q;
+    data->A = csc_matrix(3, 2, 4, A_x, A_i, A_p);
+    data->l = l;
+    data->u = u;
+    OSQPSettings *s = (OSQPSettings *)malloc(sizeof(OSQPSettings));
+    osqp_set_default_settings(s);
+    s->adaptive_rho_interval = 25; /* the default 0 picks the interval from wall clock (src/osqp.c:459-485) */
+    s->verbose = 0;
+    s->polish = 1;
+    rc = osqp_setup(&w, data, s);
+    printf("SETUP defaults rc %lld\n", (long long)rc);
+    if (rc) return 10 + (int)rc;
+    rc = osqp_solve(w);
+    report("defaults_polish", w, rc);
+    report_polish("defaults_polish", w);
+    rc = osqp_update_polish(w, 0);
+    c_float q2[2] = {2.5, 3.2};
+    rc |= osqp_update_lin_cost(w, q2);
+    rc |= osqp_solve(w);
+    report("defaults_no_polish", w, rc);
+    report_polish("defaults_no_polish", w);
+    osqp_cleanup(w);
+  }
+  { /* badly scaled QP: column / row norms from 1e-2 to 1e2, so D, E, c are far from 1 */
+    c_float P_x[6] = {200.0, 3.0, 0.5, 0.02, 0.001, 0.004};
+    c_int P_i[6] = {0, 0, 1, 1, 2, 3}, P_p[5] = {0, 1, 3, 5, 6};
+    c_float q[4] = {-40.0, 0.3, -0.01, 0.002};
+    c_float A_x[9] = {100.0, 1.0, 2.0, 0.5, 1.0, 0.01, 0.02, 0.05, 1.0};
+    c_int A_i[9] = {0, 3, 0, 1, 4, 1, 2, 2, 4}, A_p[5] = {0, 2, 5, 7, 9};
+    c_float l[5] = {-50.0, -1.0, -0.004, -1e30, 0.2}, u[5] = {80.0, 1.5, 0.004, 0.3, 0.2};
+    OSQPData *data = (OSQPData *)calloc(1, sizeof(OSQPData));
+    data->n = 4;
+    data->m = 5;
+    data->P = csc_matrix(4, 4, 6, P_x, P_i, P_p);
+    data->q = q;
+    data->A = csc_matrix(5, 4, 9, A_x, A_i, A_p);
+    data->l = l;
+    data->u = u;
+    OSQPSettings *s = (OSQPSettings *)malloc(sizeof(OSQPSettings));
+    osqp_set_default_settings(s);
+    s->adaptive_rho_interval = 25;
+    s->eps_abs = s->eps_rel = 1e-6;
+    s->verbose = 0;
+    w = NULL;
+    rc = osqp_setup(&w, data, s);
+    printf("SETUP badly_scaled rc %lld\n", (long long)rc);
+    if (rc) return 10 + (int)rc;
+    rc = osqp_solve(w);
+    report("badly_scaled", w, rc);
+    c_float l2[5] = {-50.0, -1.0, -0.004, -1e30, 0.1}, u2[5] = {80.0, 0.2, 0.004, 0.3, 0.1};
+    rc = osqp_update_bounds(w, l2, u2);
+    rc |= osqp_update_polish(w, 1);
+    rc |= osqp_solve(w);
+    report("badly_scaled_bounds_polish", w, rc);
+    report_polish("badly_scaled_bounds_polish", w);
+    c_float P_new[6] = {150.0, 2.0, 0.8, 0.01, 0.002, 0.004};
+    rc = osqp_update_P(w, P_new, NULL, 6);
+    rc |= osqp_update_polish(w, 0);
+    rc |= osqp_solve(w);
+    report("badly_scaled_P", w, rc);
+    osqp_cleanup(w);
+  }
+  return 0;
+}
+
 int main(int argc, char **argv) {
-  int which = argc > 1 ? atoi(argv[1]) : 7, rc = 0;
+  int which = argc > 1 ? atoi(argv[1]) : 15, rc = 0;
   if (which & 1) rc = part_a();
   if (!rc && (which & 2)) rc = part_b();
   if (!rc && (which & 4)) rc = part_c();
+  if (!rc && (which & 8)) rc = part_d();
   printf("DONE rc %d\n", rc);
   return rc;
 }

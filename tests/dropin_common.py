@@ -37,6 +37,8 @@ def parse(text):
                 rec[w[k]] = float(w[k + 1]) if w[k] in ("obj", "pri", "dua") else int(w[k + 1])
                 k += 2
             rec["status"] = line.split('"')[1]
+        elif w[0] == "POLISH":
+            out["solves"].setdefault(w[1], {})["status_polish"] = int(w[3])
         elif w[0] in ("X", "Y") and len(w) > 1:
             out["solves"].setdefault(w[1], {})[w[0].lower()] = np.array([float(v) for v in w[2:]])
     return out
@@ -55,7 +57,7 @@ def assert_same_run(got, want, tol, what):
     assert list(got["solves"]) == list(want["solves"]) and want["solves"], (what, list(got["solves"]))
     for tag, w in want["solves"].items():
         g = got["solves"][tag]
-        for key in ("rc", "n", "m", "status_val", "iter", "status"):
+        for key in ("rc", "n", "m", "status_val", "iter", "status", "status_polish"):
             assert g.get(key) == w.get(key), (what, tag, key, g.get(key), w.get(key))
         assert g["x"].shape == (w["n"],) and g["y"].shape == (w["m"],), (what, tag)
         assert rel(g["x"], w["x"]) < tol, (what, tag, "x", rel(g["x"], w["x"]))

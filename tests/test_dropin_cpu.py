@@ -40,7 +40,12 @@ def test_reference_linked_api_program_reproduces_the_golden_output():
     got, want = parse(cp.stdout), parse(open(GOLDEN_API).read())
     assert want["rc"] == {"SETUP generic": 0, "BADRHO": 1, "CLEANUP": 0, "SETUP combine": 0, "SETUP unconstrained": 0,
                           "SETUP non_cvx_small_sigma": 5, "SETUP non_cvx": 0, "SETUP infeasibility1": 0,
-                          "SETUP infeasibility2": 0, "SETUP infeasibility3": 0, "SETUP infeasibility4": 0, "DONE": 0}
+                          "SETUP infeasibility2": 0, "SETUP infeasibility3": 0, "SETUP infeasibility4": 0,
+                          "SETUP defaults": 0, "SETUP badly_scaled": 0, "DONE": 0}
+    # part D: default settings (Ruiz scaling 10, adaptive rho) + polish; the reference keeps a stale status_polish
+    assert want["solves"]["defaults_polish"]["status_polish"] == 1
+    assert abs(want["solves"]["defaults_polish"]["obj"] - 1.88) < 1e-12            # polished to the known answer
+    assert want["solves"]["badly_scaled_bounds_polish"]["status_polish"] == 1
     sv = {t: r["status_val"] for t, r in want["solves"].items()}
     assert (sv["unconstrained"], sv["non_cvx"], sv["infeasibility1"], sv["infeasibility2"], sv["infeasibility3"]) == \
         (1, -7, 1, -3, -4)

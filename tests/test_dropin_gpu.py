@@ -22,7 +22,9 @@ REL_TOL = 1e-6
 def test_user_program_linked_against_the_product_matches_the_reference(name, golden, ref_name):
     """api_b200 (tests/dropin/api_user.c): the stock API on the reference's basic_qp problem (osqp_setup,
     osqp_solve, update_lin_cost, update_lower/upper_bound, warm_start_x/_y, update_rho, update_P_A,
-    update_max_iter, cleanup) and the combine variant (setup 15+3, solve, update_Z_horizon +2)."""
+    update_max_iter, cleanup), the combine variant (setup 15+3, solve, update_Z_horizon +2), the reference's small
+    test problems, and part D: osqp_set_default_settings as it is (Ruiz scaling 10, adaptive rho) + polish on
+    basic_qp and on a badly scaled QP, with osqp_update_bounds / osqp_update_P / osqp_update_polish in between."""
     assert os.path.exists(binary(name)), f"{name} not built: run `python __graft_entry__.py`"
     cp = run(name)
     assert cp.returncode == 0, (cp.returncode, cp.stdout[-500:], cp.stderr[-2000:])
