@@ -489,6 +489,9 @@ c_int rldl_batch_lane_stats(RLDLBatch *b, c_int *stats);
  * from the start of the solve to the moment it finished + 1e6 x the engine that finished it (1 streaming kernel,
  * 2 latency-mode kernel).  Returns 1 if tracing was never switched on. */
 c_int rldl_batch_get_trace(RLDLBatch *b, c_float *t);
+/* diagnostic: raw copy of the first n ints of the device scheduler state (csrc/rldl_device.h, kSched*), readable
+ * from another host thread while a solve is running */
+c_int rldl_batch_debug_sched(RLDLBatch *b, int *out, c_int n);
 /* the CUDA stream (cudaStream_t) every launch and copy of this handle is issued on, so a
  * caller can bracket calls with its own events on the launching stream */
 void *rldl_batch_stream(const RLDLBatch *b);

@@ -509,12 +509,17 @@ c_int Batch::solve() {
       const bool run_lane = run_stream && lane > 0 && unfinished >= 4 * lat_below;
       if (run_stream) {
         int s_ctas = 0;
+        if (run_lane) CK(preload_lane_kernels());  // before anything of this round runs (see below)
         const int retire = lat_retire_below > 0 ? lat_retire_below : 6 * lat_below;
         const int park = !lat_ok ? 0 : ((run_lane && lane_tail > 0) ? std::min(lat_below, lane_tail) : lat_below);
         CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, park, tune,
                               run_lane ? lane : 0, retire, run_lane ? ev_reset : nullptr, &s_ctas, stream));
         launches++;
         if (run_lane) {
+          // The lane CTAs spin until a kernel launched AFTER them (k_set_tail_flag) has run.  With CUDA's lazy module
+          // loading the first launch of a kernel loads it, which can wait for running kernels to finish: a deadlock
+          // if the kernel to be loaded is the one the running kernel waits for.  Hence preload_lane_kernels() above;
+          // the lane CTAs also give up waiting after a second without a hand-over.
           // latency-mode CTAs beside the streaming kernel: pending until its CTAs on SMs 0..lane-1 retire, then fed
           // with the most-unconverged instances by the streaming groups (their chains would bound the tail)
           CK(cudaStreamWaitEvent(stream2, ev_reset, 0));

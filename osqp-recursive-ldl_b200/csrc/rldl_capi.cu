@@ -878,6 +878,15 @@ c_int rldl_batch_set_tuning(RLDLBatch *h, const char *name, c_int value) {
   else return 1;
   return 0;
 }
+// diagnostic: raw copy of the device scheduler state (kSchedCounters ints) — usable while a solve is running
+c_int rldl_batch_debug_sched(RLDLBatch *h, int *out, c_int n) {
+  HB(h);
+  if (n > rldl::kSchedCounters) n = rldl::kSchedCounters;
+  static cudaStream_t dbg = nullptr;
+  if (!dbg && cudaStreamCreateWithFlags(&dbg, cudaStreamNonBlocking) != cudaSuccess) return 1;
+  if (cudaMemcpyAsync(out, h->b->D.sched, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, dbg) != cudaSuccess) return 1;
+  return cudaStreamSynchronize(dbg) == cudaSuccess ? 0 : 1;
+}
 c_int rldl_batch_get_trace(RLDLBatch *h, c_float *t) { HB(h); return t ? h->b->get_trace(t) : 1; }
 c_int rldl_batch_lane_stats(RLDLBatch *h, c_int *stats) {
   HB(h);

@@ -49,6 +49,7 @@ cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const Setti
                                int resume, int park_below, const StreamTuning &tune, int k_l, int retire_below,
                                cudaEvent_t reset_done, int *grid_out, cudaStream_t st);
 cudaError_t launch_set_tail_flag(const BatchDev &B, cudaStream_t st);
+cudaError_t preload_lane_kernels();  // forces the (lazy) load of the kernels launched while lane CTAs may be spinning
 // latency-mode kernel (rldl_latency.cu): one instance per CTA, factor resident in shared memory
 int latency_t_blocks(int Nmax);  // nx x (nx+2) blocks of global scratch per CTA of the latency-mode kernel
 size_t latency_smem_bytes(const ModelDev &M, int N);  // (size_t)-1 if the shape is not in the table

@@ -292,9 +292,16 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         if (sched_ring_nonempty(B, kSchedLQ)) i = sched_pop(B, kSchedLQ);
         if (i < 0 && claim_mode == 2 && !ld_volatile(B.sched + kSchedTailFlag)) {
           atomicAdd(B.sched + kSchedLWant, 1);
+          unsigned long long t_wait0;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_wait0));
           for (int spins = 1;; spins++) {
             if (sched_ring_nonempty(B, kSchedLQ) && (i = sched_pop(B, kSchedLQ)) >= 0) break;
             if (ld_volatile(B.sched + kSchedUnfinished) <= 0 || ld_volatile(B.sched + kSchedTailFlag)) break;
+            if ((spins & 255) == 0) {  // safety net: never wait for another kernel for more than a second
+              unsigned long long now;
+              asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+              if (now - t_wait0 > 1000000000ull) break;
+            }
             __nanosleep(2000);
             if ((spins & 7) == 0) {  // nobody qualified for a while: lower the hand-over threshold by one bucket
               const int t = ld_volatile(B.sched + kSchedTop);

@@ -853,7 +853,7 @@ __device__ __forceinline__ void sweep_rows(double (&X)[NP], double *rowbuf, int 
 // and the input block (lanes NX..A-1) are swept separately — 12^3 + 4^3 instead of 16^3 multiply-adds at C5 — and
 // W = Xinv F' only multiplies the non-zero block of each row.
 template <class SH>
-__global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B, double sigma, int k0,
+__global__ void __launch_bounds__(128, SH::A <= 16 ? 4 : 3) k_factor_stream(ModelDev M, BatchDev B, double sigma, int k0,
                                                           const int *only_flagged, int write_unpacked) {
   constexpr int A = SH::A, NX = SH::NX, NY = SH::NY, CW = SH::CW, G = SH::G, RS = SH::RS;
   constexpr int AE = SH::AE, NXE = SH::NXE, NU = SH::NU, BD = SH::BD;
@@ -924,7 +924,6 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
         Sx[j] = (d <= NX / 2) ? dp[d * NX + gl] : dp[(NX - d) * NX + j];
       }
     }
-    double Fr[A];  // row gl of F (lanes < NX), class 0 at stage 0, class 1 after
     int flag = 0;
     for (int k = k0; k <= N; k++) {
       const bool term = (k == N);
@@ -1033,10 +1032,9 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
       }
       if (term) break;
       // ---- W = Xinv F' (row gl), S = diag(1/rho_d) + F W (row gl, lanes < NX) ----
-      if (k == k0 || k == 1) {
-#pragma unroll
-        for (int i = 0; i < A; i++) Fr[i] = (gl < NX) ? Fd[(k == 0 ? 0 : A * NX) + i * NX + gl] : 0.0;
-      }
+      // row gl of F is read from shared memory where it is used (lane-distinct, conflict-free): 32 registers less
+      // than holding it across the stage loop, which buys a fourth CTA per SM
+      const double *Fg = Fd + (k == 0 ? 0 : A * NX) + (gl < NX ? gl : 0);
       const double *Ft = FdT + (k == 0 ? 0 : A * NX);
       __syncwarp(gm);
       if (gl < A) {
@@ -1079,8 +1077,9 @@ __global__ void __launch_bounds__(128, 3) k_factor_stream(ModelDev M, BatchDev B
       for (int c = 0; c < NX; c++) Sx[c] = 0.0;
 #pragma unroll
       for (int i = 0; i < A; i++) {
+        const double fi = (gl < NX) ? Fg[i * NX] : 0.0;
 #pragma unroll
-        for (int c = 0; c < NX; c++) Sx[c] = fma(Fr[i], tb[i * NXE + c], Sx[c]);
+        for (int c = 0; c < NX; c++) Sx[c] = fma(fi, tb[i * NXE + c], Sx[c]);
       }
       if (gl < NX) {
         const int rc = row_class(rk + SH::CLS, NY + gl);
@@ -1170,6 +1169,11 @@ __global__ void k_set_tail_flag(int *sched) { atomicExch(sched + kSchedTailFlag,
 cudaError_t launch_set_tail_flag(const BatchDev &B, cudaStream_t st) {
   k_set_tail_flag<<<1, 1, 0, st>>>(B.sched);
   return cudaGetLastError();
+}
+
+cudaError_t preload_lane_kernels() {
+  cudaFuncAttributes at;
+  return cudaFuncGetAttributes(&at, k_set_tail_flag);
 }
 
 cudaError_t launch_vec_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,

@@ -112,7 +112,7 @@ osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions clea
 rldl_batch_setup rldl_batch_solve rldl_batch_solve_to_host rldl_batch_update_bounds rldl_batch_partial_update_bounds
 rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
 rldl_batch_refactor rldl_batch_update_model rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_kkt_solve_static rldl_batch_max_static_doubles rldl_batch_get_solution rldl_batch_get_info
-rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel rldl_batch_set_tuning rldl_batch_lane_stats rldl_batch_get_trace rldl_batch_get_scaling rldl_batch_get_polish
+rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel rldl_batch_set_tuning rldl_batch_lane_stats rldl_batch_get_trace rldl_batch_debug_sched rldl_batch_get_scaling rldl_batch_get_polish
 rldl_batch_free
 rldl_device_count rldl_set_device rldl_version
 """.split()

@@ -201,3 +201,17 @@ def test_solve_to_host_delivers_what_get_returns(name, batch, below, kernel, pin
     assert np.array_equal(out["x"][:, :n], want["x"][:, :n]) and np.array_equal(out["y"][:, :m], want["y"][:, :m])
     if want["status"][1] in (-3, 3):
         assert (out["x"][1, :n] == float(0x7fc00000)).all()
+
+
+def test_lane_first_use_in_a_fresh_process_does_not_deadlock():
+    """The concurrent latency-mode CTAs spin until a kernel launched after them (k_set_tail_flag) has run; with CUDA's
+    lazy module loading the FIRST launch of that kernel in a process used to wait for the spinning CTAs (adaptive rho:
+    parked instances keep the unfinished count above zero, so they never left) — a deadlock that only shows when the
+    lane is the first thing a process does.  tools/exp_hang.py runs exactly that, in a fresh interpreter."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cp = subprocess.run([sys.executable, os.path.join(root, "tools", "exp_hang.py"), "8", "1"], capture_output=True,
+                        text=True, timeout=150)
+    assert cp.returncode == 0 and "ALL DONE" in cp.stdout, (cp.returncode, cp.stdout[-800:], cp.stderr[-800:])
