@@ -19,6 +19,21 @@
 #pragma once
 #include <cstdint>
 
+// In-kernel bounds asserts of the debug build (make debug: -DRLDL_DEBUG); compiled out otherwise.
+#ifdef RLDL_DEBUG
+#include <cstdio>
+#define RLDL_ASSERT(cond)                                                                                  \
+  do {                                                                                                     \
+    if (!(cond)) {                                                                                         \
+      printf("RLDL_ASSERT failed: %s  (%s:%d, block %d thread %d)\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, \
+             (int)threadIdx.x);                                                                            \
+      __trap();                                                                                            \
+    }                                                                                                      \
+  } while (0)
+#else
+#define RLDL_ASSERT(cond) ((void)0)
+#endif
+
 namespace rldl {
 
 // Row-wise ELL view of one small shared model matrix inside the model buffer.

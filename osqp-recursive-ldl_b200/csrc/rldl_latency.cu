@@ -207,6 +207,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       const int t0 = c * CH, cnt = min(CH, nblk - t0);
       const int p_lo = fwd ? 1 + t0 : (NC - t0) - (cnt - 1);
       const int s = c % NS;
+      RLDL_ASSERT(cnt >= 1 && cnt <= CH && p_lo >= 1 && p_lo + cnt - 1 <= NC && NC < B.Nmax / 2 + 2);  // chain blocks
       mbar_expect_tx(tbars_s + 8u * s, (uint32_t)(cnt * TBLK * 8));
       bulk_g2s(tring_s + 8u * (uint32_t)(s * CH * TBLK), Tsrc + (size_t)p_lo * TBLK, (uint32_t)(cnt * TBLK * 8),
                tbars_s + 8u * s);
@@ -342,6 +343,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     __syncthreads();
     const int inst = ctl[0];
     if (inst < 0) break;
+    RLDL_ASSERT(inst < B.batch);
+    RLDL_ASSERT((long long)(N + 1) * RS <= B.rec_stride && L.end * 8 <= 227 * 1024);
     const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
     double *x = B.x + vo, *z = B.z + ro, *y = B.y + ro, *dx = B.dx + vo, *dy = B.dy + ro;
     const double *recb = B.rec + (size_t)inst * B.rec_stride;

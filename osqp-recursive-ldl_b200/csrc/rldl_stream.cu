@@ -90,6 +90,7 @@ __global__ void __launch_bounds__(256) k_vec_records(BatchDev B, int k0, int par
   // loop runs one DRAM round trip per stage and leaves the memory system idle)
   constexpr int U = 4, W = (SH::BB + 31) / 32;
   static_assert(W <= kClsWords, "class words");
+  RLDL_ASSERT(k0 >= 0 && k0 <= N && N <= B.Nmax && (long long)(N + 1) * RS <= B.rec_stride);
   for (int kb = k0 + wid; kb <= N; kb += U * nw) {
     double lv[U][W], uv[U][W], qv[U];
     unsigned long long old[U][W];
@@ -320,6 +321,10 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     const int k = fwd ? ipos : npos - 1 - ipos;
     const double *src = recb + (size_t)k * RS + (fwd ? 0 : SH::XOFF);
     const uint32_t bytes = fwd ? SH::FWD_BYTES : SH::BWD_BYTES;
+    RLDL_ASSERT(s >= 0 && s < D);                                             // ring slot
+    RLDL_ASSERT(k >= 0 && k <= N && ipos >= 0 && ipos < npos);                // stage of the packet
+    RLDL_ASSERT((long long)k * RS + (fwd ? 0 : SH::XOFF) + bytes / 8 <= B.rec_stride);  // inside the instance's records
+    RLDL_ASSERT(recb >= B.rec && recb + B.rec_stride <= B.rec + (size_t)B.batch * B.rec_stride);
     const uint32_t bar = bars_s + 8u * s;
     mbar_expect_tx(bar, bytes);
     if (l2_hints & 1) bulk_g2s_hint(ring_s + 8u * (s * RS + (fwd ? 0 : SH::XOFF)), src, bytes, bar, pol_first);
@@ -420,6 +425,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     const int i = acquire(-1, &fresh);
     if (i < 0) return false;
     inst = i;
+    RLDL_ASSERT(inst >= 0 && inst < B.batch);
     __threadfence();  // order the loads below after the hand-over of the instance
     const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
     x = B.x + vo; z = B.z + ro; y = B.y + ro; dx = B.dx + vo; dy = B.dy + ro;
@@ -912,6 +918,7 @@ __global__ void __launch_bounds__(128, SH::A <= 16 ? 4 : 3) k_factor_stream(Mode
     const double rho_in = B.rho[inst], rho_eq = kRhoEq * rho_in;
     const double inv_in = 1.0 / rho_in, inv_eq = 1.0 / rho_eq, inv_min = 1.0 / kRhoMin;
     double *rec = B.rec + (size_t)inst * B.rec_stride;
+    RLDL_ASSERT(k0 >= 0 && k0 <= N && (long long)(N + 1) * RS <= B.rec_stride);
     double Sx[NX];  // row gl of Sinv_{k-1} (lanes < NX)
 #pragma unroll
     for (int j = 0; j < NX; j++) Sx[j] = 0.0;

@@ -70,7 +70,10 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ int ld_volatile(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
 
 __device__ __forceinline__ void sched_push(const BatchDev &B, int b, int inst) {
+  RLDL_ASSERT(b >= 0 && b < kSchedRings);
+  RLDL_ASSERT(inst >= 0 && inst < B.batch);
   const int idx = atomicAdd(B.sched + 2 + kSchedRings + b, 1);
+  RLDL_ASSERT(idx - ld_volatile(B.sched + 2 + b) < B.batch);  // an instance sits in at most one ring: never full
   int *sl = B.sched_slots + (size_t)b * B.batch + (idx % B.batch);
   while (atomicCAS(sl, -1, inst) != -1) __nanosleep(32);
 }
@@ -84,6 +87,7 @@ __device__ __forceinline__ int sched_pop(const BatchDev &B, int b) {
       int *sl = B.sched_slots + (size_t)b * B.batch + (h % B.batch);
       int v;
       while ((v = atomicExch(sl, -1)) < 0) __nanosleep(32);
+      RLDL_ASSERT(v < B.batch);
       return v;
     }
   }

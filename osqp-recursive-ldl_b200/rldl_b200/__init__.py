@@ -13,7 +13,8 @@ import numpy as np
 from . import mpc  # noqa: F401
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "librldl_b200.so")
+# RLDL_B200_LIB selects another build of the same library (the -DRLDL_DEBUG build with in-kernel asserts)
+LIB_PATH = os.environ.get("RLDL_B200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "librldl_b200.so")
 
 c_int = C.c_longlong
 c_float = C.c_double
