@@ -174,10 +174,12 @@ c_int Batch::upload_model(const csc *Q0, const csc *Qi, const csc *QN, const csc
 
 // Which kernels serve the model, and the stage-record layout that goes with them.
 c_int Batch::configure_stream() {
-  // Ruiz-scaled problems carry a step size per row and a sigma per variable: they run on the runtime-shape kernels
-  streaming = !generic && !scaled() && stream_supported(M, N);
-  stream_record_dims(M, &D.qa, &D.PX, &D.PS, &D.bb, &D.bd, &D.PXX);
-  D.RS = D.qa + D.PX + D.PS + kClsWords + 2 * D.bb;
+  // Ruiz-scaled problems carry a step size per row and a sigma per variable: the BASELINE shapes have streaming
+  // variants with that record layout (Shape<..., RZ = 1>), other scaled models run on the runtime-shape kernels
+  M.scaled = scaled() ? 1 : 0;
+  streaming = !generic && stream_supported(M, N);
+  stream_record_dims(M, &D.qa, &D.PX, &D.PS, &D.bb, &D.bd, &D.PXX, &D.sigw, &D.clsw);
+  D.RS = D.qa + D.sigw + D.PX + D.PS + D.clsw + 2 * D.bb;
   D.rec_stride = (long long)(Nmax + 1) * D.RS;
   const size_t bs = (size_t)batch;
   const size_t want = streaming ? bs * (size_t)D.rec_stride : 1;
@@ -438,7 +440,7 @@ c_int Batch::factor(int k0, bool only_flagged) {
   last_factor_ms = ms;
   // algorithmic bytes: pivot inverses written once (diagonal-packed records on the streaming path), the row
   // classes of the record (streaming) or rho_vec (runtime shapes) read once, per stage and instance
-  const double per_stage = streaming ? (double)D.PX + D.PS + kClsWords : (double)a * a + (double)nx * nx + b;
+  const double per_stage = streaming ? (double)D.PX + D.PS + D.clsw + D.sigw : (double)a * a + (double)nx * nx + b;
   factor_bytes = 8.0 * batch * ((N - k0) * per_stage + (streaming ? (double)D.PX : (double)nx * nx) + nt);
   return 0;
 }
@@ -612,7 +614,8 @@ bool Batch::use_stream() const {
 // the whole Nmax-sized problem (setup), not just the current horizon.
 c_int Batch::retype(int k0, int parts, bool only_parked, bool want_flags, bool all_rows) {
   if (streaming) {
-    CK(launch_vec_records(M, D, k0, parts | (only_parked ? 4 : 0), nullptr, want_flags ? d_changed : nullptr, stream));
+    CK(launch_vec_records(M, D, k0, parts | (only_parked ? 4 : 0), nullptr, want_flags ? d_changed : nullptr,
+                          settings.sigma, stream));
     launches++;
     if (!all_rows) return 0;
     // rows beyond the current horizon are typed once at setup, as the reference does (recursive_ldl.c:2190)
@@ -944,7 +947,7 @@ double Batch::admm_bytes_per_iteration() const {
   if (use_stream()) {
     // streaming kernel: every stage record is streamed once forward ([q|Xinv|Sinv|rho]) and once
     // backward ([Xinv|Sinv|rho|l|u]); the iterates x,z,y are counted first-read + last-write only
-    const double fwd = D.qa + D.PX + D.PS + kClsWords, bwd = D.PX + D.PS + kClsWords + 2.0 * D.bb;
+    const double fwd = D.qa + D.sigw + D.PX + D.PS + D.clsw, bwd = D.PX + D.PS + D.clsw + 2.0 * D.bb;
     return 8.0 * ((N + 1) * (fwd + bwd) + 2.0 * (D.n + 2.0 * D.m));
   }
   // generic kernel: the full (unpacked) pivot inverses streamed once forward and once backward,

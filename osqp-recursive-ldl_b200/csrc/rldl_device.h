@@ -57,6 +57,7 @@ struct ModelDev {
   const int *idx;
   int nval;  // entries in val[] / idx[] (the ELL part is copied to shared memory by the streaming kernels)
   int bd;    // 1: no state-input cross terms in the cost and one-variable path rows => block-diagonal pivots
+  int scaled;  // 1: the handle is Ruiz-scaled (settings.scaling > 0): selects the record layout with per-row step sizes
 };
 
 struct SettingsDev {
@@ -112,6 +113,7 @@ struct BatchDev {
   double *rec;
   int qa, PX, PS, bb, RS;
   int bd, PXX;
+  int sigw, clsw;          // doubles of the sigma part (0 unless Ruiz-scaled) and of the row-class / step-size part
   long long rec_stride;    // (Nmax+1)*RS doubles per instance
   // Device work scheduler of the persistent ADMM kernel (rldl_stream.cu):
   //   sched[0] fresh-instance counter, sched[1] instances parked for a rho refactorisation,

@@ -31,10 +31,11 @@ cudaError_t launch_scatter_rows(double *dst, int ld, const double *src, int len,
                                 cudaStream_t st);
 // streaming path (rldl_stream.cu)
 bool stream_supported(const ModelDev &M, int N);
-void stream_record_dims(const ModelDev &M, int *qa, int *PX, int *PS, int *bb, int *bd, int *PXX);
+void stream_record_dims(const ModelDev &M, int *qa, int *PX, int *PS, int *bb, int *bd, int *PXX, int *sigw,
+                        int *clsw);
 // vector part of the stage records (parts bit 0: q; bit 1: row classes, rho_vec, l, u + change flags)
 cudaError_t launch_vec_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,
-                               int *changed, cudaStream_t st);
+                               int *changed, double sigma, cudaStream_t st);
 // launch knobs of the streaming kernel (rldl_batch_set_tuning; 0 / -1 = the measured default)
 struct StreamTuning {
   int ring_depth = 0;   // stage records in flight per lane group (default 2)

@@ -348,10 +348,9 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
     double *x = B.x + vo, *z = B.z + ro, *y = B.y + ro, *dx = B.dx + vo, *dy = B.dy + ro;
     const double *recb = B.rec + (size_t)inst * B.rec_stride;
-    const double rho_in = __ldcg(B.rho + inst), rho_eq = kRhoEq * rho_in;
-    const double inv_in = 1.0 / rho_in, inv_eq = 1.0 / rho_eq, inv_min = 1.0 / kRhoMin;
-    auto rho_of = [&](int c) -> double { return c == 0 ? rho_in : (c == 1 ? rho_eq : kRhoMin); };
-    auto rinv_of = [&](int c) -> double { return c == 0 ? inv_in : (c == 1 ? inv_eq : inv_min); };
+    const double rho_in = __ldcg(B.rho + inst);
+    RhoClasses rcl;
+    rcl.set(rho_in);
     // ---------------- the whole factor of the instance -> shared memory (TMA bulk copies) ----------------
     if (threadIdx.x == 0) mbar_expect_tx(bar_s, (uint32_t)((N + 1) * RS * 8));
     __syncthreads();
@@ -432,11 +431,11 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       const int ilo = (k == 0) ? NX : 0;
       const double *sl_ = recs + k * RS;
       double g = 0.0;
-      if (gl >= ilo && gl < dim) g = sigma * xv - sl_[gl];
+      if (gl >= ilo && gl < dim) g = rec_sigma<SH>(sl_, gl, sigma) * xv - sl_[gl];
 #pragma unroll
       for (int t = 0; t < NYT; t++) {
         const int rr = gl + G * t;
-        if (rr < np) w[rr] = rho_of(row_class(sl_ + SH::CLS, rr)) * zp[t] - yp[t];
+        if (rr < np) w[rr] = rec_rho<SH>(sl_, rr, rcl) * zp[t] - yp[t];
       }
       __syncwarp(gm);
       double tt = 0.0;
@@ -451,8 +450,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       __syncwarp(gm);
       if (!term) {
         if (gl < NX) {
-          const double ri = rinv_of(row_class(sl_ + SH::CLS, NY + gl));
-          const double tdv = (zd - yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
+          const double tdv = (zd - rec_div_rho<SH>(yd, sl_, NY + gl, rcl)) -
+                             dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
           td2[gl] = tdv; td2[gl + NX] = tdv;
         }
         __syncwarp(gm);
@@ -606,10 +605,9 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
           if (rr < np) {
             const int ri = roff + rr;
             const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
-            const int rc = row_class(sl_ + SH::CLS, rr);
-            const double rho = rho_of(rc), rinv = rinv_of(rc), zo = zp[t], yo = yp[t];
+            const double rho = rec_rho<SH>(sl_, rr, rcl), zo = zp[t], yo = yp[t];
             const double zh = alpha * zt + oma * zo;
-            const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
+            const double zn = fmin(fmax(zh + rec_div_rho<SH>(yo, sl_, rr, rcl), sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
             z[ri] = zn; y[ri] = yo + d;
             zp[t] = zn; yp[t] = yo + d;  // handed to phase A of the next iteration
@@ -618,11 +616,11 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         }
         if (!term && gl < NX) {
           const int ri = roff + NY + gl;
-          const int rc = row_class(sl_ + SH::CLS, NY + gl);
-          const double rho = rho_of(rc), rinv = rinv_of(rc);
-          const double zt = (zd - yd * rinv) + nud * rinv;
+          const double rho = rec_rho<SH>(sl_, NY + gl, rcl);
+          const double yr = rec_div_rho<SH>(yd, sl_, NY + gl, rcl);
+          const double zt = (zd - yr) + rec_div_rho<SH>(nud, sl_, NY + gl, rcl);
           const double zh = alpha * zt + oma * zd;
-          const double zn = fmin(fmax(zh + yd * rinv, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
+          const double zn = fmin(fmax(zh + yr, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
           const double d = rho * (zh - zn);
           z[ri] = zn; y[ri] = yd + d;
           if (store_delta) dy[ri] = d;
@@ -708,12 +706,14 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       // projected delta_y with its norm and support-function value; norm of delta_x and q'delta_x
       if (store_delta) {
         const double *lg = B.l + ro, *ug = B.u + ro, *qg = B.q + vo;
+        const double *sEg = SH::RZ ? B.sE + ro : nullptr;  // Ruiz-scaled: finiteness is tested on the scaled bounds
         double ny_ = 0.0, lhs_ = 0.0, nx_ = 0.0, qdx_ = 0.0;
         for (int r = threadIdx.x; r < m; r += blockDim.x) {
           double d = __ldcg(dy + r);
           const double lv = __ldcg(lg + r), uv = __ldcg(ug + r);
-          if (uv > kInfBound) d = (lv < -kInfBound) ? 0.0 : fmin(d, 0.0);
-          else if (lv < -kInfBound) d = fmax(d, 0.0);
+          const double e = SH::RZ ? sEg[r] : 1.0;
+          if (e * uv > kInfBound) d = (e * lv < -kInfBound) ? 0.0 : fmin(d, 0.0);
+          else if (e * lv < -kInfBound) d = fmax(d, 0.0);
           dy[r] = d;
           ny_ = fmax(ny_, fabs(d));
           lhs_ += uv * fmax(d, 0.0) + lv * fmin(d, 0.0);
@@ -737,6 +737,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         int status = -10;
         double obj = 0.0, rho_new = rho_in;
         Resid R = {0, 0, 0, 0, 0, 0, 0, 0};
+        const double cs = SH::RZ ? B.sC[inst] : 1.0;
         {
           double a[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
           for (int g2 = gl; g2 < NG; g2 += G) {
@@ -768,7 +769,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
           int prim_ok = 0, dual_ok = 0, prim_inf = 0, dual_inf = 0;
           if (m == 0) prim_ok = 1;
           else if (R.pri < ea + er * fmax(R.nz, R.nAx)) prim_ok = 1;
-          else if (cny > epi && clhs < -epi * cny) prim_inf = primal_infeasible<G>(M, B, inst, gl, gm, rs, epi, m);
+          else if (cs * cny > epi && clhs < -epi * cny) prim_inf = primal_infeasible<G>(M, B, inst, gl, gm, rs, epi, m);
           if (R.dua < ea + er * fmax(fmax(R.nq, R.nAty), R.nPx)) dual_ok = 1;
           else if (cnx > edi && cqdx < -edi * cnx) dual_inf = dual_infeasible<G>(M, B, inst, gl, gm, rs, edi, n);
           if (prim_ok && dual_ok) { status = approximate ? 2 : 1; return 1; }
@@ -780,9 +781,13 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
           obj = R.obj;
           if (check_term(0)) done = true;
         }
+        // the rho estimate reads the norms of the SCALED problem (auxil.c:13-55); the stage-parallel residuals above are
+        // the unscaled ones, so the Ruiz-scaled variants take one sweep of the shared routine where the estimate is used
+        Resid Rs = R;
         if (!done && can_adapt) {
           if (!can_check) { obj = R.obj; }
-          const double rn = rho_estimate(R, rho_in);
+          if constexpr (SH::RZ) compute_residuals<G>(M, B, inst, gl, gm, rs, &Rs);
+          const double rn = rho_estimate(Rs, rho_in);
           if (rn > rho_in * S.adaptive_rho_tolerance || rn < rho_in / S.adaptive_rho_tolerance) {
             rho_changed = true;
             rho_new = fmin(fmax(rn, kRhoMin), kRhoMax);
@@ -811,7 +816,10 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         if (done) {
           const bool has_sol = !(status == -3 || status == 3 || status == -4 || status == 4 || status == -7);
           if (has_sol) obj = R.obj;
-          const double rho_est = rho_estimate(R, rho_new);
+          if constexpr (SH::RZ) {
+            if (has_sol) compute_residuals<G>(M, B, inst, gl, gm, rs, &Rs);
+          }
+          const double rho_est = rho_estimate(Rs, rho_new);
           if (!has_sol) {  // store_solution (auxil.c:527-563)
             if (status == -3 || status == 3) {
               double nrm = 0.0;
@@ -887,8 +895,8 @@ int latency_t_blocks(int Nmax) { return lat_t_blocks(Nmax); }
 
 size_t latency_smem_bytes(const ModelDev &M, int N) {
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_) \
-  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_)) return latency_smem_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(N);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_, sc_) \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_, sc_)) return latency_smem_t<Shape<a_, nx_, ny_, nt_, cw_, bd_, sc_>>(N);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return (size_t)-1;
@@ -898,9 +906,9 @@ cudaError_t launch_admm_latency(const ModelDev &M, const BatchDev &B, const Sett
                                 int resume, double *Tg, int ctas, int reset_parked, int claim_mode, int stream_ctas,
                                 cudaStream_t st) {
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                    \
-  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))         \
-    return launch_latency_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, Tg, ctas, reset_parked, \
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_, sc_)                    \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_, sc_))         \
+    return launch_latency_t<Shape<a_, nx_, ny_, nt_, cw_, bd_, sc_>>(M, B, S, warm_start, resume, Tg, ctas, reset_parked, \
                                                                  claim_mode, stream_ctas, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X

@@ -64,7 +64,7 @@ __device__ __forceinline__ unsigned long long spread_bits(unsigned v) {  // bit 
 
 template <class SH>
 __global__ void __launch_bounds__(256) k_vec_records(BatchDev B, int k0, int parts, const int *only_flagged,
-                                                     int *changed) {
+                                                     int *changed, double sigma) {
   // one CTA per instance, one warp per stage (stages k0 + w, k0 + w + 8, ...): at every step the CTA reads
   // 8 consecutive stages of q / l / u (2 KB runs) — a warp walking its own row alone leaves HBM at a tenth of
   // its bandwidth (one 224-byte access per DRAM page and 9 000 concurrent streams)
@@ -93,25 +93,35 @@ __global__ void __launch_bounds__(256) k_vec_records(BatchDev B, int k0, int par
   RLDL_ASSERT(k0 >= 0 && k0 <= N && N <= B.Nmax && (long long)(N + 1) * RS <= B.rec_stride);
   for (int kb = k0 + wid; kb <= N; kb += U * nw) {
     double lv[U][W], uv[U][W], qv[U];
+    double sg[U], ev[U][W], orho[U][W];  // Ruiz-scaled variants: sigma_i, E_r, the step size the record held
     unsigned long long old[U][W];
+    const double cs = SH::RZ ? B.sC[inst] : 1.0;
 #pragma unroll
     for (int j = 0; j < U; j++) {
       const int k = kb + j * nw;
       const bool on = k <= N, term = (k == N);
       const int rows = term ? NT : BQ;
       const int dim = term ? NX : A, ilo = (k == 0 && !term) ? NX : 0, xoff = k * A - NX;
-      qv[j] = 0.0;
-      if (on && (parts & 1) && lane >= ilo && lane < dim) qv[j] = __ldcs(B.q + vo + xoff + lane);
+      qv[j] = 0.0; sg[j] = sigma;
+      if (on && (parts & 1) && lane >= ilo && lane < dim) {
+        qv[j] = __ldcs(B.q + vo + xoff + lane);
+        if constexpr (SH::RZ) {
+          const double d = B.sD[vo + xoff + lane];
+          sg[j] = sigma / (cs * d * d);
+        }
+      }
 #pragma unroll
       for (int w = 0; w < W; w++) {
         const int r = 32 * w + lane;
-        lv[j][w] = uv[j][w] = 0.0; old[j][w] = 0ull;
+        lv[j][w] = uv[j][w] = 0.0; old[j][w] = 0ull; ev[j][w] = 1.0; orho[j][w] = 0.0;
         if (on && (parts & 2)) {
           if (r < rows) {
             const size_t ri = ro + (size_t)k * BQ + r;
             lv[j][w] = __ldcs(B.l + ri); uv[j][w] = __ldcs(B.u + ri);
+            if constexpr (SH::RZ) { ev[j][w] = B.sE[ri]; orho[j][w] = rec[(size_t)k * RS + SH::CLS + r]; }
           }
-          if (lane == 0) old[j][w] = (unsigned long long)__double_as_longlong(rec[(size_t)k * RS + SH::CLS + w]);
+          if (!SH::RZ && lane == 0)
+            old[j][w] = (unsigned long long)__double_as_longlong(rec[(size_t)k * RS + SH::CLS + w]);
         }
       }
     }
@@ -123,29 +133,47 @@ __global__ void __launch_bounds__(256) k_vec_records(BatchDev B, int k0, int par
       double *rk = rec + (size_t)k * RS;
       if (parts & 1) {
         static_assert(SH::QA <= 32, "q part of a record fits one warp pass");
-        if (lane < SH::QA) rk[lane] = qv[j];
+        if (lane < SH::QA) {
+          rk[lane] = qv[j];
+          if constexpr (SH::RZ) rk[SH::SIG + lane] = sg[j];
+        }
       }
       if (parts & 2) {
         const int rows = term ? NT : BQ;
 #pragma unroll
         for (int w = 0; w < W; w++) {
           const int r = 32 * w + lane;
-          int c = 0;
-          if (r < rows) {
-            c = (lv[j][w] < -kInfBound && uv[j][w] > kInfBound) ? 2 : ((uv[j][w] - lv[j][w] < kRhoTol) ? 1 : 0);
-            B.rho_vec[ro + (size_t)k * BQ + r] = c == 2 ? kRhoMin : (c == 1 ? kRhoEq * rho : rho);
+          if constexpr (SH::RZ) {
+            // rows are typed on the SCALED bounds (osqp.c:815-817, auxil.c:79-145); in unscaled variables the step
+            // size of the row is rho_class * E_r^2 / c
+            double rv = rho;
+            if (r < rows) {
+              const double e = ev[j][w];
+              rv = row_rho(e * lv[j][w], e * uv[j][w], rho) * e * e / cs;
+              B.rho_vec[ro + (size_t)k * BQ + r] = rv;
+              if (rv != orho[j][w]) ch = 1;
+            }
+            if (r < SH::BB) { rk[SH::CLS + r] = rv; rk[SH::LO + r] = lv[j][w]; rk[SH::UP + r] = uv[j][w]; }
+          } else {
+            int c = 0;
+            if (r < rows) {
+              c = (lv[j][w] < -kInfBound && uv[j][w] > kInfBound) ? 2 : ((uv[j][w] - lv[j][w] < kRhoTol) ? 1 : 0);
+              B.rho_vec[ro + (size_t)k * BQ + r] = c == 2 ? kRhoMin : (c == 1 ? kRhoEq * rho : rho);
+            }
+            const unsigned long long wv = spread_bits(__ballot_sync(FULL, c == 1)) |
+                                          (spread_bits(__ballot_sync(FULL, c == 2)) << 1);
+            if (lane == 0) {
+              if (old[j][w] != wv) ch = 1;
+              rk[SH::CLS + w] = __longlong_as_double((long long)wv);
+            }
+            if (r < SH::BB) { rk[SH::LO + r] = lv[j][w]; rk[SH::UP + r] = uv[j][w]; }
           }
-          const unsigned long long wv = spread_bits(__ballot_sync(FULL, c == 1)) |
-                                        (spread_bits(__ballot_sync(FULL, c == 2)) << 1);
-          if (lane == 0) {
-            if (old[j][w] != wv) ch = 1;
-            rk[SH::CLS + w] = __longlong_as_double((long long)wv);
-          }
-          if (r < SH::BB) { rk[SH::LO + r] = lv[j][w]; rk[SH::UP + r] = uv[j][w]; }
         }
+        if constexpr (!SH::RZ) {
 #pragma unroll
-        for (int w = W; w < kClsWords; w++)
-          if (lane == 0) rk[SH::CLS + w] = 0.0;
+          for (int w = W; w < kClsWords; w++)
+            if (lane == 0) rk[SH::CLS + w] = 0.0;
+        }
       }
     }
   }
@@ -162,20 +190,21 @@ __global__ void __launch_bounds__(256) k_vec_records(BatchDev B, int k0, int par
 
 template <class SH>
 static cudaError_t launch_vec_records_t(const BatchDev &B, int k0, int parts, const int *only_flagged, int *changed,
-                                        cudaStream_t st) {
+                                        double sigma, cudaStream_t st) {
   const int stages = B.N + 1 - k0;
   const int threads = stages >= 8 ? 256 : (stages >= 4 ? 128 : (stages >= 2 ? 64 : 32));
-  k_vec_records<SH><<<B.batch, threads, 0, st>>>(B, k0, parts, only_flagged, changed);
+  k_vec_records<SH><<<B.batch, threads, 0, st>>>(B, k0, parts, only_flagged, changed, sigma);
   return cudaGetLastError();
 }
 
 // Record layout of the specialisation that serves M (the first table entry that does; the full a x a layout
 // when none does and the records are unused).
-void stream_record_dims(const ModelDev &M, int *qa, int *PX, int *PS, int *bb, int *bd, int *PXX) {
+void stream_record_dims(const ModelDev &M, int *qa, int *PX, int *PS, int *bb, int *bd, int *PXX, int *sigw,
+                        int *clsw) {
   const int cw = max_c_width(M);
-  int use_bd = 0;
-#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_) \
-  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_)) { use_bd = bd_; goto found; }
+  int use_bd = 0, use_sc = 0;
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_, sc_) \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_, sc_)) { use_bd = bd_; use_sc = sc_; goto found; }
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
 found:
@@ -185,6 +214,8 @@ found:
   *PX = use_bd ? *PXX + even_up(dp_size(M.a - M.nx)) : even_up(dp_size(M.a));
   *PS = even_up(dp_size(M.nx));
   *bb = even_up(M.b);
+  *sigw = use_sc ? *qa : 0;
+  *clsw = use_sc ? *bb : kClsWords;
 }
 
 // ---------------------------------------------------------------------------
@@ -308,12 +339,10 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
   bool have = false;
   const double *recb = nullptr;
   double *x = nullptr, *z = nullptr, *y = nullptr, *dx = nullptr, *dy = nullptr, *ykg = nullptr, *skg = nullptr;
-  double rho_in = 0.0, rho_eq = 0.0, inv_in = 0.0, inv_eq = 0.0, inv_min = 0.0;
+  double rho_in = 0.0;
+  RhoClasses rcl;
   MutVec<NYT> cur;
 
-  // step size of a row and its reciprocal from the row's class (0 inequality, 1 equality, 2 loose)
-  auto rho_of = [&](int c) -> double { return c == 0 ? rho_in : (c == 1 ? rho_eq : kRhoMin); };
-  auto rinv_of = [&](int c) -> double { return c == 0 ? inv_in : (c == 1 ? inv_eq : inv_min); };
   const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
   // leader only: issue the packet at position ipos into ring slot `s`, advance ipos
   auto issue = [&](int s) {
@@ -431,8 +460,8 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     x = B.x + vo; z = B.z + ro; y = B.y + ro; dx = B.dx + vo; dy = B.dy + ro;
     ykg = B.yk + (size_t)inst * B.ykstride; skg = B.sk + (size_t)inst * B.skstride;
     recb = B.rec + (size_t)inst * B.rec_stride;
-    rho_in = __ldcg(B.rho + inst); rho_eq = kRhoEq * rho_in;
-    inv_in = 1.0 / rho_in; inv_eq = 1.0 / rho_eq; inv_min = 1.0 / kRhoMin;
+    rho_in = __ldcg(B.rho + inst);
+    rcl.set(rho_in);
     ipos = 0;
     if (gl == 0) {
       int s = slot;
@@ -493,11 +522,11 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         const double *sl_ = ring + slot * RS;
         consume_wait();
         double g = 0.0;
-        if (gl >= ilo && gl < dim) g = sigma * cur.x - sl_[gl];
+        if (gl >= ilo && gl < dim) g = rec_sigma<SH>(sl_, gl, sigma) * cur.x - sl_[gl];
 #pragma unroll
         for (int t = 0; t < NYT; t++) {
           const int rr = gl + G * t;
-          if (rr < np) w[rr] = rho_of(row_class(sl_ + SH::CLS, rr)) * cur.zp[t] - cur.yp[t];
+          if (rr < np) w[rr] = rec_rho<SH>(sl_, rr, rcl) * cur.zp[t] - cur.yp[t];
         }
         __syncwarp(gm);
         double tt = 0.0;
@@ -520,8 +549,8 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         __syncwarp(gm);
         if (!term) {
           if (gl < NX) {
-            const double ri = rinv_of(row_class(sl_ + SH::CLS, NY + gl));
-            const double tdv = (cur.zd - cur.yd * ri) - dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
+            const double tdv = (cur.zd - rec_div_rho<SH>(cur.yd, sl_, NY + gl, rcl)) -
+                               dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
             td2[gl] = tdv; td2[gl + NX] = tdv;
           }
           __syncwarp(gm);
@@ -571,10 +600,9 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           if (rr < np) {
             const int ri = roff + rr;
             const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
-            const int rc = row_class(sl_ + SH::CLS, rr);
-            const double rho = rho_of(rc), rinv = rinv_of(rc), zo = cur.zp[t], yo = cur.yp[t];
+            const double rho = rec_rho<SH>(sl_, rr, rcl), zo = cur.zp[t], yo = cur.yp[t];
             const double zh = alpha * zt + oma * zo;
-            const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
+            const double zn = fmin(fmax(zh + rec_div_rho<SH>(yo, sl_, rr, rcl), sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
             z[ri] = zn; y[ri] = yo + d;
             nw.zp[t] = zn; nw.yp[t] = yo + d;
@@ -583,12 +611,12 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         }
         if (!term && gl < NX) {
           const int ri = roff + NY + gl;
-          const int rc = row_class(sl_ + SH::CLS, NY + gl);
-          const double rho = rho_of(rc), rinv = rinv_of(rc);
+          const double rho = rec_rho<SH>(sl_, NY + gl, rcl);
           const double zo = cur.zd, yo = cur.yd;
-          const double zt = (zo - yo * rinv) + nud * rinv;
+          const double yr = rec_div_rho<SH>(yo, sl_, NY + gl, rcl);
+          const double zt = (zo - yr) + rec_div_rho<SH>(nud, sl_, NY + gl, rcl);
           const double zh = alpha * zt + oma * zo;
-          const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
+          const double zn = fmin(fmax(zh + yr, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
           const double d = rho * (zh - zn);
           z[ri] = zn; y[ri] = yo + d;
           nw.zd = zn; nw.yd = yo + d;
@@ -610,15 +638,15 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       bool done = false, rho_changed = false, at_tail = false;
       int status = -10;
       double obj = 0.0, rho_new = rho_in;
-      Resid R = {0, 0, 0, 0, 0, 0, 0, 0};
+      Resid R = {0, 0, 0, 0, 0, 0, 0, 0}, Rs = R;  // Rs: the norms of the scaled problem (rho estimate), = R unless SC
       if (can_check) {
-        R = compute_residuals<G>(M, B, inst, gl, gm, rs);
+        R = compute_residuals<G>(M, B, inst, gl, gm, rs, &Rs);
         obj = R.obj;
         if (check_termination<G>(M, B, S, inst, gl, gm, rs, R, 0, &status, &obj)) done = true;
       }
       if (!done && can_adapt) {  // adapt_rho (auxil.c:57-77); the refactorisation itself is a separate launch
-        if (!can_check) { R = compute_residuals<G>(M, B, inst, gl, gm, rs); obj = R.obj; }
-        const double rn = rho_estimate(R, rho_in);
+        if (!can_check) { R = compute_residuals<G>(M, B, inst, gl, gm, rs, &Rs); obj = R.obj; }
+        const double rn = rho_estimate(Rs, rho_in);
         if (rn > rho_in * S.adaptive_rho_tolerance || rn < rho_in / S.adaptive_rho_tolerance) {
           rho_changed = true;
           rho_new = fmin(fmax(rn, kRhoMin), kRhoMax);
@@ -631,7 +659,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       }
       if (!done && (iter == S.max_iter || timed_out)) {
         if (!can_check) {
-          R = compute_residuals<G>(M, B, inst, gl, gm, rs);
+          R = compute_residuals<G>(M, B, inst, gl, gm, rs, &Rs);
           obj = R.obj;
           check_termination<G>(M, B, S, inst, gl, gm, rs, R, 0, &status, &obj);
         }
@@ -648,7 +676,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       if (done) {
         const bool has_sol = !(status == -3 || status == 3 || status == -4 || status == 4 || status == -7);
         if (has_sol) obj = R.obj;
-        const double rho_est = rho_estimate(R, rho_new);
+        const double rho_est = rho_estimate(Rs, rho_new);
         if (!has_sol) {  // store_solution (auxil.c:527-563)
           if (status == -3 || status == 3) {
             double nrm = 0.0;
@@ -907,7 +935,10 @@ __global__ void __launch_bounds__(128, SH::A <= 16 ? 4 : 3) k_factor_stream(Mode
     }
   }
   __syncthreads();
-  double *gbuf = smem + M_END + (size_t)grp * (2 * AE + TB);
+  // per-group buffer stride = 2 (mod 16) doubles: the broadcast loads of the groups of one warp (pivot row, W, F')
+  // then fall into different banks — one wavefront per LDS.128 instead of one per group
+  constexpr int GSTRIDE = ((2 * AE + TB + 15) & ~15) + 2;
+  double *gbuf = smem + M_END + (size_t)grp * GSTRIDE;
   double *rowbuf = gbuf, *tb = gbuf + 2 * AE;
   const int urow = gl - NX;  // this lane's row of the input block (BD), negative on the state lanes
 
@@ -915,8 +946,8 @@ __global__ void __launch_bounds__(128, SH::A <= 16 ? 4 : 3) k_factor_stream(Mode
     if (only_flagged && !only_flagged[inst]) continue;
     // per-row step sizes from the 2-bit row classes of the record (written by k_vec_records) and the
     // instance's rho: no rho_vec traffic
-    const double rho_in = B.rho[inst], rho_eq = kRhoEq * rho_in;
-    const double inv_in = 1.0 / rho_in, inv_eq = 1.0 / rho_eq, inv_min = 1.0 / kRhoMin;
+    RhoClasses rcl;
+    rcl.set(B.rho[inst]);
     double *rec = B.rec + (size_t)inst * B.rec_stride;
     RLDL_ASSERT(k0 >= 0 && k0 <= N && (long long)(N + 1) * RS <= B.rec_stride);
     double Sx[NX];  // row gl of Sinv_{k-1} (lanes < NX)
@@ -941,12 +972,9 @@ __global__ void __launch_bounds__(128, SH::A <= 16 ? 4 : 3) k_factor_stream(Mode
       double Xr[XW], Xu[BD ? NU : 1];
       double dg = 0.0;
       if (gl < dim) {
-        dg = sigma;
+        dg = rec_sigma<SH>(rk, gl, sigma);  // (Ruiz-scaled: sigma / (c D_i^2), written by k_vec_records)
         const double cc = c2[cls * AE + gl];
-        if (cc != 0.0) {
-          const int rc = row_class(rk + SH::CLS, ci[cls * AE + gl]);
-          dg = fma(cc, rc == 0 ? rho_in : (rc == 1 ? rho_eq : kRhoMin), dg);
-        }
+        if (cc != 0.0) dg = fma(cc, rec_rho<SH>(rk, ci[cls * AE + gl], rcl), dg);
       }
       if constexpr (BD) {
 #pragma unroll
@@ -1089,8 +1117,7 @@ __global__ void __launch_bounds__(128, SH::A <= 16 ? 4 : 3) k_factor_stream(Mode
         for (int c = 0; c < NX; c++) Sx[c] = fma(fi, tb[i * NXE + c], Sx[c]);
       }
       if (gl < NX) {
-        const int rc = row_class(rk + SH::CLS, NY + gl);
-        const double rinv = rc == 0 ? inv_in : (rc == 1 ? inv_eq : inv_min);
+        const double rinv = rec_div_rho<SH>(1.0, rk, NY + gl, rcl);
 #pragma unroll
         for (int c = 0; c < NX; c++)
           if (c == gl) Sx[c] += rinv;
@@ -1131,7 +1158,8 @@ static cudaError_t launch_factor_stream_t(const ModelDev &M, const BatchDev &B, 
   constexpr int TB = A * A > A * NXE ? A * A : A * NXE;
   constexpr int M_END = ((2 * A * NX) * 2 + 3 * A * A + 3 * AE + (3 * AE + 1) / 2 + 1) & ~1;
   const int threads = 128, groups = (threads / 32) * SH::GPW;
-  const size_t shm = ((size_t)M_END + (size_t)groups * (2 * AE + TB)) * sizeof(double);
+  constexpr int GSTRIDE = ((2 * AE + TB + 15) & ~15) + 2;  // as in the kernel
+  const size_t shm = ((size_t)M_END + (size_t)groups * GSTRIDE) * sizeof(double);
   auto kern = k_factor_stream<SH>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm);
   if (e != cudaSuccess) return e;
@@ -1151,8 +1179,8 @@ static cudaError_t launch_factor_stream_t(const ModelDev &M, const BatchDev &B, 
 bool stream_supported(const ModelDev &M, int N) {
   if (N < 1) return false;
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_) \
-  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_)) return true;
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_, sc_) \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_, sc_)) return true;
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return false;
@@ -1162,9 +1190,9 @@ cudaError_t launch_admm_stream(const ModelDev &M, const BatchDev &B, const Setti
                                int resume, int park_below, const StreamTuning &tune, int k_l, int retire_below,
                                cudaEvent_t reset_done, int *grid_out, cudaStream_t st) {
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                                          \
-  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))      \
-    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, S, warm_start, resume, park_below, tune, k_l, \
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_, sc_)                                          \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_, sc_))      \
+    return launch_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_, sc_>>(M, B, S, warm_start, resume, park_below, tune, k_l, \
                                                                 retire_below, reset_done, grid_out, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
@@ -1184,11 +1212,11 @@ cudaError_t preload_lane_kernels() {
 }
 
 cudaError_t launch_vec_records(const ModelDev &M, const BatchDev &B, int k0, int parts, const int *only_flagged,
-                               int *changed, cudaStream_t st) {
+                               int *changed, double sigma, cudaStream_t st) {
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                                          \
-  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))      \
-    return launch_vec_records_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(B, k0, parts, only_flagged, changed, st);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_, sc_)                                          \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_, sc_))      \
+    return launch_vec_records_t<Shape<a_, nx_, ny_, nt_, cw_, bd_, sc_>>(B, k0, parts, only_flagged, changed, sigma, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;
@@ -1197,9 +1225,9 @@ cudaError_t launch_vec_records(const ModelDev &M, const BatchDev &B, int k0, int
 cudaError_t launch_factor_stream(const ModelDev &M, const BatchDev &B, double sigma, int k0,
                                  const int *only_flagged, int write_unpacked, cudaStream_t st) {
   const int cw = max_c_width(M);
-#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_)                                          \
-  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_))      \
-    return launch_factor_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_>>(M, B, sigma, k0, only_flagged, write_unpacked, st);
+#define RLDL_X(a_, nx_, ny_, nt_, cw_, bd_, sc_)                                          \
+  if (shape_serves(M, cw, a_, nx_, ny_, nt_, cw_, bd_, sc_))      \
+    return launch_factor_stream_t<Shape<a_, nx_, ny_, nt_, cw_, bd_, sc_>>(M, B, sigma, k0, only_flagged, write_unpacked, st);
   RLDL_SHAPES(RLDL_X)
 #undef RLDL_X
   return cudaErrorInvalidValue;

@@ -141,6 +141,38 @@ __device__ __forceinline__ int row_class(const double *cls, int row) {
   const unsigned long long wv = reinterpret_cast<const unsigned long long *>(cls)[row >> 5];
   return (int)((wv >> (2 * (row & 31))) & 3ull);
 }
+// Step size of row `row` of a stage and a division by it, from the record: the row's class and the instance's three
+// class values (rho, 1e3 rho, 1e-6, with precomputed reciprocals), or — Ruiz-scaled variants — the stored value
+// (and a true division, as the runtime-shape kernels do).
+struct RhoClasses {
+  double rho[3], inv[3];
+  __device__ __forceinline__ void set(double rho_in) {
+    rho[0] = rho_in; rho[1] = 1e3 * rho_in; rho[2] = 1e-6;
+    inv[0] = 1.0 / rho[0]; inv[1] = 1.0 / rho[1]; inv[2] = 1.0 / rho[2];
+  }
+};
+template <class SH>
+__device__ __forceinline__ double rec_rho(const double *rec, int row, const RhoClasses &rc) {
+  if constexpr (SH::RZ) return rec[SH::CLS + row];
+  else {
+    const int c = row_class(rec + SH::CLS, row);
+    return c == 0 ? rc.rho[0] : (c == 1 ? rc.rho[1] : rc.rho[2]);
+  }
+}
+template <class SH>
+__device__ __forceinline__ double rec_div_rho(double v, const double *rec, int row, const RhoClasses &rc) {
+  if constexpr (SH::RZ) return v / rec[SH::CLS + row];
+  else {
+    const int c = row_class(rec + SH::CLS, row);
+    return v * (c == 0 ? rc.inv[0] : (c == 1 ? rc.inv[1] : rc.inv[2]));
+  }
+}
+template <class SH>
+__device__ __forceinline__ double rec_sigma(const double *rec, int i, double sigma) {
+  if constexpr (SH::RZ) return rec[SH::SIG + i];
+  else return sigma;
+}
+
 // doubles of the diagonal-packed form of a symmetric n x n matrix
 __host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
 
@@ -151,9 +183,13 @@ __host__ __device__ inline int dp_size(int n) { return (n / 2 + 1) * n; }
 // pivot block X_k = Q_k + sigma I + C' rho C + [Sinv_{k-1} 0; 0 0] is block diagonal, and so is its inverse: the
 // record then carries the nx x nx and the nu x nu diagonal block instead of the a x a block (C5: 96 instead of
 // 144 doubles per stage and sweep direction).
-template <int A_, int NX_, int NY_, int NT_, int CW_, int BD_ = 0>
+// RZ = 1: Ruiz-scaled handle (settings.scaling > 0).  The scaled iteration is the unscaled one with a sigma per
+// variable and a step size per row, so the record carries sigma_i = sigma / (c D_i^2) behind q and the
+// per-row step sizes rho_j in place of the 2-bit row classes (C5: 240 / 264 instead of 198 / 238 doubles per stage
+// and sweep direction).
+template <int A_, int NX_, int NY_, int NT_, int CW_, int BD_ = 0, int RZ_ = 0>
 struct Shape {
-  static constexpr int A = A_, NX = NX_, NY = NY_, NT = NT_, CW = CW_, BD = BD_;
+  static constexpr int A = A_, NX = NX_, NY = NY_, NT = NT_, CW = CW_, BD = BD_, RZ = RZ_;
   static constexpr int NU = A - NX;
   static constexpr int B = NX + NY;
   static constexpr int G = A <= 8 ? 8 : (A <= 16 ? 16 : 32);
@@ -164,13 +200,14 @@ struct Shape {
   static constexpr int PXX = ((NX / 2 + 1) * NX + 1) & ~1, PUU = ((NU / 2 + 1) * NU + 1) & ~1;
   static constexpr int QA = (A + 1) & ~1, PX = BD ? PXX + PUU : (((A / 2 + 1) * A + 1) & ~1),
                        PS = ((NX / 2 + 1) * NX + 1) & ~1, BB = (B + 1) & ~1;
-  // stage record: [ q | Xinv (diagonal-packed; BD: its xx block, then its uu block) | Sinv (diagonal-packed) |
-  //                 row classes (2 bits per row) | l | u ]
+  // stage record: [ q | (RZ: sigma per variable) | Xinv (diagonal-packed; BD: its xx block, then its uu block) |
+  //                 Sinv (diagonal-packed) | row classes (2 bits per row; RZ: step size per row) | l | u ]
   static_assert(B <= 32 * kClsWords, "row classes of a stage must fit the class words of the record");
-  static constexpr int RS = QA + PX + PS + kClsWords + 2 * BB;
-  static constexpr int XOFF = QA, UOFF = QA + PXX, SOFF = QA + PX, CLS = QA + PX + PS, LO = CLS + kClsWords,
-                       UP = LO + BB;
-  static constexpr uint32_t FWD_BYTES = 8u * (QA + PX + PS + kClsWords), BWD_BYTES = 8u * (PX + PS + kClsWords + 2 * BB);
+  static constexpr int SIGW = RZ ? QA : 0, CLSW = RZ ? BB : kClsWords;
+  static constexpr int RS = QA + SIGW + PX + PS + CLSW + 2 * BB;
+  static constexpr int SIG = QA, XOFF = QA + SIGW, UOFF = XOFF + PXX, SOFF = XOFF + PX, CLS = XOFF + PX + PS,
+                       LO = CLS + CLSW, UP = LO + BB;
+  static constexpr uint32_t FWD_BYTES = 8u * (QA + SIGW + PX + PS + CLSW), BWD_BYTES = 8u * (PX + PS + CLSW + 2 * BB);
   // per-group scratch (doubles, every block even-sized)
   static constexpr int AE = (A + 1) & ~1, NXE = (NX + 1) & ~1;
   // the vectors of the forward sweep (w, tv2, yv, td2, sp) and of the backward sweep (vn2, vc, nud, gg2)
@@ -299,23 +336,28 @@ struct MutVec {  // the mutable per-stage values a lane owns (iterates and forwa
 // other box-constrained MPC shapes (nx,nu) = (2,1) (4,1) (6,2) (6,3) (8,4) (16,4): odd and even block sizes
 // in every lane-group width.  Any other shape runs on the runtime-shape kernels of rldl_kernels.cu.
 // Last column: 1 = the block-diagonal-pivot variant (chosen first when the model qualifies, ModelDev::bd).
-#define RLDL_SHAPES(X)    \
-  X(6, 4, 6, 4, 1, 1)     \
-  X(16, 12, 16, 12, 1, 1) \
-  X(11, 8, 11, 8, 1, 1)   \
-  X(6, 4, 6, 4, 1, 0)     \
-  X(16, 12, 16, 12, 1, 0) \
-  X(11, 8, 11, 8, 1, 0)   \
-  X(3, 2, 3, 2, 1, 0)     \
-  X(5, 4, 5, 4, 1, 0)     \
-  X(8, 6, 8, 6, 1, 0)     \
-  X(9, 6, 9, 6, 1, 0)     \
-  X(12, 8, 12, 8, 1, 0)   \
-  X(20, 16, 20, 16, 1, 0)
+#define RLDL_SHAPES(X)       \
+  X(6, 4, 6, 4, 1, 1, 0)     \
+  X(16, 12, 16, 12, 1, 1, 0) \
+  X(11, 8, 11, 8, 1, 1, 0)   \
+  X(6, 4, 6, 4, 1, 1, 1)     \
+  X(16, 12, 16, 12, 1, 1, 1) \
+  X(11, 8, 11, 8, 1, 1, 1)   \
+  X(6, 4, 6, 4, 1, 0, 0)     \
+  X(16, 12, 16, 12, 1, 0, 0) \
+  X(11, 8, 11, 8, 1, 0, 0)   \
+  X(3, 2, 3, 2, 1, 0, 0)     \
+  X(5, 4, 5, 4, 1, 0, 0)     \
+  X(8, 6, 8, 6, 1, 0, 0)     \
+  X(9, 6, 9, 6, 1, 0, 0)     \
+  X(12, 8, 12, 8, 1, 0, 0)   \
+  X(20, 16, 20, 16, 1, 0, 0)
 
-// does table entry (a, nx, ny, nt, cw, bd) serve this model?
-inline bool shape_serves(const ModelDev &M, int cw_model, int a, int nx, int ny, int nt, int cw, int bd) {
-  return M.a == a && M.nx == nx && M.ny == ny && M.nt == nt && cw_model <= cw && (bd == 0 || M.bd != 0);
+// does table entry (a, nx, ny, nt, cw, bd, sc) serve this model?  (sc: the Ruiz-scaled variants exist for the
+// block-diagonal BASELINE shapes; other scaled models run on the runtime-shape kernels)
+inline bool shape_serves(const ModelDev &M, int cw_model, int a, int nx, int ny, int nt, int cw, int bd, int sc) {
+  return M.a == a && M.nx == nx && M.ny == ny && M.nt == nt && cw_model <= cw && (bd == 0 || M.bd != 0) &&
+         sc == (M.scaled ? 1 : 0);
 }
 
 inline int max_c_width(const ModelDev &M) {

@@ -29,12 +29,24 @@ def _ref_out(g, tag, nmax, mmax):
 
 
 @pytest.mark.parametrize("name", ["C1", "C3", "C4"])
-def test_scaled_solves_match_golden(name):
+@pytest.mark.parametrize("mode", ["latency", "stream", "generic"])
+def test_scaled_solves_match_golden(name, mode):
+    """Every ADMM kernel on Ruiz-scaled problems: the BASELINE shapes have streaming / latency-mode variants whose stage
+    records carry sigma per variable and the step size per row (Shape<..., RZ = 1>); the runtime-shape kernels serve
+    everything else."""
     g = np.load(os.path.join(GOLD, f"scaled_{name}.npz"))
     mdl, N, x0, q, l, u = scaled_problem(name, int(g["batch"]))
     n, m = int(g["n"]), int(g["m"])
+
+    def tune(gb):
+        assert gb.select_kernel(2) == 0      # the shape-specialised kernels serve the scaled BASELINE shapes
+        if mode == "generic":
+            assert gb.select_kernel(1) == 0
+        else:
+            gb.set_tuning(lat_below=100000 if mode == "latency" else 0)
+
     gb = R.Batch(mdl, N, N, q, l, u, gpu_settings(scaling=10))
-    assert gb.select_kernel(2) == 1          # scaled problems run on the runtime-shape kernels
+    tune(gb)
     D, E, c = gb.get_scaling()
     assert np.abs(D[:, :n] / g["D"] - 1).max() < 1e-12 and np.abs(E[:, :m] / g["E"] - 1).max() < 1e-12
     assert np.abs(c / g["c"] - 1).max() < 1e-12
@@ -43,12 +55,36 @@ def test_scaled_solves_match_golden(name):
     gb.free()
     assert not bad, bad[:3]
     ga = R.Batch(mdl, N, N, q, l, u, gpu_settings(scaling=10, **ADAPT), rho=g["rho_a"])
+    tune(ga)
     assert ga.solve() == 0
     out = ga.get()
     ga.free()
     bad = compare(out, _ref_out(g, "_a", q.shape[1], l.shape[1]), n, m)
     assert not bad, bad[:3]
     assert (out["rho_updates"] == g["rho_updates_a"]).all()
+
+
+def test_scaled_batch_on_streaming_kernels_matches_reference_sample():
+    """C5-shaped batch with the OSQP default scaling = 10, large enough for the streaming kernel with pre-emption and the
+    hand-off to the latency-mode kernel: every instance against the runtime-shape kernels, a sample against the
+    reference's stock path."""
+    mdl, N, x0, q, l, u = scaled_problem("C3", 6000)
+    gb = R.Batch(mdl, N, N, q, l, u, gpu_settings(scaling=10))
+    assert gb.select_kernel(2) == 0
+    gb.set_tuning(lat_below=512)
+    assert gb.solve() == 0
+    out = gb.get()
+    n, m, _, _ = gb.dims()
+    gb.free()
+    gg = R.Batch(mdl, N, N, q[:400], l[:400], u[:400], gpu_settings(scaling=10))
+    assert gg.select_kernel(1) == 0 and gg.solve() == 0
+    bad = compare({k: v[:400] for k, v in out.items()}, gg.get(), n, m)
+    gg.free()
+    assert not bad, bad[:3]
+    idx = np.sort(np.random.default_rng(8).choice(6000, 24, replace=False))
+    ref = ref_run(mdl, N, N, q[idx], l[idx], u[idx], [("solve",), ("get",)], path="stock", scaling=10)[1]
+    bad = compare({k: v[idx] for k, v in out.items()}, ref, n, m)
+    assert not bad, bad[:3]
 
 
 def test_scaled_updates_and_warm_start_match_reference():
