@@ -629,11 +629,17 @@ c_int Batch::retype(int k0, int parts, bool only_parked, bool want_flags, bool a
 
 // scale_data (src/scaling.c:44-156) for every instance, from the resident model, the current horizon and the
 // current q; a no-op when settings.scaling == 0.
-c_int Batch::rescale() {
+c_int Batch::rescale(bool carry_iterates) {
   scale_stale = false;
   if (!scaled()) return 0;
+  // carry_iterates (P / A update): the reference's iterates live in scaled coordinates and survive the new
+  // equilibration numerically unchanged (osqp.c:1033-1051) — reproduce that warm-start point
+  const bool carry = carry_iterates && have_scaling;
+  if (carry) { CK(launch_rescale_iterates(D, 1, stream)); launches++; }
   CK(launch_ruiz(M, D, (int)settings.scaling, stream));
   launches++;
+  if (carry) { CK(launch_rescale_iterates(D, 0, stream)); launches++; }
+  have_scaling = true;
   return 0;
 }
 
@@ -790,7 +796,7 @@ c_int Batch::update_rho(const c_float *rho) {
 c_int Batch::refactor() {
   CK(cudaSetDevice(device));
   c_int rc = 0;
-  if (scale_stale) rc = rescale();  // P / A changed: the reference unscales, updates and scales again (osqp.c:1033-1051)
+  if (scale_stale) rc = rescale(true);  // P / A changed: the reference unscales, updates and scales again (osqp.c:1033-1051)
   if (rc) return rc;
   rc = retype(0, 3, false, false);
   if (rc) return rc;

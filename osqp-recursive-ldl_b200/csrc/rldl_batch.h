@@ -64,7 +64,8 @@ struct Batch {
 
   bool scaled() const { return settings.scaling > 0; }
   bool scale_stale = false;  // the model changed since the last equilibration
-  c_int rescale();
+  c_int rescale(bool carry_iterates = false);
+  bool have_scaling = false;  // an equilibration has been computed on this handle
   c_int fetch_scaling(int inst, c_float *Dv, c_float *Ev, c_float *c);
   c_int configure_stream();
   size_t rec_cap = 0;       // doubles allocated for D.rec

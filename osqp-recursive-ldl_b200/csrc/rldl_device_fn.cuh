@@ -406,13 +406,13 @@ struct Resid {
 // (scaled_termination = 0: auxil.c:251, 263, 314, 327 unscale them).  Under Ruiz scaling `scaled`, when given,
 // receives the same seven norms of the scaled problem (||E (Ax - z)||, ||c D (Px + q + A'y)||, ...): the rho
 // estimate reads those (compute_rho_estimate works on the scaled vectors, auxil.c:13-55).
-template <int G>
+template <int G, bool WITH_SCALED = true>
 __device__ Resid compute_residuals(const ModelDev &M, const BatchDev &B, int inst, int lane, unsigned gm,
                                    const Scratch &sm, Resid *scaled = nullptr) {
   const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
   const double *q = B.q + vo, *x = B.x + vo, *z = B.z + ro, *y = B.y + ro;
   double pri = 0, nz = 0, nAx = 0, dua = 0, nq = 0, nAty = 0, nPx = 0, oq = 0, oP = 0;
-  const bool ws = scaled != nullptr && B.sD != nullptr;
+  const bool ws = WITH_SCALED && scaled != nullptr && B.sD != nullptr;  // (WITH_SCALED = false: no code for it)
   const double *sD = ws ? B.sD + vo : nullptr, *sE = ws ? B.sE + ro : nullptr;
   const double sc = ws ? B.sC[inst] : 1.0;
   double s_pri = 0, s_nz = 0, s_nAx = 0, s_dua = 0, s_nq = 0, s_nAty = 0, s_nPx = 0;

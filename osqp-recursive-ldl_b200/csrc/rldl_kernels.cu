@@ -137,6 +137,32 @@ __global__ void k_ruiz(ModelDev M, BatchDev B, int iters) {
   if (lane == 0) B.sC[inst] = c;
 }
 
+// The iterates between the unscaled coordinates the kernels work in and the scaled coordinates of the current
+// equilibration (x_s = D^-1 x, z_s = E z, y_s = c E^-1 y; scaling.c:177-192, osqp.c:942-945).  The reference keeps
+// its iterates in scaled coordinates and leaves them numerically untouched when osqp_update_P / _A re-runs
+// scale_data (osqp.c:1033-1051), i.e. a warm start after a matrix update continues from D_new (D_old^-1 x): the
+// same is done here by going to scaled coordinates before the new equilibration and back after it.
+__global__ void k_rescale_iterates(BatchDev B, int to_scaled) {
+  const int inst = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (inst >= B.batch) return;
+  const size_t vo = (size_t)inst * B.nmax, ro = (size_t)inst * B.mmax;
+  const double c = B.sC[inst];
+  for (int i = lane; i < B.n; i += 32) {
+    const double d = B.sD[vo + i];
+    B.x[vo + i] = to_scaled ? B.x[vo + i] / d : B.x[vo + i] * d;
+  }
+  for (int r = lane; r < B.m; r += 32) {
+    const double e = B.sE[ro + r];
+    B.z[ro + r] = to_scaled ? B.z[ro + r] * e : B.z[ro + r] / e;
+    B.y[ro + r] = to_scaled ? c * B.y[ro + r] / e : e * B.y[ro + r] / c;
+  }
+}
+cudaError_t launch_rescale_iterates(const BatchDev &B, int to_scaled, cudaStream_t st) {
+  const int threads = 128, wpb = threads / 32;
+  k_rescale_iterates<<<(B.batch + wpb - 1) / wpb, threads, 0, st>>>(B, to_scaled);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_ruiz(const ModelDev &M, const BatchDev &B, int iters, cudaStream_t st) {
   const int threads = 128, wpb = threads / 32;
   k_ruiz<<<(B.batch + wpb - 1) / wpb, threads, 0, st>>>(M, B, iters);

@@ -6,6 +6,7 @@
 namespace rldl {
 size_t factor_smem_doubles(int a, int nx, int ny, int nt);
 size_t admm_smem_doubles(int a, int nx, int ny, int nt);
+cudaError_t launch_rescale_iterates(const BatchDev &B, int to_scaled, cudaStream_t st);
 cudaError_t launch_ruiz(const ModelDev &M, const BatchDev &B, int iters, cudaStream_t st);
 cudaError_t launch_set_rho_vec(const BatchDev &B, int m, int *changed, cudaStream_t st);
 cudaError_t launch_factor(const ModelDev &M, const BatchDev &B, double sigma, int k0,

@@ -450,7 +450,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       __syncwarp(gm);
       if (!term) {
         if (gl < NX) {
-          const double tdv = (zd - rec_div_rho<SH>(yd, sl_, NY + gl, rcl)) -
+          const double tdv = (zd - yd * rec_rinv<SH>(sl_, NY + gl, rcl)) -
                              dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
           td2[gl] = tdv; td2[gl + NX] = tdv;
         }
@@ -605,9 +605,11 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
           if (rr < np) {
             const int ri = roff + rr;
             const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
-            const double rho = rec_rho<SH>(sl_, rr, rcl), zo = zp[t], yo = yp[t];
+            double rho, rinv;
+            rec_rho_pair<SH>(sl_, rr, rcl, rho, rinv);
+            const double zo = zp[t], yo = yp[t];
             const double zh = alpha * zt + oma * zo;
-            const double zn = fmin(fmax(zh + rec_div_rho<SH>(yo, sl_, rr, rcl), sl_[SH::LO + rr]), sl_[SH::UP + rr]);
+            const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
             z[ri] = zn; y[ri] = yo + d;
             zp[t] = zn; yp[t] = yo + d;  // handed to phase A of the next iteration
@@ -616,11 +618,11 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         }
         if (!term && gl < NX) {
           const int ri = roff + NY + gl;
-          const double rho = rec_rho<SH>(sl_, NY + gl, rcl);
-          const double yr = rec_div_rho<SH>(yd, sl_, NY + gl, rcl);
-          const double zt = (zd - yr) + rec_div_rho<SH>(nud, sl_, NY + gl, rcl);
+          double rho, rinv;
+          rec_rho_pair<SH>(sl_, NY + gl, rcl, rho, rinv);
+          const double zt = (zd - yd * rinv) + nud * rinv;
           const double zh = alpha * zt + oma * zd;
-          const double zn = fmin(fmax(zh + yr, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
+          const double zn = fmin(fmax(zh + yd * rinv, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
           const double d = rho * (zh - zn);
           z[ri] = zn; y[ri] = yd + d;
           if (store_delta) dy[ri] = d;

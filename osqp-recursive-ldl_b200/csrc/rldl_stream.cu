@@ -549,7 +549,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         __syncwarp(gm);
         if (!term) {
           if (gl < NX) {
-            const double tdv = (cur.zd - rec_div_rho<SH>(cur.yd, sl_, NY + gl, rcl)) -
+            const double tdv = (cur.zd - cur.yd * rec_rinv<SH>(sl_, NY + gl, rcl)) -
                                dense_mv<A, NX>(Fd + (k == 0 ? 0 : A * NX) + gl, yvs);
             td2[gl] = tdv; td2[gl + NX] = tdv;
           }
@@ -600,9 +600,11 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
           if (rr < np) {
             const int ri = roff + rr;
             const double zt = ell_row<CW>(Cv + cls * ROWS * CW, Ci + cls * ROWS * CW, rr, vcur);
-            const double rho = rec_rho<SH>(sl_, rr, rcl), zo = cur.zp[t], yo = cur.yp[t];
+            double rho, rinv;
+            rec_rho_pair<SH>(sl_, rr, rcl, rho, rinv);
+            const double zo = cur.zp[t], yo = cur.yp[t];
             const double zh = alpha * zt + oma * zo;
-            const double zn = fmin(fmax(zh + rec_div_rho<SH>(yo, sl_, rr, rcl), sl_[SH::LO + rr]), sl_[SH::UP + rr]);
+            const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + rr]), sl_[SH::UP + rr]);
             const double d = rho * (zh - zn);
             z[ri] = zn; y[ri] = yo + d;
             nw.zp[t] = zn; nw.yp[t] = yo + d;
@@ -611,12 +613,12 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
         }
         if (!term && gl < NX) {
           const int ri = roff + NY + gl;
-          const double rho = rec_rho<SH>(sl_, NY + gl, rcl);
+          double rho, rinv;
+          rec_rho_pair<SH>(sl_, NY + gl, rcl, rho, rinv);
           const double zo = cur.zd, yo = cur.yd;
-          const double yr = rec_div_rho<SH>(yo, sl_, NY + gl, rcl);
-          const double zt = (zo - yr) + rec_div_rho<SH>(nud, sl_, NY + gl, rcl);
+          const double zt = (zo - yo * rinv) + nud * rinv;
           const double zh = alpha * zt + oma * zo;
-          const double zn = fmin(fmax(zh + yr, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
+          const double zn = fmin(fmax(zh + yo * rinv, sl_[SH::LO + NY + gl]), sl_[SH::UP + NY + gl]);
           const double d = rho * (zh - zn);
           z[ri] = zn; y[ri] = yo + d;
           nw.zd = zn; nw.yd = yo + d;
@@ -640,12 +642,12 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       double obj = 0.0, rho_new = rho_in;
       Resid R = {0, 0, 0, 0, 0, 0, 0, 0}, Rs = R;  // Rs: the norms of the scaled problem (rho estimate), = R unless SC
       if (can_check) {
-        R = compute_residuals<G>(M, B, inst, gl, gm, rs, &Rs);
+        R = compute_residuals<G, SH::RZ != 0>(M, B, inst, gl, gm, rs, &Rs);
         obj = R.obj;
         if (check_termination<G>(M, B, S, inst, gl, gm, rs, R, 0, &status, &obj)) done = true;
       }
       if (!done && can_adapt) {  // adapt_rho (auxil.c:57-77); the refactorisation itself is a separate launch
-        if (!can_check) { R = compute_residuals<G>(M, B, inst, gl, gm, rs, &Rs); obj = R.obj; }
+        if (!can_check) { R = compute_residuals<G, SH::RZ != 0>(M, B, inst, gl, gm, rs, &Rs); obj = R.obj; }
         const double rn = rho_estimate(Rs, rho_in);
         if (rn > rho_in * S.adaptive_rho_tolerance || rn < rho_in / S.adaptive_rho_tolerance) {
           rho_changed = true;
@@ -659,7 +661,7 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
       }
       if (!done && (iter == S.max_iter || timed_out)) {
         if (!can_check) {
-          R = compute_residuals<G>(M, B, inst, gl, gm, rs, &Rs);
+          R = compute_residuals<G, SH::RZ != 0>(M, B, inst, gl, gm, rs, &Rs);
           obj = R.obj;
           check_termination<G>(M, B, S, inst, gl, gm, rs, R, 0, &status, &obj);
         }
@@ -1117,7 +1119,7 @@ __global__ void __launch_bounds__(128, SH::A <= 16 ? 4 : 3) k_factor_stream(Mode
         for (int c = 0; c < NX; c++) Sx[c] = fma(fi, tb[i * NXE + c], Sx[c]);
       }
       if (gl < NX) {
-        const double rinv = rec_div_rho<SH>(1.0, rk, NY + gl, rcl);
+        const double rinv = rec_rinv<SH>(rk, NY + gl, rcl);
 #pragma unroll
         for (int c = 0; c < NX; c++)
           if (c == gl) Sx[c] += rinv;

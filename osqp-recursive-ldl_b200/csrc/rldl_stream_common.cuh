@@ -141,30 +141,41 @@ __device__ __forceinline__ int row_class(const double *cls, int row) {
   const unsigned long long wv = reinterpret_cast<const unsigned long long *>(cls)[row >> 5];
   return (int)((wv >> (2 * (row & 31))) & 3ull);
 }
-// Step size of row `row` of a stage and a division by it, from the record: the row's class and the instance's three
-// class values (rho, 1e3 rho, 1e-6, with precomputed reciprocals), or — Ruiz-scaled variants — the stored value
-// (and a true division, as the runtime-shape kernels do).
+// Step size of row `row` of a stage and its reciprocal, from the record: the row's class and the instance's class
+// values (rho, 1e3 rho, 1e-6, reciprocals precomputed as in the reference's rho_inv_vec, auxil.c:96), or — Ruiz-scaled
+// variants — the stored per-row value.
 struct RhoClasses {
-  double rho[3], inv[3];
-  __device__ __forceinline__ void set(double rho_in) {
-    rho[0] = rho_in; rho[1] = 1e3 * rho_in; rho[2] = 1e-6;
-    inv[0] = 1.0 / rho[0]; inv[1] = 1.0 / rho[1]; inv[2] = 1.0 / rho[2];
+  double rho_in, rho_eq, inv_in, inv_eq, inv_min;
+  __device__ __forceinline__ void set(double r) {
+    rho_in = r; rho_eq = kRhoEq * r;
+    inv_in = 1.0 / rho_in; inv_eq = 1.0 / rho_eq; inv_min = 1.0 / kRhoMin;
   }
 };
+template <class SH>
+__device__ __forceinline__ void rec_rho_pair(const double *rec, int row, const RhoClasses &rc, double &rho, double &rinv) {
+  if constexpr (SH::RZ) {
+    rho = rec[SH::CLS + row];
+    rinv = 1.0 / rho;
+  } else {
+    const int c = row_class(rec + SH::CLS, row);
+    rho = c == 0 ? rc.rho_in : (c == 1 ? rc.rho_eq : kRhoMin);
+    rinv = c == 0 ? rc.inv_in : (c == 1 ? rc.inv_eq : rc.inv_min);
+  }
+}
 template <class SH>
 __device__ __forceinline__ double rec_rho(const double *rec, int row, const RhoClasses &rc) {
   if constexpr (SH::RZ) return rec[SH::CLS + row];
   else {
     const int c = row_class(rec + SH::CLS, row);
-    return c == 0 ? rc.rho[0] : (c == 1 ? rc.rho[1] : rc.rho[2]);
+    return c == 0 ? rc.rho_in : (c == 1 ? rc.rho_eq : kRhoMin);
   }
 }
 template <class SH>
-__device__ __forceinline__ double rec_div_rho(double v, const double *rec, int row, const RhoClasses &rc) {
-  if constexpr (SH::RZ) return v / rec[SH::CLS + row];
+__device__ __forceinline__ double rec_rinv(const double *rec, int row, const RhoClasses &rc) {
+  if constexpr (SH::RZ) return 1.0 / rec[SH::CLS + row];
   else {
     const int c = row_class(rec + SH::CLS, row);
-    return v * (c == 0 ? rc.inv[0] : (c == 1 ? rc.inv[1] : rc.inv[2]));
+    return c == 0 ? rc.inv_in : (c == 1 ? rc.inv_eq : rc.inv_min);
   }
 }
 template <class SH>
