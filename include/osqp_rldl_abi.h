@@ -497,6 +497,41 @@ c_int rldl_batch_debug_sched(RLDLBatch *b, int *out, c_int n);
 void *rldl_batch_stream(const RLDLBatch *b);
 void  rldl_batch_free(RLDLBatch *b);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Multi-device handle (SURVEY §8e inside the library).  No counterpart in the reference, which is single-threaded
+ * with one workspace per problem (its users parallelise over workspaces, SURVEY §8b "Threading").
+ * The batch is cut into `nshards` contiguous shards (0 = one per device), shard s on devices[s % ndev]
+ * (devices = NULL: every visible device); each call below runs its per-shard rldl_batch_* calls on one host thread
+ * per shard and returns when all have.  Instances share nothing: there is no collective and no peer-to-peer
+ * traffic, every shard writes its own rows of the caller's arrays (layouts as in the rldl_batch_* calls, whole
+ * batch).  Pinned host arrays make rldl_multi_solve_to_host deliver from inside the kernels on every device.
+ * --------------------------------------------------------------------------------------------------------- */
+typedef struct RLDLMulti RLDLMulti;
+c_int rldl_multi_setup(RLDLMulti **out, const c_int *devices, c_int ndev, c_int nshards, const OSQPDataRLDL *model,
+                       const OSQPSettings *settings, c_int Nmax, c_int N, c_int nx, c_int nu, c_int ny, c_int nt,
+                       c_int batch, const c_float *q, const c_float *l, const c_float *u, const c_float *rho);
+/* number of shards; first[s] = first instance of shard s, device[s] = its device (either may be NULL) */
+c_int rldl_multi_shards(const RLDLMulti *m, c_int *first, c_int *device);
+/* the shard's own handle, for the rldl_batch_* calls that have no multi form (tuning, diagnostics) */
+RLDLBatch *rldl_multi_shard_handle(RLDLMulti *m, c_int shard);
+c_int rldl_multi_solve(RLDLMulti *m);
+c_int rldl_multi_solve_to_host(RLDLMulti *m, c_float *x, c_float *y, c_int *iter, c_int *status_val,
+                               c_float *obj_val, c_float *pri_res, c_float *dua_res, c_int *rho_updates,
+                               c_float *rho_estimate);
+c_int rldl_multi_get_solution(RLDLMulti *m, c_float *x, c_float *y);
+c_int rldl_multi_get_info(RLDLMulti *m, c_int *iter, c_int *status_val, c_float *obj_val, c_float *pri_res,
+                          c_float *dua_res, c_int *rho_updates, c_float *rho_estimate);
+c_int rldl_multi_update_bounds(RLDLMulti *m, const c_float *l, const c_float *u);
+c_int rldl_multi_partial_update_bounds(RLDLMulti *m, c_int start, c_int stop, const c_float *l, const c_float *u);
+c_int rldl_multi_update_lin_cost(RLDLMulti *m, const c_float *q);
+c_int rldl_multi_warm_start(RLDLMulti *m, const c_float *x, const c_float *y);
+c_int rldl_multi_warm_start_shift(RLDLMulti *m);
+c_int rldl_multi_update_horizon(RLDLMulti *m, c_int N);
+c_int rldl_multi_update_rho(RLDLMulti *m, const c_float *rho);
+c_int rldl_multi_refactor(RLDLMulti *m);
+c_int rldl_multi_update_settings(RLDLMulti *m, const OSQPSettings *settings);
+void  rldl_multi_free(RLDLMulti *m);
+
 /* device plumbing */
 c_int rldl_device_count(void);
 c_int rldl_set_device(c_int device);

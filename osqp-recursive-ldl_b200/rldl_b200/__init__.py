@@ -115,6 +115,10 @@ rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_warm_start_shift rld
 rldl_batch_refactor rldl_batch_update_model rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_kkt_solve_static rldl_batch_max_static_doubles rldl_batch_get_solution rldl_batch_get_info
 rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel rldl_batch_set_tuning rldl_batch_lane_stats rldl_batch_get_trace rldl_batch_debug_sched rldl_batch_get_scaling rldl_batch_get_polish
 rldl_batch_free
+rldl_multi_setup rldl_multi_shards rldl_multi_shard_handle rldl_multi_solve rldl_multi_solve_to_host
+rldl_multi_get_solution rldl_multi_get_info rldl_multi_update_bounds rldl_multi_partial_update_bounds
+rldl_multi_update_lin_cost rldl_multi_warm_start rldl_multi_warm_start_shift rldl_multi_update_horizon
+rldl_multi_update_rho rldl_multi_refactor rldl_multi_update_settings rldl_multi_free
 rldl_device_count rldl_set_device rldl_version
 """.split()
 
@@ -188,16 +192,35 @@ def lib():
         "rldl_batch_last_times": [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)],
         "rldl_batch_counters": [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(c_int)],
         "rldl_batch_free": [vp],
+        "rldl_multi_setup": [C.POINTER(vp), vp, c_int, c_int, C.POINTER(OSQPDataRLDL), C.POINTER(OSQPSettings)] +
+                            [c_int] * 7 + [vp] * 4,
+        "rldl_multi_shards": [vp, vp, vp],
+        "rldl_multi_solve": [vp],
+        "rldl_multi_solve_to_host": [vp] * 10,
+        "rldl_multi_get_solution": [vp, vp, vp],
+        "rldl_multi_get_info": [vp] * 8,
+        "rldl_multi_update_bounds": [vp, vp, vp],
+        "rldl_multi_partial_update_bounds": [vp, c_int, c_int, vp, vp],
+        "rldl_multi_update_lin_cost": [vp, vp],
+        "rldl_multi_warm_start": [vp, vp, vp],
+        "rldl_multi_warm_start_shift": [vp],
+        "rldl_multi_update_horizon": [vp, c_int],
+        "rldl_multi_update_rho": [vp, vp],
+        "rldl_multi_refactor": [vp],
+        "rldl_multi_update_settings": [vp, C.POINTER(OSQPSettings)],
+        "rldl_multi_free": [vp],
     }
     for name, args in sig.items():
         fn = getattr(L, name)
         fn.argtypes = args
         fn.restype = None if name in ("get_L_dimensions", "rldl_batch_dims", "rldl_batch_last_times",
-                                      "rldl_batch_counters", "rldl_batch_free") else c_int
+                                      "rldl_batch_counters", "rldl_batch_free", "rldl_multi_free") else c_int
     L.rldl_batch_select_kernel.argtypes = [vp, c_int]
     L.rldl_batch_select_kernel.restype = c_int
     L.rldl_batch_set_tuning.argtypes = [vp, C.c_char_p, c_int]
     L.rldl_batch_set_tuning.restype = c_int
+    L.rldl_multi_shard_handle.argtypes = [vp, c_int]
+    L.rldl_multi_shard_handle.restype = vp
     L.rldl_batch_max_static_doubles.argtypes = []
     L.rldl_batch_max_static_doubles.restype = c_int
     L.rldl_batch_stream.argtypes = [vp]
@@ -401,3 +424,57 @@ class Batch:
             self.free()
         except Exception:
             pass
+
+
+class Multi:
+    """A batch sharded over devices inside the library (rldl_multi_* in the C ABI)."""
+
+    def __init__(self, model, N, Nmax, q, l, u, settings: OSQPSettings, devices=None, nshards=0, rho=None):
+        L = lib()
+        self.sm = StageModel(model)
+        self.batch, self.nmax, self.mmax = q.shape[0], q.shape[1], l.shape[1]
+        q, l, u = (np.ascontiguousarray(v, np.float64) for v in (q, l, u))
+        rho = None if rho is None else np.ascontiguousarray(rho, np.float64)
+        dev = None if devices is None else np.ascontiguousarray(devices, np.int64)
+        h = C.c_void_p()
+        rc = L.rldl_multi_setup(C.byref(h), _p(dev), 0 if dev is None else len(dev), nshards, C.byref(self.sm.data),
+                                C.byref(settings), Nmax, N, model.nx, model.nu, model.ny, model.nt, self.batch,
+                                _p(q), _p(l), _p(u), _p(rho))
+        if rc:
+            raise RuntimeError(f"rldl_multi_setup failed with code {rc}")
+        self.h = h
+
+    def shards(self):
+        n = lib().rldl_multi_shards(self.h, None, None)
+        first, dev = np.zeros(n, np.int64), np.zeros(n, np.int64)
+        lib().rldl_multi_shards(self.h, _p(first), _p(dev))
+        return first.tolist(), dev.tolist()
+
+    def empty_out(self):
+        B = self.batch
+        return dict(x=np.zeros((B, self.nmax)), y=np.zeros((B, self.mmax)), iter=np.zeros(B, np.int64),
+                    status=np.zeros(B, np.int64), obj=np.zeros(B), pri_res=np.zeros(B), dua_res=np.zeros(B),
+                    rho_updates=np.zeros(B, np.int64), rho_estimate=np.zeros(B))
+
+    _KEYS = ("x", "y", "iter", "status", "obj", "pri_res", "dua_res", "rho_updates", "rho_estimate")
+
+    def solve(self):
+        return lib().rldl_multi_solve(self.h)
+
+    def solve_to_host(self, out):
+        return lib().rldl_multi_solve_to_host(self.h, *[_p(out[k]) for k in self._KEYS])
+
+    def get(self):
+        out = self.empty_out()
+        assert lib().rldl_multi_get_solution(self.h, _p(out["x"]), _p(out["y"])) == 0
+        assert lib().rldl_multi_get_info(self.h, *[_p(out[k]) for k in self._KEYS[2:]]) == 0
+        return out
+
+    def call(self, name, *arrays_or_ints):
+        args = [_p(np.ascontiguousarray(a)) if isinstance(a, np.ndarray) else a for a in arrays_or_ints]
+        return getattr(lib(), "rldl_multi_" + name)(self.h, *args)
+
+    def free(self):
+        if self.h:
+            lib().rldl_multi_free(self.h)
+            self.h = None

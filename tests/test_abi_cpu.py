@@ -19,7 +19,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def header_symbols():
     txt = open(os.path.join(ROOT, "include", "osqp_rldl_abi.h")).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
-    names = re.findall(r"^\s*(?:const\s+)?(?:c_int|void|char|csc)\s*\*?\s*(\w+)\s*\(", txt, flags=re.M)
+    names = re.findall(r"^\s*(?:const\s+)?(?:c_int|void|char|csc|RLDLBatch)\s*\*?\s*(\w+)\s*\(", txt, flags=re.M)
     return sorted(set(n for n in names if not n.startswith("(")))
 
 
