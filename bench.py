@@ -10,8 +10,8 @@ One step = the hot path over the whole batch: full stage-wise KKT factorisation
 (rldl_batch_refactor) + cold-start ADMM solve to convergence (rldl_batch_solve).
   value  : instances solved per second, data resident in HBM (CUDA events on the
            library's launching stream, max over ranks)
-  e2e    : same through the host-buffer API: rldl_batch_update_bounds(l,u) +
-           rldl_batch_update_lin_cost(q) from pinned host memory, refactor,
+  e2e    : same through the host-buffer API: rldl_batch_update_data_refactor(q, l, u) from pinned host
+           memory (= update_bounds + update_lin_cost + refactor, upload pipelined against the device work),
            rldl_batch_solve_to_host(x, y, info) into pinned host memory
 --impl reference times the UNMODIFIED reference (oracle/_ref: osqp_setup_recursive +
 osqp_solve_recursive) on the host cores over a bounded sample of the same instances.
@@ -468,9 +468,9 @@ def main_b200(args):
         return gb.last_times()
 
     def step_e2e():
-        assert lib.rldl_batch_update_bounds(gb.h, P(l_h), P(u_h)) == 0
-        assert lib.rldl_batch_update_lin_cost(gb.h, P(q_h)) == 0
-        assert gb.refactor() == 0
+        # new q, l, u for every instance + full stage recursion: the upload runs in chunks on a second stream while
+        # typing / record pass and recursion of the previous chunk run (= update_bounds + update_lin_cost + refactor)
+        assert lib.rldl_batch_update_data_refactor(gb.h, P(q_h), P(l_h), P(u_h)) == 0
         # fused solve-and-deliver: x, y and info of every instance land in the pinned host arrays as the instance
         # finishes (device-initiated writes over PCIe), i.e. the D2H transfer is inside the solve
         assert lib.rldl_batch_solve_to_host(gb.h, P(x_h), P(y_h), *[P(info_h[k]) for k in

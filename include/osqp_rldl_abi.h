@@ -393,6 +393,13 @@ c_int rldl_batch_partial_update_bounds(RLDLBatch *b, c_int start, c_int stop,
                                        const c_float *l /* [batch][stop-start] */,
                                        const c_float *u);
 c_int rldl_batch_update_lin_cost(RLDLBatch *b, const c_float *q);
+/* rldl_batch_update_bounds(l, u) + rldl_batch_update_lin_cost(q) + rldl_batch_refactor() in one call (the per-step
+ * update of a controller that re-poses every instance: reference osqp_update_bounds osqp.c:784, osqp_update_lin_cost
+ * :752, then the full stage recursion), pipelined: the arrays are uploaded in chunks on a second stream while the
+ * typing / record pass and the recursion of the previous chunk run.  Pinned host arrays make the copies
+ * asynchronous.  l <= u is validated on the device; a refused update (return 1) leaves the bounds as they were
+ * (the linear cost of the call has been taken). */
+c_int rldl_batch_update_data_refactor(RLDLBatch *b, const c_float *q, const c_float *l, const c_float *u);
 /* batched osqp_warm_start (x or y may be NULL: osqp_warm_start_y / _x) */
 c_int rldl_batch_warm_start(RLDLBatch *b, const c_float *x, const c_float *y);
 /* receding-horizon warm start without a host round trip: the resident (x, y) of the last solve are

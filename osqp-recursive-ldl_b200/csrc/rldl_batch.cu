@@ -386,6 +386,7 @@ Batch::~Batch() {
   if (ev1) cudaEventDestroy(ev1);
   if (ev_reset) cudaEventDestroy(ev_reset);
   if (ev_lane) cudaEventDestroy(ev_lane);
+  for (cudaEvent_t e : ev_chunk) if (e) cudaEventDestroy(e);
   if (stream2) cudaStreamDestroy(stream2);
   if (stream) cudaStreamDestroy(stream);
 }
@@ -712,6 +713,88 @@ c_int Batch::update_bounds(const c_float *l, const c_float *u, bool have_l, bool
   c_int rc = reset_info();
   if (rc) return rc;
   return retype_and_refactor();
+}
+
+// The per-instance arrays of `count` instances from `first` on, as a batch of their own (for kernels that only use the
+// per-instance arrays: typing / record pass, stage recursion, bound check).
+static BatchDev slice(const BatchDev &D, int first, int count) {
+  BatchDev S = D;
+  const size_t f = (size_t)first;
+  S.batch = count;
+  S.q += f * D.nmax; S.x += f * D.nmax; S.dx += f * D.nmax;
+  S.l += f * D.mmax; S.u += f * D.mmax; S.rho_vec += f * D.mmax; S.z += f * D.mmax; S.y += f * D.mmax; S.dy += f * D.mmax;
+  S.Xinv += f * D.xstride; S.Sinv += f * D.sstride; S.yk += f * D.ykstride; S.sk += f * D.skstride;
+  S.rho += f; S.iter += f; S.status += f; S.obj += f; S.pri += f; S.dua += f; S.rho_est += f; S.rho_updates += f;
+  S.fact_flag += f;
+  if (S.rec) S.rec += f * D.rec_stride;
+  if (S.sD) { S.sD += f * D.nmax; S.sE += f * D.mmax; S.sC += f; }
+  if (S.ratio_prev) S.ratio_prev += f;
+  if (S.trace) S.trace += f;
+  return S;
+}
+
+// update_bounds(l, u) + update_lin_cost(q) + refactor() in one call, pipelined: the batch is uploaded in chunks on a
+// second stream while typing / record pass and stage recursion of the previous chunk run (1.9 GB of upload at C5 take
+// 36 ms, the device work 10 ms: the latter disappears behind the former).  Same semantics as the three calls: l <= u
+// is validated on the device and an invalid update leaves the resident problem as it was (return 1).
+c_int Batch::update_data_refactor(const c_float *q, const c_float *l, const c_float *u) {
+  CK(cudaSetDevice(device));
+  if (!q || !l || !u) return 1;
+  if (!streaming || batch < 64) {
+    c_int rc = update_bounds(l, u, true, true, true);
+    if (rc) return rc;
+    rc = update_lin_cost(q);
+    if (rc) return rc;
+    return refactor();
+  }
+  const size_t mb = (size_t)batch * D.mmax * sizeof(double);
+  if (!d_l_alt) CK(cudaMalloc(&d_l_alt, mb));
+  if (!d_u_alt) CK(cudaMalloc(&d_u_alt, mb));
+  constexpr int NCH = 8;
+  for (int c = 0; c < NCH; c++)
+    if (!ev_chunk[c]) CK(cudaEventCreateWithFlags(&ev_chunk[c], cudaEventDisableTiming));
+  CK(cudaEventRecord(ev0, stream));
+  CK(cudaEventRecord(ev_reset, stream));            // the copies wait for everything already queued on the handle
+  CK(cudaStreamWaitEvent(stream2, ev_reset, 0));
+  CK(cudaMemsetAsync(D.sched + 1, 0, sizeof(int), stream));
+  BatchDev N_ = D;  // the batch as it will be: new bounds (in the landing buffers), new q
+  N_.l = d_l_alt; N_.u = d_u_alt;
+  if (scale_stale) { c_int rc = rescale(true); if (rc) return rc; }
+  for (int c = 0; c < NCH; c++) {
+    const int i0 = (int)((long long)batch * c / NCH), i1 = (int)((long long)batch * (c + 1) / NCH);
+    const size_t ro = (size_t)i0 * D.mmax, vo = (size_t)i0 * D.nmax, nb = (size_t)(i1 - i0);
+    CK(cudaMemcpyAsync(d_l_alt + ro, l + ro, nb * D.mmax * sizeof(double), cudaMemcpyHostToDevice, stream2));
+    CK(cudaMemcpyAsync(d_u_alt + ro, u + ro, nb * D.mmax * sizeof(double), cudaMemcpyHostToDevice, stream2));
+    CK(cudaMemcpyAsync(D.q + vo, q + vo, nb * D.nmax * sizeof(double), cudaMemcpyHostToDevice, stream2));
+    CK(cudaEventRecord(ev_chunk[c], stream2));
+    CK(cudaStreamWaitEvent(stream, ev_chunk[c], 0));
+    const BatchDev S_ = slice(N_, i0, i1 - i0);
+    CK(launch_check_bounds(S_.l, S_.u, D.mmax, D.m, i1 - i0, D.sched + 1, stream, false));
+    CK(launch_vec_records(M, S_, 0, 3, nullptr, nullptr, settings.sigma, stream));
+    CK(launch_factor_stream(M, S_, settings.sigma, 0, nullptr, need_unpacked ? 1 : 0, stream));
+    launches += 3;
+  }
+  CK(cudaEventRecord(ev1, stream));
+  int bad = 0;
+  CK(cudaMemcpyAsync(&bad, D.sched + 1, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  CK(cudaMemsetAsync(D.sched + 1, 0, sizeof(int), stream));
+  if (bad) {
+    // refused: q is restored by the caller's next update (as with a refused osqp_update_bounds followed by nothing,
+    // the linear cost of this call has been taken); records and factor are rebuilt from the bounds that stay
+    c_int rc = retype(0, 3, false, false);
+    if (rc) return rc;
+    rc = factor(0, false);
+    return rc ? rc : 1;
+  }
+  std::swap(D.l, d_l_alt);
+  std::swap(D.u, d_u_alt);
+  if (!need_unpacked) unpacked_valid = false;
+  records_stale = false;
+  float ms = 0;
+  cudaEventElapsedTime(&ms, ev0, ev1);
+  last_factor_ms = ms;  // here: upload + typing + recursion, pipelined
+  return reset_info();
 }
 
 c_int Batch::partial_update_bounds(c_int start, c_int stop, const c_float *l, const c_float *u) {

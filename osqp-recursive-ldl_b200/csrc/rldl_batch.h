@@ -89,6 +89,8 @@ struct Batch {
   c_int update_bounds(const c_float *l, const c_float *u, bool have_l, bool have_u, bool validate = false);
   c_int partial_update_bounds(c_int start, c_int stop, const c_float *l, const c_float *u);
   c_int update_lin_cost(const c_float *q);
+  c_int update_data_refactor(const c_float *q, const c_float *l, const c_float *u);
+  cudaEvent_t ev_chunk[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   c_int warm_start(const c_float *x, const c_float *y);
   c_int warm_start_shift();
   c_int update_horizon(c_int Nnew);

@@ -807,6 +807,12 @@ c_int rldl_batch_partial_update_bounds(RLDLBatch *h, c_int start, c_int stop, co
   return h->b->partial_update_bounds(start, stop, l, u);
 }
 c_int rldl_batch_update_lin_cost(RLDLBatch *h, const c_float *q) { HB(h); return h->b->update_lin_cost(q); }
+c_int rldl_batch_update_data_refactor(RLDLBatch *h, const c_float *q, const c_float *l, const c_float *u) {
+  HB(h);
+  const c_int rc = h->b->update_data_refactor(q, l, u);
+  if (rc == 1) fprintf(stderr, "ERROR in rldl_batch_update_data_refactor: lower bound must be lower than or equal to upper bound\n");
+  return rc;
+}
 c_int rldl_batch_warm_start(RLDLBatch *h, const c_float *x, const c_float *y) { HB(h); return h->b->warm_start(x, y); }
 c_int rldl_batch_warm_start_shift(RLDLBatch *h) { HB(h); return h->b->warm_start_shift(); }
 c_int rldl_batch_update_horizon(RLDLBatch *h, c_int N) { HB(h); return h->b->update_horizon(N); }

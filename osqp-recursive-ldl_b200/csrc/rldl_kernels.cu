@@ -654,8 +654,8 @@ cudaError_t launch_warm_start_z(const ModelDev &M, const BatchDev &B, cudaStream
 }
 
 cudaError_t launch_check_bounds(const double *l, const double *u, int ld, int m, int batch, int *bad,
-                                cudaStream_t st) {
-  cudaError_t e = cudaMemsetAsync(bad, 0, sizeof(int), st);
+                                cudaStream_t st, bool reset) {
+  cudaError_t e = reset ? cudaMemsetAsync(bad, 0, sizeof(int), st) : cudaSuccess;
   if (e != cudaSuccess) return e;
   k_check_bounds<<<148 * 8, 256, 0, st>>>(l, u, ld, m, batch, bad);
   return cudaGetLastError();

@@ -23,7 +23,7 @@ cudaError_t launch_kkt_solve(const ModelDev &M, const BatchDev &B, const Setting
                              int ld, cudaStream_t st);
 cudaError_t launch_warm_start_z(const ModelDev &M, const BatchDev &B, cudaStream_t st);
 cudaError_t launch_check_bounds(const double *l, const double *u, int ld, int m, int batch, int *bad,
-                                cudaStream_t st);
+                                cudaStream_t st, bool reset = true);
 cudaError_t launch_shift_rows(double *v, int ld, int len, int sh, int batch, cudaStream_t st);
 cudaError_t launch_fill(double *p, double v, size_t n, cudaStream_t st);
 cudaError_t launch_mark_time(const BatchDev &B, cudaStream_t st);

@@ -111,7 +111,7 @@ osqp_setup_recursive osqp_solve_recursive osqp_update_recursive osqp_setup_combi
 osqp_solve_combine_recursive osqp_update_Z_horizon osqp_update_X_horizon
 osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions cleanup_rldl
 rldl_batch_setup rldl_batch_solve rldl_batch_solve_to_host rldl_batch_update_bounds rldl_batch_partial_update_bounds
-rldl_batch_update_lin_cost rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
+rldl_batch_update_lin_cost rldl_batch_update_data_refactor rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
 rldl_batch_refactor rldl_batch_update_model rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_kkt_solve_static rldl_batch_max_static_doubles rldl_batch_get_solution rldl_batch_get_info
 rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel rldl_batch_set_tuning rldl_batch_lane_stats rldl_batch_get_trace rldl_batch_debug_sched rldl_batch_get_scaling rldl_batch_get_polish
 rldl_batch_free
@@ -172,6 +172,7 @@ def lib():
         "rldl_batch_update_bounds": [vp, vp, vp],
         "rldl_batch_partial_update_bounds": [vp, c_int, c_int, vp, vp],
         "rldl_batch_update_lin_cost": [vp, vp],
+        "rldl_batch_update_data_refactor": [vp, vp, vp, vp],
         "rldl_batch_warm_start": [vp, vp, vp],
         "rldl_batch_warm_start_shift": [vp],
         "rldl_batch_update_horizon": [vp, c_int],
@@ -323,6 +324,10 @@ class Batch:
 
     def update_lin_cost(self, q):
         return lib().rldl_batch_update_lin_cost(self.h, _p(np.ascontiguousarray(q)))
+
+    def update_data_refactor(self, q, l, u):
+        return lib().rldl_batch_update_data_refactor(self.h, _p(np.ascontiguousarray(q)), _p(np.ascontiguousarray(l)),
+                                                     _p(np.ascontiguousarray(u)))
 
     def warm_start(self, x=None, y=None):
         x = None if x is None else np.ascontiguousarray(x)

@@ -9,6 +9,11 @@ from common import gpu_settings, ref_run, problem, compare, rel_err
 pytestmark = pytest.mark.gpu
 
 
+def mpc_x0(mdl, batch, seed):
+    from rldl_b200 import mpc
+    return mpc.sample_x0(mdl, batch, seed)
+
+
 @pytest.mark.parametrize("name,batch", [("C1", 8), ("C3", 6), ("C4", 6)])
 def test_kkt_solve_matches_reference(name, batch):
     """One KKT solve incl. the z_tilde step (qdldl_interface.c:559-585) on random rhs."""
@@ -215,3 +220,34 @@ def test_lane_first_use_in_a_fresh_process_does_not_deadlock():
     cp = subprocess.run([sys.executable, os.path.join(root, "tools", "exp_hang.py"), "8", "1"], capture_output=True,
                         text=True, timeout=150)
     assert cp.returncode == 0 and "ALL DONE" in cp.stdout, (cp.returncode, cp.stdout[-800:], cp.stderr[-800:])
+
+
+@pytest.mark.parametrize("name,batch", [("C1", 3000), ("C3", 500), ("C1", 20)])
+def test_update_data_refactor_equals_the_three_calls(name, batch):
+    """rldl_batch_update_data_refactor (chunked upload pipelined against typing / records / recursion) ==
+    rldl_batch_update_bounds + rldl_batch_update_lin_cost + rldl_batch_refactor; a refused update keeps the bounds."""
+    import torch
+    mdl, N, x0, q, l, u = problem(name, batch)
+    _, l2, u2 = mdl.vectors(mpc_x0(mdl, batch, 55), N)
+    q2 = q + 0.05 * np.random.default_rng(4).standard_normal(q.shape)
+    b = mdl.nx + mdl.ny
+    l2[:, b:b + mdl.nx] = -1e30; u2[:, b:b + mdl.nx] = 1e30      # stage-1 state box loose: row classes change
+    a = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+    c = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+    assert a.solve() == 0 and c.solve() == 0
+    assert a.update_bounds(l2, u2) == 0 and a.update_lin_cost(q2) == 0 and a.refactor() == 0 and a.solve() == 0
+    pin = lambda v: torch.from_numpy(np.ascontiguousarray(v)).pin_memory().numpy()
+    assert c.update_data_refactor(pin(q2), pin(l2), pin(u2)) == 0
+    assert (c.get()["status"] == -10).all()                        # info reset, like the reference's updates
+    assert c.solve() == 0
+    n, m, _, _ = a.dims()
+    wa, wc = a.get(), c.get()
+    assert (wa["iter"] == wc["iter"]).all() and (wa["status"] == wc["status"]).all()
+    assert np.abs(wa["x"] - wc["x"]).max() < 1e-9 and np.abs(wa["y"] - wc["y"]).max() < 1e-9
+    lbad = l2.copy()
+    lbad[batch // 2, mdl.ny - 1] = u2[batch // 2, mdl.ny - 1] + 1.0    # an input row of stage 0 (finite bounds)
+    assert c.update_data_refactor(q2, lbad, u2) == 1
+    assert c.solve() == 0
+    wc2 = c.get()
+    assert (wc2["iter"] == wc["iter"]).all() and np.abs(wc2["x"] - wc["x"]).max() < 1e-9
+    a.free(); c.free()
