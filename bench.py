@@ -465,7 +465,7 @@ def main_b200(args):
     def step_device():
         assert gb.refactor() == 0
         assert gb.solve() == 0
-        return gb.last_times()
+        return gb.last_times() + gb.stream_stats()
 
     def step_e2e():
         # new q, l, u for every instance + full stage recursion: the upload runs in chunks on a second stream while
@@ -528,7 +528,14 @@ def main_b200(args):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    achieved = iter_sum * admm_bytes / (s_ms * 1e-3) / 1e9
+    # the dominant kernel alone: CUDA events around the k_admm_stream launch and the instance-iterations that kernel
+    # executed itself, both from the library (rldl_batch_stream_stats); the iterations of the latency-mode tail are
+    # not counted at the streaming kernel's bytes
+    st_ms = float(np.mean([p[2] for p in parts])); st_iters = float(np.mean([p[3] for p in parts]))
+    if st_ms > 0:
+        achieved = st_iters * admm_bytes / (st_ms * 1e-3) / 1e9
+    else:  # the shard was small enough for the latency-mode kernel alone
+        achieved = iter_sum * admm_bytes / (s_ms * 1e-3) / 1e9
     # DRAM traffic of the same kernel: dram__bytes_read + dram__bytes_write of its committed `ncu --set full`
     # capture at uniform load (profiles/r02_stream_ncu_full_uniform_c5_batch16384.txt: 383.68 + 65.95 GB for
     # 1.6384 M instance-iterations x 235 872 algorithmic bytes = x1.163), scaled to this launch.  Only quoted for
@@ -537,7 +544,7 @@ def main_b200(args):
     traffic_source = "no ncu capture for this shape / record layout"
     if abs(admm_bytes - 235872.0) < 1.0:
         traffic_ratio = (383.681287e9 + 65.951344e9) / (16384 * 100 * 235872.0)
-        traffic = traffic_ratio * iter_sum * admm_bytes
+        traffic = traffic_ratio * (st_iters if st_ms > 0 else iter_sum) * admm_bytes
         traffic_source = ("ncu dram__bytes_read+write of this kernel at batch 16384, uniform 100 iterations "
                           "(x%.3f of algorithmic), scaled by this launch's instance-iterations" % traffic_ratio)
     # FP64 peak of the box: tools/micro/dfma.cu, measured on this pool's B200 (profiles/r02_dfma_peak_b200.txt)
@@ -547,8 +554,11 @@ def main_b200(args):
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
             "traffic": traffic, "traffic_source": traffic_source,
-            "launch_ms": s_ms, "algorithmic_bytes_per_launch": iter_sum * admm_bytes,
-            "note": "iterations finished by the latency-mode kernel (factor resident in shared memory) are counted at the streaming kernel's bytes; they are about 1 % of a single-GPU step",
+            "launch_ms": st_ms if st_ms > 0 else s_ms,
+            "algorithmic_bytes_per_launch": (st_iters if st_ms > 0 else iter_sum) * admm_bytes,
+            "instance_iterations_in_this_kernel": st_iters, "instance_iterations_of_the_solve": iter_sum,
+            "solve_ms_all_admm_kernels": s_ms,
+            "note": "achieved = instance-iterations executed by k_admm_stream itself x bytes per instance-iteration / its own CUDA-event duration (rldl_batch_stream_stats); the latency-mode kernels that finish the tail (factor resident in shared memory) are inside solve_ms_all_admm_kernels but not in this figure",
             "factor_kernel": {"kernel": "k_factor_stream (stage recursion, FP64 / shared-memory bound: ~7 flop/B; profiles/r02_factor_ncu_full_c5_batch16384.txt)",
                               "launch_ms": f_ms, "achieved": factor_bytes / (f_ms * 1e-3) / 1e9,
                               "frac": factor_bytes / (f_ms * 1e-3) / 1e9 / peak,

@@ -465,6 +465,10 @@ c_int rldl_batch_update_settings(RLDLBatch *b, const OSQPSettings *settings);
 void  rldl_batch_dims(const RLDLBatch *b, c_int *n, c_int *m, c_int *N, c_int *batch);
 /* device time of the last factorisation / ADMM launch in milliseconds (CUDA events) */
 void  rldl_batch_last_times(const RLDLBatch *b, double *factor_ms, double *solve_ms);
+/* the streaming ADMM kernel of the last solve alone: its device time (CUDA events around the launch) and the ADMM
+ * iterations, summed over instances, it executed itself (the rest of the solve's iterations ran in the latency-mode
+ * kernel) — the pair the kernel's roofline figure is computed from; 0 / 0 if the solve did not use that kernel */
+void  rldl_batch_stream_stats(const RLDLBatch *b, double *stream_ms, double *stream_instance_iterations);
 /* algorithmic bytes per instance and ADMM iteration, algorithmic bytes of
  * the last factorisation launch, and kernels launched so far on this handle */
 void  rldl_batch_counters(const RLDLBatch *b, double *admm_bytes, double *factor_bytes, c_int *launches);

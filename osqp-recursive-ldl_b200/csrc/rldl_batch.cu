@@ -326,6 +326,7 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(cudaEventCreate(&B->ev0)); CK(cudaEventCreate(&B->ev1));
   CK(cudaEventCreateWithFlags(&B->ev_reset, cudaEventDisableTiming));
   CK(cudaEventCreateWithFlags(&B->ev_lane, cudaEventDisableTiming));
+  CK(cudaEventCreate(&B->ev_s0)); CK(cudaEventCreate(&B->ev_s1));
   B->set_sizes();
   B->push_settings();
   // per-instance data
@@ -386,6 +387,8 @@ Batch::~Batch() {
   if (ev1) cudaEventDestroy(ev1);
   if (ev_reset) cudaEventDestroy(ev_reset);
   if (ev_lane) cudaEventDestroy(ev_lane);
+  if (ev_s0) cudaEventDestroy(ev_s0);
+  if (ev_s1) cudaEventDestroy(ev_s1);
   for (cudaEvent_t e : ev_chunk) if (e) cudaEventDestroy(e);
   if (stream2) cudaStreamDestroy(stream2);
   if (stream) cudaStreamDestroy(stream);
@@ -504,6 +507,8 @@ c_int Batch::solve() {
     const int lane = lat_ok ? std::min(std::max(lat_lane, 0), sms - 8) : 0;
     const size_t t_per_cta = (size_t)latency_t_blocks(Nmax) * nx * (nx + 2);
     if (lat_ok && !d_latT) CK(cudaMalloc(&d_latT, (size_t)(2 * sms) * t_per_cta * sizeof(double)));
+    stream_timed = false;
+    last_stream_ms = 0; last_stream_iters = 0;
     int unfinished = batch, resume = 0;
     CK(cudaMemcpyAsync(D.sched + kSchedUnfinished, &unfinished, sizeof(int), cudaMemcpyHostToDevice, stream));
     for (;;) {
@@ -515,8 +520,11 @@ c_int Batch::solve() {
         if (run_lane) CK(preload_lane_kernels());  // before anything of this round runs (see below)
         const int retire = lat_retire_below > 0 ? lat_retire_below : 6 * lat_below;
         const int park = !lat_ok ? 0 : ((run_lane && lane_tail > 0) ? std::min(lat_below, lane_tail) : lat_below);
+        CK(cudaEventRecord(ev_s0, stream));
         CK(launch_admm_stream(M, D, S, (int)settings.warm_start, resume, park, tune,
                               run_lane ? lane : 0, retire, run_lane ? ev_reset : nullptr, &s_ctas, stream));
+        CK(cudaEventRecord(ev_s1, stream));
+        stream_timed = true;
         launches++;
         if (run_lane) {
           // The lane CTAs spin until a kernel launched AFTER them (k_set_tail_flag) has run.  With CUDA's lazy module
@@ -562,6 +570,13 @@ c_int Batch::solve() {
   float ms = 0;
   cudaEventElapsedTime(&ms, ev0, ev1);
   last_solve_ms = ms;
+  if (use_stream() && stream_timed) {  // the streaming kernel of the (last) round alone
+    cudaEventElapsedTime(&ms, ev_s0, ev_s1);
+    last_stream_ms = ms;
+    unsigned long long it = 0;
+    CK(cudaMemcpy(&it, D.sched + kSchedStreamIters, sizeof(it), cudaMemcpyDeviceToHost));
+    last_stream_iters = (double)it;
+  }
   last_polish_ms = 0;
   if (settings.polish) return polish();  // osqp.c:589-591: only the instances that ended OSQP_SOLVED
   return 0;

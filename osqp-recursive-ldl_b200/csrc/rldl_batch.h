@@ -24,7 +24,9 @@ struct Batch {
   c_int set_trace(bool on);
   c_int get_trace(c_float *t);
   cudaStream_t stream2 = nullptr;  // the lane's stream (lower priority than `stream`)
-  cudaEvent_t ev_reset = nullptr, ev_lane = nullptr;
+  cudaEvent_t ev_reset = nullptr, ev_lane = nullptr, ev_s0 = nullptr, ev_s1 = nullptr;
+  bool stream_timed = false;
+  double last_stream_ms = 0, last_stream_iters = 0;  // the streaming kernel of the last solve alone: time, instance-iterations
   bool streaming = false;  // shapes the streaming kernels cover (rldl_stream.cu)
   bool need_unpacked = false;   // a generic-kernel consumer wants Xinv/Sinv unpacked as well as the records
   bool unpacked_valid = false;  // D.Xinv / D.Sinv match the current factorisation

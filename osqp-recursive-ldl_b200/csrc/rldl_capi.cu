@@ -854,6 +854,11 @@ void rldl_batch_last_times(const RLDLBatch *h, double *factor_ms, double *solve_
   if (factor_ms) *factor_ms = h->b->last_factor_ms;
   if (solve_ms) *solve_ms = h->b->last_solve_ms;
 }
+void rldl_batch_stream_stats(const RLDLBatch *h, double *stream_ms, double *stream_instance_iterations) {
+  if (!h || !h->b) return;
+  if (stream_ms) *stream_ms = h->b->last_stream_ms;
+  if (stream_instance_iterations) *stream_instance_iterations = h->b->last_stream_iters;
+}
 void rldl_batch_counters(const RLDLBatch *h, double *admm_bytes, double *factor_bytes, c_int *launches) {
   if (!h || !h->b) return;
   if (admm_bytes) *admm_bytes = h->b->admm_bytes_per_iteration();

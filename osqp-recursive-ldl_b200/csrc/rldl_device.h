@@ -138,7 +138,10 @@ constexpr int kSchedLWant = kSchedT0 + 2, kSchedTop = kSchedT0 + 3, kSchedStarte
 // lane statistics of the last streaming launch: hand-overs, lane CTAs that left early, instances a lane CTA took
 // from the hand-over ring / from the buckets, SMs that retired
 constexpr int kSchedStats = kSchedT0 + 6;
-constexpr int kSchedCounters = kSchedStats + 6;
+// 64-bit count of the ADMM iterations (over all instances) the last streaming launch executed itself — the rest of a
+// solve's iterations ran in the latency-mode kernel; the roofline of the streaming kernel is quoted on this count
+constexpr int kSchedStreamIters = kSchedStats + 6;
+constexpr int kSchedCounters = kSchedStreamIters + 2;
 
 constexpr int STATUS_FACTOR_ERROR = -7;  // reported as OSQP_NON_CVX
 // device-internal: instance parked by an adaptive-rho update until its factor has been refreshed (never

@@ -501,10 +501,12 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     __syncwarp(gm);
   };
 
+  unsigned long long my_iters = 0;  // ADMM iterations this group executed (summed into sched[kSchedStreamIters] at exit)
   have = start_next();
   while (__any_sync(FULL, have)) {
     if (have) {
       iter++;
+      my_iters++;
       const bool can_check = S.check_termination && (iter % S.check_termination == 0);
       const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval && (iter % S.adaptive_rho_interval == 0);
       const bool time_due = time_check_due(S, iter, can_check);
@@ -794,6 +796,8 @@ __global__ void __launch_bounds__(128, 4) k_admm_stream(ModelDev M, BatchDev B, 
     }
     __syncwarp();
   }
+  if (gl == 0 && my_iters)
+    atomicAdd(reinterpret_cast<unsigned long long *>(B.sched + kSchedStreamIters), my_iters);
 }
 
 // ------------------------------- launcher --------------------------------
@@ -834,7 +838,7 @@ static cudaError_t launch_stream_t(const ModelDev &M, const BatchDev &B, const S
   // concurrent latency-mode lane: waiting CTAs 0, hand-over threshold at the top bucket (stored inverted), CTAs
   // started 0, tail flag 0
   static_assert(kSchedTop == kSchedLWant + 1 && kSchedStarted == kSchedLWant + 2 && kSchedTailFlag == kSchedLWant + 3, "layout");
-  e = cudaMemsetAsync(B.sched + kSchedLWant, 0, (4 + 6) * sizeof(int), st);
+  e = cudaMemsetAsync(B.sched + kSchedLWant, 0, (4 + 6 + 2) * sizeof(int), st);  // lane state, statistics, iteration count
   if (e != cudaSuccess) return e;
   if (reset_done) {  // the concurrent latency-mode launch waits for this, not for the kernel
     e = cudaEventRecord(reset_done, st);

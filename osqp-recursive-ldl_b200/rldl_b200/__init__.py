@@ -113,7 +113,7 @@ osqp_allocate_combine_recursive osqp_partial_update_bounds get_L_dimensions clea
 rldl_batch_setup rldl_batch_solve rldl_batch_solve_to_host rldl_batch_update_bounds rldl_batch_partial_update_bounds
 rldl_batch_update_lin_cost rldl_batch_update_data_refactor rldl_batch_warm_start rldl_batch_warm_start_shift rldl_batch_update_horizon rldl_batch_update_rho
 rldl_batch_refactor rldl_batch_update_model rldl_batch_failed_factorisations rldl_batch_kkt_solve rldl_batch_kkt_solve_static rldl_batch_max_static_doubles rldl_batch_get_solution rldl_batch_get_info
-rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel rldl_batch_set_tuning rldl_batch_lane_stats rldl_batch_get_trace rldl_batch_debug_sched rldl_batch_get_scaling rldl_batch_get_polish
+rldl_batch_update_settings rldl_batch_dims rldl_batch_last_times rldl_batch_stream_stats rldl_batch_counters rldl_batch_stream rldl_batch_select_kernel rldl_batch_set_tuning rldl_batch_lane_stats rldl_batch_get_trace rldl_batch_debug_sched rldl_batch_get_scaling rldl_batch_get_polish
 rldl_batch_free
 rldl_multi_setup rldl_multi_shards rldl_multi_shard_handle rldl_multi_solve rldl_multi_solve_to_host
 rldl_multi_get_solution rldl_multi_get_info rldl_multi_update_bounds rldl_multi_partial_update_bounds
@@ -192,6 +192,7 @@ def lib():
         "rldl_batch_dims": [vp] + [C.POINTER(c_int)] * 4,
         "rldl_batch_last_times": [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)],
         "rldl_batch_counters": [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(c_int)],
+        "rldl_batch_stream_stats": [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)],
         "rldl_batch_free": [vp],
         "rldl_multi_setup": [C.POINTER(vp), vp, c_int, c_int, C.POINTER(OSQPDataRLDL), C.POINTER(OSQPSettings)] +
                             [c_int] * 7 + [vp] * 4,
@@ -215,7 +216,7 @@ def lib():
         fn = getattr(L, name)
         fn.argtypes = args
         fn.restype = None if name in ("get_L_dimensions", "rldl_batch_dims", "rldl_batch_last_times",
-                                      "rldl_batch_counters", "rldl_batch_free", "rldl_multi_free") else c_int
+                                      "rldl_batch_counters", "rldl_batch_stream_stats", "rldl_batch_free", "rldl_multi_free") else c_int
     L.rldl_batch_select_kernel.argtypes = [vp, c_int]
     L.rldl_batch_select_kernel.restype = c_int
     L.rldl_batch_set_tuning.argtypes = [vp, C.c_char_p, c_int]
@@ -400,6 +401,12 @@ class Batch:
         f, s = C.c_double(), C.c_double()
         lib().rldl_batch_last_times(self.h, C.byref(f), C.byref(s))
         return f.value, s.value
+
+    def stream_stats(self):
+        """(ms, instance-iterations) of the streaming ADMM kernel of the last solve alone."""
+        t, it = C.c_double(), C.c_double()
+        lib().rldl_batch_stream_stats(self.h, C.byref(t), C.byref(it))
+        return t.value, it.value
 
     def counters(self):
         a, f, n = C.c_double(), C.c_double(), c_int()
