@@ -480,7 +480,8 @@ c_int rldl_batch_select_kernel(RLDLBatch *b, c_int which);
 /* Launch knobs of this handle (per handle, not process-global; the defaults are the measured optima on B200
  * and no setting can change results beyond rounding — the tests use them to steer which kernel finishes a solve):
  *   "lat_below"   unfinished instances at which the streaming kernel hands its tail to the latency-mode kernel
- *                 (default 1024; 0 = streaming kernel only; >= batch = latency-mode kernel only)
+ *                 (default: 2048 for batches of 4096 and more, else 1024; 0 = streaming kernel only; >= batch =
+ *                 latency-mode kernel only)
  *   "ring_depth"  stage records in flight per lane group of the streaming kernel (default 2)
  *   "sched_s0"    iterations a fresh instance runs before it may be pre-empted (default check_termination;
  *                 0 = device priority scheduler off)

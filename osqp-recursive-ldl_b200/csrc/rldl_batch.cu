@@ -503,6 +503,7 @@ c_int Batch::solve() {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     const size_t lat_smem = latency_smem_bytes(M, N);
+    const int lat_below = this->lat_below >= 0 ? this->lat_below : (batch >= 4096 ? 2048 : 1024);
     const bool lat_ok = lat_below > 0 && lat_smem != (size_t)-1 && lat_smem <= 227 * 1024;
     const int lane = lat_ok ? std::min(std::max(lat_lane, 0), sms - 8) : 0;
     const size_t t_per_cta = (size_t)latency_t_blocks(Nmax) * nx * (nx + 2);

@@ -876,7 +876,7 @@ c_int rldl_batch_set_tuning(RLDLBatch *h, const char *name, c_int value) {
   HB(h);
   if (!name || value < -1) return 1;
   Batch *B = h->b;
-  if (!strcmp(name, "lat_below")) B->lat_below = (int)value < 0 ? 1024 : (int)value;
+  if (!strcmp(name, "lat_below")) B->lat_below = (int)value < 0 ? -1 : (int)value;
   else if (!strcmp(name, "ring_depth")) B->tune.ring_depth = (int)value < 0 ? 0 : (int)value;
   else if (!strcmp(name, "sched_s0")) B->tune.sched_s0 = (int)value;
   else if (!strcmp(name, "ctas_per_sm")) B->tune.ctas_per_sm = (int)value < 0 ? 0 : (int)value;
