@@ -40,8 +40,20 @@ namespace rldl {
 
 constexpr int kLatThreads = 512;
 
-// nx x (nx+2) blocks of global scratch per CTA: T_k and T_k' per stage, chain blocks and their transposes
-__host__ __device__ inline int lat_t_blocks(int Nmax) { return 2 * Nmax + 2 * (Nmax / 2 + 2); }
+// nx x (nx+2) blocks of global scratch per CTA: T_k and T_k' per stage, the products of the block tree above
+// them (levels 1.., both forms) and the chain blocks in scan order (both forms)
+constexpr int kLatMaxLevels = 6;
+__host__ __device__ inline int lat_tree_blocks(int Nmax) { return Nmax + 2 * kLatMaxLevels + 2; }
+__host__ __device__ inline int lat_chain_blocks(int Nmax) { return Nmax / 2 + kLatMaxLevels + 4; }
+__host__ __device__ inline int lat_t_blocks(int Nmax) {
+  return 2 * Nmax + 2 * lat_tree_blocks(Nmax) + 2 * lat_chain_blocks(Nmax);
+}
+// first block of level lv >= 1 inside the tree area (level lv holds the nodes j = 1 .. (N-1) >> lv)
+__host__ __device__ inline int lat_level_base(int lv, int Nmax) {
+  int b = 0;
+  for (int i = 1; i < lv; i++) b += (Nmax >> i) + 1;
+  return b;
+}
 
 template <class SH>
 struct LatLayout {  // shared-memory layout (doubles) of k_admm_cta for horizon N
@@ -49,7 +61,9 @@ struct LatLayout {  // shared-memory layout (doubles) of k_admm_cta for horizon 
   // T_k ring of the scan phases: NS slots of CH stage blocks; a block is nx rows of TS = nx+2 doubles
   // (row stride chosen so that the per-lane LDS.128 of a row are bank-conflict free)
   static constexpr int CH = 5, NS = 3, TS = SH::NX + 2, TBLK = SH::NX * TS;
-  int recs, va, vc, vd, scr, bar, ctl, tring, tbar, qs, red, end;
+  int recs, va, vc, vd, scr, bar, ctl, tring, tbar, qs, red, flg, end;
+  // ints behind `flg`: ready flags of the two recurrences, the kind of every position, the chain nodes
+  __host__ __device__ static int flag_ints(int N) { return 3 * (N + 2) + 3 * (N / 2 + kLatMaxLevels + 6); }
   __host__ __device__ explicit LatLayout(int N) {
     recs = SH::M_END;
     va = recs + (N + 1) * SH::RS;
@@ -62,10 +76,14 @@ struct LatLayout {  // shared-memory layout (doubles) of k_admm_cta for horizon 
     tbar = tring + NS * CH * TBLK;
     qs = tbar + NS + (NS & 1);
     red = qs + 3 * SH::A * SH::A;  // dense cost blocks padded to A x A (residuals)
-    end = red + NG * 10 + (kLatThreads / 32) * 4;  // per-group partial residuals + per-warp certificate partials
+    flg = red + NG * 10 + (kLatThreads / 32) * 4;  // per-group partial residuals + per-warp certificate partials
+    end = flg + (flag_ints(N) + 1) / 2;
   }
 };
 
+#ifdef RLDL_LAT_PROFILE
+__device__ long long g_lat_tr[64][12];
+#endif
 template <class SH>
 __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDev B, SettingsDev S, int warm_start,
                                                               int resume, double *Tg, int claim_mode, int stream_ctas) {
@@ -124,9 +142,13 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
   double *sc = smem + L.scr + (size_t)grp * SH::SC;
   uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L.bar);
   volatile int *ctl = reinterpret_cast<volatile int *>(smem + L.ctl);
-  volatile int *prog_f = ctl + 2, *prog_b = ctl + 3;  // progress of the forward / backward scan (see scan())
-  auto wait_prog = [&](volatile int *p, int need) {
-    while (*p < need) __nanosleep(64);  // back off: the scan warp shares its scheduler with pollers
+  // ready flags (see the block tree below): rf[k] == iter once sp_k is final, rb[k] == iter once vn_k is final;
+  // kf[k]: bit 0 = k ends a chain node, bit 1 = k starts one; ch_lo / ch_hi: the chain nodes in forward order
+  volatile int *rf = reinterpret_cast<volatile int *>(smem + L.flg), *rb = rf + (N + 2);
+  int *kf = const_cast<int *>(rb) + (N + 2), *ch_lo = kf + (N + 2), *ch_hi = ch_lo + (N / 2 + kLatMaxLevels + 6),
+      *ch_lv = ch_hi + (N / 2 + kLatMaxLevels + 6);
+  auto wait_flag = [&](volatile int *p, int want) {
+    while (*p != want) __nanosleep(64);  // back off: the scan warp shares its scheduler with pollers
     __threadfence_block();
   };
   // groups 2.. work behind the scans (group 1 shares warp 0 with the scanning group and stays out of its way)
@@ -140,8 +162,25 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
   static_assert(NX % 2 == 0, "latency-mode kernel: nx must be even (16-byte rows of T)");
   double *tring = smem + L.tring;
   uint64_t *tbars = reinterpret_cast<uint64_t *>(smem + L.tbar);
+  // ---- the block tree over the stages 1..N-1 of the two recurrences ----
+  // A node (lv, j) is the aligned run of 2^lv stages ending at j 2^lv; its operator M = T_end ... T_start is formed
+  // once per instance.  The sequential chain (group 0) runs over the widest nodes only: as many of level LV as fit,
+  // then one node per set bit of what is left.  Inside a chain node the aggregates go up the tree before the scan
+  // (levels 2.. in CTA-wide steps; level 1 by the owner of the pair) and the states come down behind it, one hop per
+  // level, each by the group that owns the pair the position belongs to.  LV = 1 is the pairs-only chain.
+  const int LV = min(max(B.lat_levels, 1), kLatMaxLevels);
   if (threadIdx.x == 0) {
     ctl[2] = 0; ctl[3] = 0;
+    for (int k = 0; k < N + 2; k++) kf[k] = 0;
+    int q = 0, pos = 1, rem = N - 1;
+    for (int lv = LV; lv >= 0; lv--)
+      while (rem >= (1 << lv)) {
+        q++;
+        ch_lo[q] = pos; ch_hi[q] = pos + (1 << lv) - 1; ch_lv[q] = lv;
+        kf[ch_hi[q]] |= 1; kf[ch_lo[q]] |= 2;
+        pos += 1 << lv; rem -= 1 << lv;
+      }
+    ctl[2] = q;
     mbar_init(bar, 1);
     for (int d = 0; d < NS; d++) mbar_init(&tbars[d], 1);
   }
@@ -175,15 +214,26 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
   // (2*Nmax*TBLK doubles per CTA, L2-resident), written once per instance by this CTA and streamed back
   // through the shared-memory ring by bulk async copies, CH stages per copy
   double *TB = Tg + (size_t)blockIdx.x * lat_t_blocks(B.Nmax) * TBLK, *TD = TB + (size_t)B.Nmax * TBLK;
-  // Blocked scans: the stages 1..N-1 of the two recurrences are taken in pairs (2j-1, 2j), j = 1..J, plus a
-  // leftover stage N-1 when N-1 is odd.  The sequential chain runs over the pairs only,
-  //     sp_2j     = (c_2j     + T_2j c_2j-1)      + (T_2j T_2j-1)  sp_2j-2
-  //     vn_2j-1   = (d_2j-1   + T_2j-1' d_2j)     + (T_2j T_2j-1)' vn_2j+1
-  // (NC = J + leftover steps instead of N-1), and the stage in the middle of every pair is filled in by the group
-  // that owns the pair (sp_2j-1 = c_2j-1 + T_2j-1 sp_2j-2, vn_2j = d_2j + T_2j' vn_2j+1), off the chain.
-  // CB[p] / CD[p], p = 1..NC: the chain blocks (P_p = T_2p T_2p-1, or T_N-1 for the leftover) and their transposes.
-  double *CB = TD + (size_t)B.Nmax * TBLK, *CD = CB + (size_t)(B.Nmax / 2 + 2) * TBLK;
-  const int J = (N - 1) / 2, LEFT = (N - 1) & 1, NC = J + LEFT, NI = J + 2;
+  // Blocked scans over the block tree above.  With the aggregates
+  //     C(node) = c_end + T_end (c_end-1 + ...),           kept in place at vc[end],
+  //     D(node) = d_start + T_start' (d_start+1 + ...),    kept in place at vd[start],
+  // the sequential chain is  sp_end = C(node) + M(node) sp_start-1  (forward) and
+  // vn_start = D(node) + M(node)' vn_end+1  (backward) over the NC chain nodes.  Behind it, the end of a left child
+  // (forward: sp_e = C(left) + M(left) sp_start-1) and the start of a right child (backward:
+  // vn_o = D(right) + M(right)' vn_end+1) follow level by level, down to the pairs; the stage in the middle of a
+  // pair is filled in by the group that owns the pair (sp_2j-1 = c_2j-1 + T_2j-1 sp_2j-2, vn_2j = d_2j + T_2j' vn_2j+1).
+  // LB / LD: the operators of the levels 1.. (row-major / transposed); CB[q] / CD[q], q = 1..NC: those of the chain
+  // nodes, copied out in scan order for the bulk-copy ring.
+  double *LB = TD + (size_t)B.Nmax * TBLK, *LD = LB + (size_t)lat_tree_blocks(B.Nmax) * TBLK;
+  double *CB = LD + (size_t)lat_tree_blocks(B.Nmax) * TBLK, *CD = CB + (size_t)lat_chain_blocks(B.Nmax) * TBLK;
+  const int J = (N - 1) / 2, LEFT = (N - 1) & 1, NC = ctl[2], NI = J + 2;
+  // operator of node (lv, j), row-major (mb) or transposed (md); level 0 is T_j itself
+  auto mb = [&](int lv, int j) -> double * {
+    return lv == 0 ? TB + (size_t)j * TBLK : LB + (size_t)(lat_level_base(lv, B.Nmax) + j) * TBLK;
+  };
+  auto md = [&](int lv, int j) -> double * {
+    return lv == 0 ? TD + (size_t)j * TBLK : LD + (size_t)(lat_level_base(lv, B.Nmax) + j) * TBLK;
+  };
   // row gl of an nx x nx block in global memory (L2) times a vector in shared memory
   auto tmv = [&](const double *blk, const double *v) -> double {
     const double2 *r = reinterpret_cast<const double2 *>(blk + (gl < NX ? gl : 0) * TS);
@@ -196,10 +246,10 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     }
     return (acc[0] + acc[1]) + (acc[2] + acc[3]);
   };
-  // One scan (group 0) over the chain: step p = 1..NC (fwd, vec = vc) writes sp_2p from sp_2p-2 (leftover:
-  // sp_N-1 from sp_N-2); step p = NC..1 (bwd, vec = vd) writes vn_2p-1 from vn_2p+1 (leftover, first: vn_N-1 from
-  // vn_N).  The source vector is re-read from shared memory by broadcast LDS.128; one __syncwarp per step.
-  auto scan = [&](const bool fwd) {
+  // One scan (group 0) over the chain: step q = 1..NC (fwd, vec = vc) writes sp at the end of chain node q from sp
+  // in front of it; step q = NC..1 (bwd, vec = vd) writes vn at the start of node q from vn behind it.  The source
+  // vector is re-read from shared memory by broadcast LDS.128; one __syncwarp per step.
+  auto scan = [&](const bool fwd, const int iter_) {
     const double *Tsrc = fwd ? CB : CD;
     double *vec = fwd ? vc : vd;
     const int nblk = NC, nchunk = (nblk + CH - 1) / CH;
@@ -207,26 +257,24 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       const int t0 = c * CH, cnt = min(CH, nblk - t0);
       const int p_lo = fwd ? 1 + t0 : (NC - t0) - (cnt - 1);
       const int s = c % NS;
-      RLDL_ASSERT(cnt >= 1 && cnt <= CH && p_lo >= 1 && p_lo + cnt - 1 <= NC && NC < B.Nmax / 2 + 2);  // chain blocks
+      RLDL_ASSERT(cnt >= 1 && cnt <= CH && p_lo >= 1 && p_lo + cnt - 1 <= NC && NC < lat_chain_blocks(B.Nmax));
       mbar_expect_tx(tbars_s + 8u * s, (uint32_t)(cnt * TBLK * 8));
       bulk_g2s(tring_s + 8u * (uint32_t)(s * CH * TBLK), Tsrc + (size_t)p_lo * TBLK, (uint32_t)(cnt * TBLK * 8),
                tbars_s + 8u * s);
     };
     if (gl == 0)
       for (int c = 0; c < NS && c < nchunk; c++) issue_chunk(c);
-    // progress counter of this scan: number of chain steps done; the other direction's counter is idle during
-    // this phase and is reset here for its next use
-    volatile int *prog = fwd ? prog_f : prog_b;
-    int done_ = 0;
-    if (gl == 0) {
-      *(fwd ? prog_b : prog_f) = 0;
-      __threadfence_block();
-    }
+    volatile int *ready = fwd ? rf : rb;  // published per chain step; the groups working behind the scan poll it
     // 32-bit shared addresses: nothing but the mat-vec itself is on the chain
     const int row = (gl < NX) ? gl : 0;
     const uint32_t vec_s = smem_u32(vec);
     const int tstep = fwd ? TBLK * 8 : -TBLK * 8;
     int s = 0, t = 0;
+    int dst_n = 0, src_n = 0;
+    if (NC > 0) {
+      dst_n = fwd ? ch_hi[1] : ch_lo[NC];
+      src_n = fwd ? ch_lo[1] - 1 : ch_hi[NC] + 1;
+    }
     for (int c = 0; c < nchunk; c++) {
 #ifdef RLDL_LAT_PROFILE
       const long long w0_ = clock64();
@@ -238,10 +286,12 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       const int cnt = min(CH, nblk - c * CH);
       uint32_t ta = tring_s + 8u * (uint32_t)((s * CH + (fwd ? 0 : cnt - 1)) * TBLK + row * TS);
       for (int r = 0; r < cnt; r++, t++) {
-        const int p = fwd ? t + 1 : NC - t;
-        const bool pair = p <= J;
-        const int dst = pair ? (fwd ? 2 * p : 2 * p - 1) : N - 1;
-        const int src = pair ? (fwd ? 2 * p - 2 : 2 * p + 1) : (fwd ? N - 2 : N);
+        const int dst = dst_n, src = src_n;
+        {  // the next step's positions: off the chain
+          const int q = fwd ? min(t + 2, NC) : max(NC - t - 1, 1);
+          dst_n = fwd ? ch_hi[q] : ch_lo[q];
+          src_n = fwd ? ch_lo[q] - 1 : ch_hi[q] + 1;
+        }
         const uint32_t pd = vec_s + 8u * (uint32_t)(dst * NXE), ps = vec_s + 8u * (uint32_t)(src * NXE);
         // (loading the next step's T rows ahead of the STS below was measured slower: the loads sit in the
         // in-order LSU queue in front of the store the next step is waiting for)
@@ -260,9 +310,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         }
         if (gl < NX) sts64(pd + 8u * gl, cur + ((acc[0] + acc[1]) + (acc[2] + acc[3])));
         __syncwarp(gm);
-        // publish (after the __syncwarp: the stores of one warp reach shared memory in program order);
-        // the groups working behind the scan poll this counter
-        if (gl == 0) *prog = ++done_;
+        // publish (after the __syncwarp: the stores of one warp reach shared memory in program order)
+        if (gl == 0) ready[dst] = iter_;
         ta += tstep;
       }
       if (gl == 0 && c + NS < nchunk) issue_chunk(c + NS);
@@ -371,6 +420,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     mbar_wait(bar_s, phase);
     phase ^= 1u;
     __syncthreads();
+    for (int k = threadIdx.x; k < 2 * (N + 2); k += blockDim.x) rf[k] = -1;  // rf and rb: nothing is ready
     // ---------------- T_k = Sinv_k F_k Xinv_k[:, 0:nx], one group per stage ----------------
     for (int k = grp; k < N; k += NG) {
       const double *sl_ = recs + k * RS;
@@ -393,29 +443,38 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     }
     __threadfence();
     __syncthreads();
-    // ---------------- chain blocks: P_p = T_2p T_2p-1 (and the leftover T_N-1), one group per block ----------------
-    for (int p = 1 + grp; p <= NC; p += NG) {
-      const bool pair = p <= J;
-      const double *T2 = TB + (size_t)(pair ? 2 * p : N - 1) * TBLK;  // rows of the left factor
-      const double *T1t = TD + (size_t)(pair ? 2 * p - 1 : 0) * TBLK;  // rows of T_2p-1' = columns of T_2p-1
-      if (gl < NX) {
-        double rowv[NX];
+    // ---------------- the operators of the block tree, level by level: M(lv, j) = M(lv-1, 2j) M(lv-1, 2j-1),
+    // one group per node ----------------
+    for (int lv = 1; lv <= LV; lv++) {
+      const int cnt = (N - 1) >> lv;
+      for (int j = 1 + grp; j <= cnt; j += NG) {
+        const double *T2 = mb(lv - 1, 2 * j);       // rows of the left factor
+        const double *T1t = md(lv - 1, 2 * j - 1);  // rows of the right factor's transpose = its columns
+        double *ob = mb(lv, j), *od = md(lv, j);
+        if (gl < NX) {
+          double rowv[NX];
 #pragma unroll
-        for (int mm = 0; mm < NX; mm++) rowv[mm] = __ldcg(T2 + gl * TS + mm);
+          for (int mm = 0; mm < NX; mm++) rowv[mm] = __ldcg(T2 + gl * TS + mm);
 #pragma unroll 1
-        for (int c = 0; c < NX; c++) {
-          double v = 0.0;
-          if (pair) {
+          for (int c = 0; c < NX; c++) {
+            double v = 0.0;
 #pragma unroll
             for (int mm = 0; mm < NX; mm++) v = fma(rowv[mm], __ldcg(T1t + c * TS + mm), v);
-          } else {
-#pragma unroll
-            for (int mm = 0; mm < NX; mm++)
-              if (mm == c) v = rowv[mm];
+            ob[gl * TS + c] = v;
+            od[c * TS + gl] = v;
           }
-          CB[(size_t)p * TBLK + gl * TS + c] = v;
-          CD[(size_t)p * TBLK + c * TS + gl] = v;
         }
+      }
+      __threadfence();
+      __syncthreads();
+    }
+    // the chain nodes, copied out in scan order
+    for (int q = 1 + grp; q <= NC; q += NG) {
+      const int lv = ch_lv[q], j = ch_hi[q] >> lv;
+      const double *sb = mb(lv, j), *sd = md(lv, j);
+      for (int e = gl; e < TBLK; e += G) {
+        CB[(size_t)q * TBLK + e] = __ldcg(sb + e);
+        CD[(size_t)q * TBLK + e] = __ldcg(sd + e);
       }
     }
     __threadfence();  // the chain blocks are read back by bulk async copies (async proxy)
@@ -490,16 +549,24 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     __syncthreads();
     // ---------------- ADMM iterations (osqp.c:354-519) ----------------
 #ifdef RLDL_LAT_PROFILE
-    long long pt[7] = {0, 0, 0, 0, 0, 0, 0}, pc = 0;
-#define PT(i) do { const long long now_ = clock64(); pt[i] += now_ - pc; pc = now_; } while (0)
+    long long pt[7] = {0, 0, 0, 0, 0, 0, 0}, pc = 0;  // [0] / [6]: aggregates before the forward / backward scan
+    unsigned long long gt0_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt0_));
+    const int iter0_ = iter;
+    auto gtime_ = []() -> long long { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return (long long)t; };
+#define PT(i) do { const long long now_ = gtime_(); pt[i] += now_ - pc; pc = now_; } while (0)
+#define TR(slot) do { if (blockIdx.x == 0 && iter == 101 && gl == 0) g_lat_tr[grp][slot] = gtime_(); } while (0)
 #else
 #define PT(i)
+#define TR(slot)
 #endif
     for (;;) {
       iter++;
 #ifdef RLDL_LAT_PROFILE
-      pc = clock64();
+      pc = gtime_();
+      if (blockIdx.x == 0 && iter == 101 && gl == 0) for (int e_ = 0; e_ < 12; e_++) g_lat_tr[grp][e_] = 0;
 #endif
+      TR(0);
       const bool can_check = S.check_termination && (iter % S.check_termination == 0);
       const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval && (iter % S.adaptive_rho_interval == 0);
       const bool last = iter == S.max_iter;
@@ -508,20 +575,58 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       // ===== phases B and C, pipelined.  B (group 0): sp_k = c_k + T_k sp_{k-1}, in place in vc.
       //       C (groups 2..): e_k = a_k + Xinv_k (F_k' sp_k - J' sp_{k-1}), d_k = e_k[0:nx], as soon as the scan
       //       has published sp_k =====
+      // the aggregates of the levels 2.. (level 1 was done by the owners of the pairs: pre_fwd)
+      for (int lv = 2; lv <= LV; lv++) {
+        const int cnt = (N - 1) >> lv;
+        if (cnt == 0) break;
+        for (int j = 1 + grp; j <= cnt; j += NG) {
+          const int end = j << lv, mid = end - (1 << (lv - 1));
+          if (gl < NX) vc[end * NXE + gl] += tmv(mb(lv - 1, 2 * j), vc + mid * NXE);
+        }
+        __syncthreads();
+      }
+      PT(0);
+      TR(1);
       if (grp == 0) {
-        scan(true);
+        scan(true, iter);
+        TR(2);
         PT(1);
       } else if (grp >= 2) {
         for (int it = grp - 2; it < NI; it += NGW) {
-          // chain steps this item waits for: pair j: sp_2j (step j); last item: the whole chain
-          wait_prog(prog_f, it == 0 ? 0 : (it <= J ? it : NC));
-          if (it >= 1 && it <= J) {  // fill the middle stage: sp_2j-1 = c_2j-1 + T_2j-1 sp_2j-2
-            if (gl < NX) vc[(2 * it - 1) * NXE + gl] += tmv(TB + (size_t)(2 * it - 1) * TBLK, vc + (2 * it - 2) * NXE);
+          if (it >= 1 && it <= J) {
+            const int e = 2 * it;
+            if (!(kf[e] & 1)) {  // sp_e comes down the tree: the end of a left child of width 2^t
+              const int t = __ffs(e) - 1, src = e - (1 << t);
+              const double2 *r = reinterpret_cast<const double2 *>(mb(t, e >> t) + (gl < NX ? gl : 0) * TS);
+              double2 rowv[NX / 2];
+#pragma unroll
+              for (int j = 0; j < NX / 2; j++) rowv[j] = __ldcg(r + j);  // in flight while the flag is polled
+              if (src > 0) wait_flag(rf + src, iter);
+              const double *v = vc + src * NXE;
+              double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+              for (int j = 0; j < NX / 2; j++) {
+                acc[(2 * j) & 3] = fma(rowv[j].x, v[2 * j], acc[(2 * j) & 3]);
+                acc[(2 * j + 1) & 3] = fma(rowv[j].y, v[2 * j + 1], acc[(2 * j + 1) & 3]);
+              }
+              if (gl < NX) vc[e * NXE + gl] += (acc[0] + acc[1]) + (acc[2] + acc[3]);
+              __syncwarp(gm);
+              if (gl == 0) { __threadfence_block(); rf[e] = iter; }
+            }
+            if (it == grp - 2) TR(2);
+            // fill the middle stage: sp_2j-1 = c_2j-1 + T_2j-1 sp_2j-2
+            if (e > 2) wait_flag(rf + (e - 2), iter);
+            if (gl < NX) vc[(e - 1) * NXE + gl] += tmv(TB + (size_t)(e - 1) * TBLK, vc + (e - 2) * NXE);
             __syncwarp(gm);
+            if (it == grp - 2) TR(3);
+          } else if (it == J + 1) {  // leftover and terminal stage: sp_N-1 (and sp_N-2 in front of a leftover stage)
+            if (2 * J > 0) wait_flag(rf + 2 * J, iter);
+            if (LEFT) wait_flag(rf + (N - 1), iter);
           }
           for (int k = item_lo(it); k <= item_hi(it); k++) {
             const bool term = (k == N);
             const double *sl_ = recs + k * RS;
+            if (it >= 1 && it <= J && k == 2 * it && (kf[k] & 1)) wait_flag(rf + k, iter);  // sp_2j from the chain
             if (gl < A) {
               double gg = 0.0;
               if (!term) gg = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, vc + k * NXE);
@@ -540,25 +645,62 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
             if (gl < NX) vd[(2 * it - 1) * NXE + gl] += tmv(TD + (size_t)(2 * it - 1) * TBLK, vd + 2 * it * NXE);
             __syncwarp(gm);
           }
+          if (it == grp - 2) TR(4);
         }
       }
       __syncthreads();
+      TR(5);
       PT(2);
       // ===== phases D and E, pipelined.  D (group 0): vn_k = d_k + T_k' vn_{k+1}, k = N-1 .. 1, in place in vd
       //       (vn_N = d_N; stage 0 has no state) =====
       // (phase E below runs behind this scan: groups 2.. take their stages in descending order and start on
       // stage k once vn_{k+1} is published)
+      for (int lv = 2; lv <= LV; lv++) {  // the aggregates of the levels 2.., kept at the start of every node
+        const int cnt = (N - 1) >> lv;
+        if (cnt == 0) break;
+        for (int j = 1 + grp; j <= cnt; j += NG) {
+          const int start = ((j - 1) << lv) + 1, rs_ = start + (1 << (lv - 1));
+          if (gl < NX) vd[start * NXE + gl] += tmv(md(lv - 1, 2 * j - 1), vd + rs_ * NXE);
+        }
+        __syncthreads();
+      }
+      PT(6);
+      TR(6);
       if (grp == 0) {
-        scan(false);
+        scan(false, iter);
+        TR(7);
         PT(3);
       }
       // ===== phase E: v_k = e_k + Xinv_k F_k' (Sinv_k vn_{k+1}), nu^d_k, ADMM step (auxil.c:188-228) =====
       for (int it = (grp >= 2 && grp - 2 < NI) ? (grp - 2) + ((NI - 1 - (grp - 2)) / NGW) * NGW : -1; it >= 0; it -= NGW) {
-       // chain steps this item waits for: pair j: vn_2j+1 (LEFT + J - j steps); stage 0: the whole chain (vn_1)
-       wait_prog(prog_b, it == 0 ? NC : (it <= J ? LEFT + J - it : 0));
-       if (it >= 1 && it <= J) {  // fill the middle stage: vn_2j = d_2j + T_2j' vn_2j+1
+       if (it >= 1 && it <= J) {
+         const int o = 2 * it - 1;
+         if (!(kf[o] & 2)) {  // vn_o comes down the tree: the start of a right child of width 2^t
+           const int t = __ffs(o - 1) - 1, src = o + (1 << t);
+           const double2 *r = reinterpret_cast<const double2 *>(md(t, ((o - 1) >> t) + 1) + (gl < NX ? gl : 0) * TS);
+           double2 rowv[NX / 2];
+#pragma unroll
+           for (int j = 0; j < NX / 2; j++) rowv[j] = __ldcg(r + j);  // in flight while the flag is polled
+           if (src < N) wait_flag(rb + src, iter);
+           const double *v = vd + src * NXE;
+           double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+           for (int j = 0; j < NX / 2; j++) {
+             acc[(2 * j) & 3] = fma(rowv[j].x, v[2 * j], acc[(2 * j) & 3]);
+             acc[(2 * j + 1) & 3] = fma(rowv[j].y, v[2 * j + 1], acc[(2 * j + 1) & 3]);
+           }
+           if (gl < NX) vd[o * NXE + gl] += (acc[0] + acc[1]) + (acc[2] + acc[3]);
+           __syncwarp(gm);
+           if (gl == 0) { __threadfence_block(); rb[o] = iter; }
+         }
+         if (it == grp - 2) TR(7);
+         // fill the middle stage: vn_2j = d_2j + T_2j' vn_2j+1
+         if (o + 2 < N) wait_flag(rb + (o + 2), iter);
          if (gl < NX) vd[2 * it * NXE + gl] += tmv(TD + (size_t)(2 * it) * TBLK, vd + (2 * it + 1) * NXE);
          __syncwarp(gm);
+         if (it == grp - 2) TR(8);
+       } else if (it == 0) {  // stage 0 reads vn_1: the end of the chain
+         if (N > 1) wait_flag(rb + 1, iter);
        }
        for (int k = item_hi(it); k >= item_lo(it); k--) {
         const bool term = (k == N);
@@ -641,9 +783,24 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         stage_A(k, xnew, zp, yp, zd, yd);
        }
        pre_fwd(it);
+       if (it == grp - 2) TR(9);
       }
       if (!(can_check || can_adapt || last || time_due)) {
         __syncthreads();  // iterates of this iteration visible to every group of the CTA
+        TR(10);
+#ifdef RLDL_LAT_PROFILE
+        if (blockIdx.x == 0 && iter == 101) {
+          __threadfence(); __syncthreads();
+          if (threadIdx.x == 0) {
+            const long long t0_ = g_lat_tr[0][0];
+            for (int g_ = 0; g_ < NG; g_++) {
+              printf("trace grp %2d:", g_);
+              for (int e_ = 0; e_ < 11; e_++) printf(" %6lld", g_lat_tr[g_][e_] ? g_lat_tr[g_][e_] - t0_ : -1);
+              printf("\n");
+            }
+          }
+        }
+#endif
         PT(4);
         continue;
       }
@@ -862,9 +1019,13 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
       deliver_to_host(B, inst, threadIdx.x, blockDim.x, n, m, __ldcg(B.status + inst), __ldcg(B.iter + inst),
                       __ldcg(B.obj + inst), __ldcg(B.pri + inst), __ldcg(B.dua + inst), __ldcg(B.rho_est + inst));
 #ifdef RLDL_LAT_PROFILE
-    if (threadIdx.x == 0 && blockIdx.x == 0)
-      printf("lat profile inst %d iters %d: cycles/iter A %lld B %lld C %lld D %lld E %lld epi %lld  (T waits in B+D %lld)\n", inst, iter,
-             pt[0] / iter, pt[1] / iter, pt[2] / iter, pt[3] / iter, pt[4] / iter, pt[5] / iter, twait_ / iter);
+    unsigned long long gt1_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt1_));
+    if (threadIdx.x == 0 && blockIdx.x < 3)
+      printf("ns/iter %lld  ", (long long)(gt1_ - gt0_) / max(iter - iter0_, 1));
+    if (threadIdx.x == 0 && blockIdx.x < 3)
+      printf("lat profile inst %d iters %d: ns/iter up %lld B %lld C %lld up %lld D %lld E %lld epi %lld  (T waits in B+D %lld)\n", inst, iter,
+             pt[0] / iter, pt[1] / iter, pt[2] / iter, pt[6] / iter, pt[3] / iter, pt[4] / iter, pt[5] / iter, twait_ / iter);
 #endif
     __syncthreads();  // ctl is rewritten by the next claim
   }
