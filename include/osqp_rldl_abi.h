@@ -491,6 +491,9 @@ c_int rldl_batch_select_kernel(RLDLBatch *b, c_int which);
  *                 its most-unconverged instances, whose chains would otherwise bound the tail (default 8, 0 = off)
  *   "lat_retire_below"  unfinished instances at which the streaming CTAs on the lane's SMs retire
  *                 (default 6 x lat_below)
+ *   "lat_levels"  levels of the block tree under the sequential chain of the latency-mode kernel (default 1 = the
+ *                 chain runs over pairs of stages; k = over runs of 2^k stages, with k - 1 more hops behind it;
+ *                 1..6; measured neutral on B200)
  * value = -1 restores the default.  Returns 0, or 1 for an unknown name / invalid value. */
 c_int rldl_batch_set_tuning(RLDLBatch *b, const char *name, c_int value);
 /* statistics of the concurrent latency-mode lane in the last streaming launch (6 values): instances handed over,

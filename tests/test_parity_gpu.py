@@ -172,6 +172,26 @@ def test_other_specialised_shapes_match_reference(nx, nu, monkeypatch):
         gb.free()
 
 
+@pytest.mark.parametrize("nx,nu,N", [(12, 4, 2), (12, 4, 7), (12, 4, 12), (12, 4, 22), (6, 2, 13), (16, 4, 10), (2, 1, 6)])
+def test_latency_mode_block_tree_levels_match_reference(nx, nu, N):
+    """The latency-mode kernel with 1..5 levels of the block tree under its sequential chain (tuning knob
+    "lat_levels": 1 = pairs of stages, the default; deeper trees shorten the chain and add hops behind it), over
+    horizons with every shape of leftover (N - 1 = 1, 6, 11, 21, ...): each against the unmodified reference."""
+    from rldl_b200 import mpc
+    batch = 12
+    mdl = mpc.random_model(nx, nu, seed=500 + nx * 10 + nu)
+    q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch, 11 + N), N, N)
+    res = ref_run(mdl, N, N, q, l, u, [("solve",), ("get",), ("dims",)])
+    ref, (n, m) = res[1], res[2]
+    gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
+    for lv in (1, 2, 3, 4, 5):
+        gb.set_tuning(lat_below=100000, lat_levels=lv)
+        assert gb.solve() == 0
+        bad = compare(gb.get(), ref, n, m)
+        assert not bad, (nx, nu, N, lv, bad[:5])
+    gb.free()
+
+
 @pytest.mark.parametrize("name,batch,below,kernel", [("C1", 3000, 1024, 0), ("C1", 500, 100000, 0), ("C3", 300, 100, 0),
                                                      ("C1", 64, 0, 1)],
                          ids=["stream+tail", "latency", "C3 hand-off", "generic"])
