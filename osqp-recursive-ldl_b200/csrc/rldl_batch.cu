@@ -312,7 +312,7 @@ c_int Batch::create(Batch **out, const csc *Q0, const csc *Qi, const csc *QN, co
   CK(dalloc(&D.rho_updates, bs)); CK(dalloc(&D.fact_flag, bs));
   CK(dalloc(&B->d_changed, bs));
   CK(dalloc(&B->d_ratio, bs));
-  D.ratio_prev = B->d_ratio; D.sched_key = 1; D.lat_levels = 1;
+  D.ratio_prev = B->d_ratio; D.sched_key = 1; D.lat_levels = 1; D.lat_lockstep = 1;
   if (B->scaled()) { CK(dalloc(&D.sD, bs * D.nmax)); CK(dalloc(&D.sE, bs * D.mmax)); CK(dalloc(&D.sC, bs)); }
   CK(dalloc(&D.sched, kSchedCounters));
   rc = B->configure_stream();

@@ -885,6 +885,7 @@ c_int rldl_batch_set_tuning(RLDLBatch *h, const char *name, c_int value) {
   else if (!strcmp(name, "lat_lane")) B->lat_lane = (int)value < 0 ? 8 : (int)value;
   else if (!strcmp(name, "lat_retire_below")) B->lat_retire_below = (int)value < 0 ? 0 : (int)value;
   else if (!strcmp(name, "lane_tail")) B->lane_tail = (int)value < 0 ? 0 : (int)value;
+  else if (!strcmp(name, "lat_lockstep")) B->D.lat_lockstep = (int)value < 0 ? 1 : ((int)value ? 1 : 0);
   else if (!strcmp(name, "lat_levels")) B->D.lat_levels = (int)value < 1 ? 1 : (int)value;
   else if (!strcmp(name, "sched_key")) B->D.sched_key = (int)value < 0 ? 1 : ((int)value ? 1 : 0);
   else return 1;

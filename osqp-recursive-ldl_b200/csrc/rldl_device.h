@@ -104,6 +104,7 @@ struct BatchDev {
   // yet): with the current ratio it gives the convergence rate and from it the predicted remaining iterations, the
   // urgency the device scheduler sorts by
   double *ratio_prev;
+  int lat_lockstep;  // latency-mode kernel: 1 = a warp per item, its two lane groups on the two stages side by side
   int lat_levels;  // latency-mode kernel: levels of the block tree under the sequential chain (1 = pairs only)
   int sched_key;  // 0: urgency = log of the distance from the tolerances (round 1); 1: log of the predicted remaining iterations
   // Streaming layout (rldl_stream.cu): one record per (instance, stage), RS doubles:

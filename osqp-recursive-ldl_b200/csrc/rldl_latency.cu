@@ -246,6 +246,21 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
     }
     return (acc[0] + acc[1]) + (acc[2] + acc[3]);
   };
+  // the same in two halves: the row is fetched from L2 before a flag is polled, the product follows the flag
+  auto ld_rows = [&](const double *blk, double2 (&rowv)[NX / 2]) {
+    const double2 *r = reinterpret_cast<const double2 *>(blk + (gl < NX ? gl : 0) * TS);
+#pragma unroll
+    for (int j = 0; j < NX / 2; j++) rowv[j] = __ldcg(r + j);
+  };
+  auto dot_rows = [&](const double2 (&rowv)[NX / 2], const double *v) -> double {
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int j = 0; j < NX / 2; j++) {
+      acc[(2 * j) & 3] = fma(rowv[j].x, v[2 * j], acc[(2 * j) & 3]);
+      acc[(2 * j + 1) & 3] = fma(rowv[j].y, v[2 * j + 1], acc[(2 * j + 1) & 3]);
+    }
+    return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+  };
   // One scan (group 0) over the chain: step q = 1..NC (fwd, vec = vc) writes sp at the end of chain node q from sp
   // in front of it; step q = NC..1 (bwd, vec = vd) writes vn at the start of node q from vn behind it.  The source
   // vector is re-read from shared memory by broadcast LDS.128; one __syncwarp per step.
@@ -322,6 +337,17 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
   // item J+1 = the leftover stage (if any) and the terminal stage
   auto item_lo = [&](int it) -> int { return it == 0 ? 0 : (it <= J ? 2 * it - 1 : 2 * J + 1); };
   auto item_hi = [&](int it) -> int { return it == 0 ? 0 : (it <= J ? 2 * it : N); };
+  // Lockstep variant (two lane groups per warp, tuning knob "lat_lockstep"): a WARP owns an item and its two lane
+  // groups take the two stages of the item side by side — the upper stage by group 0 of the warp, the lower one by
+  // group 1 — so the groups of a warp are released together and never run diverged, and the item released last
+  // costs one stage, not two.  Warp 0 keeps the scan.
+  const bool LK = (SH::GPW == 2) && B.lat_lockstep != 0;
+  constexpr int NWK = kLatThreads / 32 - 1;
+  auto half_stage = [&](int it) -> int {
+    if (it == 0) return gw == 0 ? 0 : -1;
+    if (it <= J) return gw == 0 ? 2 * it : 2 * it - 1;
+    return gw == 0 ? N : (LEFT ? N - 1 : -1);
+  };
 
   for (;;) {
     // ---------------- claim an instance ----------------
@@ -525,24 +551,53 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         __syncwarp(gm);
       }
     };
-    // first iteration: phase A from the iterates in HBM, by the groups that will own the items in phase E
-    if (grp >= 2) {
-      for (int it = grp - 2; it < NI; it += NGW) {
-        for (int k = item_lo(it); k <= item_hi(it); k++) {
-          const bool term = (k == N);
-          const int dim = term ? NX : A, np = term ? NT : NY;
-          const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
-          const double xv = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
-          double zp[NYT], yp[NYT], zd = 0.0, yd = 0.0;
+    // phase C for one stage (its sp_k and sp_k-1 are final)
+    auto stage_C = [&](int k) {
+      const bool term = (k == N);
+      const double *sl_ = recs + k * RS;
+      if (gl < A) {
+        double gg = 0.0;
+        if (!term) gg = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, vc + k * NXE);
+        if (k > 0 && gl < NX) gg -= vc[(k - 1) * NXE + gl];
+        v2_store<SH>(gg2, gl, gg);
+      }
+      __syncwarp(gm);
+      if (gl < A) {
+        const double e = va[k * AE + gl] + xinv_mv<SH>(sl_, gl, gg2, wr);
+        va[k * AE + gl] = e;
+        if (gl < NX) vd[k * NXE + gl] = e;
+      }
+      __syncwarp(gm);
+    };
+    // phase A for one stage from the iterates in HBM (first iteration of an instance)
+    auto stage_A_from_hbm = [&](int k) {
+      const bool term = (k == N);
+      const int dim = term ? NX : A, np = term ? NT : NY;
+      const int xoff = k * A - NX, roff = k * BQ, ilo = (k == 0) ? NX : 0;
+      const double xv = (gl >= ilo && gl < dim) ? __ldcg(x + xoff + gl) : 0.0;
+      double zp[NYT], yp[NYT], zd = 0.0, yd = 0.0;
 #pragma unroll
-          for (int t = 0; t < NYT; t++) {
-            const int rr = gl + G * t;
-            zp[t] = yp[t] = 0.0;
-            if (rr < np) { zp[t] = __ldcg(z + roff + rr); yp[t] = __ldcg(y + roff + rr); }
-          }
-          if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
-          stage_A(k, xv, zp, yp, zd, yd);
+      for (int t = 0; t < NYT; t++) {
+        const int rr = gl + G * t;
+        zp[t] = yp[t] = 0.0;
+        if (rr < np) { zp[t] = __ldcg(z + roff + rr); yp[t] = __ldcg(y + roff + rr); }
+      }
+      if (!term && gl < NX) { zd = __ldcg(z + roff + NY + gl); yd = __ldcg(y + roff + NY + gl); }
+      stage_A(k, xv, zp, yp, zd, yd);
+    };
+    // first iteration: phase A from the iterates in HBM, by the groups that will own the items in phase E
+    if (LK) {
+      if (wid >= 1)
+        for (int it = wid - 1; it < NI; it += NWK) {
+          const int k = half_stage(it);
+          if (k >= 0) stage_A_from_hbm(k);
+          __syncwarp(FULL);
+          if (gw == 0) pre_fwd(it);
+          __syncwarp(FULL);
         }
+    } else if (grp >= 2) {
+      for (int it = grp - 2; it < NI; it += NGW) {
+        for (int k = item_lo(it); k <= item_hi(it); k++) stage_A_from_hbm(k);
         pre_fwd(it);
       }
     }
@@ -591,6 +646,45 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         scan(true, iter);
         TR(2);
         PT(1);
+      } else if (LK) {
+        if (wid >= 1)
+          for (int it = wid - 1; it < NI; it += NWK) {
+            const int k = half_stage(it);
+            if (it >= 1 && it <= J) {
+              const int e = 2 * it;
+              if (gw == 0) {
+                if (!(kf[e] & 1)) {  // sp_e comes down the tree (see the other variant below)
+                  const int t = __ffs(e) - 1, src = e - (1 << t);
+                  double2 rowv[NX / 2];
+                  ld_rows(mb(t, e >> t), rowv);
+                  if (src > 0) wait_flag(rf + src, iter);
+                  const double add = dot_rows(rowv, vc + src * NXE);
+                  if (gl < NX) vc[e * NXE + gl] += add;
+                  __syncwarp(gm);
+                  if (gl == 0) { __threadfence_block(); rf[e] = iter; }
+                } else {
+                  wait_flag(rf + e, iter);  // sp_2j from the chain
+                }
+              } else {  // the middle stage: sp_2j-1 = c_2j-1 + T_2j-1 sp_2j-2
+                if (e > 2) wait_flag(rf + (e - 2), iter);
+                if (gl < NX) vc[(e - 1) * NXE + gl] += tmv(TB + (size_t)(e - 1) * TBLK, vc + (e - 2) * NXE);
+              }
+              __syncwarp(FULL);
+            } else if (it == J + 1) {
+              if (2 * J > 0) wait_flag(rf + 2 * J, iter);
+              if (LEFT) wait_flag(rf + (N - 1), iter);
+            }
+            if (it == wid - 1) TR(3);
+            if (k >= 0) stage_C(k);
+            if (it >= 1 && it <= J) {  // backward pre-step: d_2j-1 += T_2j-1' d_2j
+              __syncwarp(FULL);
+              if (gw == 1) {
+                if (gl < NX) vd[(2 * it - 1) * NXE + gl] += tmv(TD + (size_t)(2 * it - 1) * TBLK, vd + 2 * it * NXE);
+              }
+              __syncwarp(FULL);
+            }
+            if (it == wid - 1) TR(4);
+          }
       } else if (grp >= 2) {
         for (int it = grp - 2; it < NI; it += NGW) {
           if (it >= 1 && it <= J) {
@@ -624,22 +718,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
             if (LEFT) wait_flag(rf + (N - 1), iter);
           }
           for (int k = item_lo(it); k <= item_hi(it); k++) {
-            const bool term = (k == N);
-            const double *sl_ = recs + k * RS;
             if (it >= 1 && it <= J && k == 2 * it && (kf[k] & 1)) wait_flag(rf + k, iter);  // sp_2j from the chain
-            if (gl < A) {
-              double gg = 0.0;
-              if (!term) gg = dense_mv<NX, A>(FdT + (k == 0 ? 0 : A * NX) + gl, vc + k * NXE);
-              if (k > 0 && gl < NX) gg -= vc[(k - 1) * NXE + gl];
-              v2_store<SH>(gg2, gl, gg);
-            }
-            __syncwarp(gm);
-            if (gl < A) {
-              const double e = va[k * AE + gl] + xinv_mv<SH>(sl_, gl, gg2, wr);
-              va[k * AE + gl] = e;
-              if (gl < NX) vd[k * NXE + gl] = e;
-            }
-            __syncwarp(gm);
+            stage_C(k);
           }
           if (it >= 1 && it <= J) {  // backward pre-step: d_2j-1 += T_2j-1' d_2j
             if (gl < NX) vd[(2 * it - 1) * NXE + gl] += tmv(TD + (size_t)(2 * it - 1) * TBLK, vd + 2 * it * NXE);
@@ -672,37 +752,8 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         PT(3);
       }
       // ===== phase E: v_k = e_k + Xinv_k F_k' (Sinv_k vn_{k+1}), nu^d_k, ADMM step (auxil.c:188-228) =====
-      for (int it = (grp >= 2 && grp - 2 < NI) ? (grp - 2) + ((NI - 1 - (grp - 2)) / NGW) * NGW : -1; it >= 0; it -= NGW) {
-       if (it >= 1 && it <= J) {
-         const int o = 2 * it - 1;
-         if (!(kf[o] & 2)) {  // vn_o comes down the tree: the start of a right child of width 2^t
-           const int t = __ffs(o - 1) - 1, src = o + (1 << t);
-           const double2 *r = reinterpret_cast<const double2 *>(md(t, ((o - 1) >> t) + 1) + (gl < NX ? gl : 0) * TS);
-           double2 rowv[NX / 2];
-#pragma unroll
-           for (int j = 0; j < NX / 2; j++) rowv[j] = __ldcg(r + j);  // in flight while the flag is polled
-           if (src < N) wait_flag(rb + src, iter);
-           const double *v = vd + src * NXE;
-           double acc[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-           for (int j = 0; j < NX / 2; j++) {
-             acc[(2 * j) & 3] = fma(rowv[j].x, v[2 * j], acc[(2 * j) & 3]);
-             acc[(2 * j + 1) & 3] = fma(rowv[j].y, v[2 * j + 1], acc[(2 * j + 1) & 3]);
-           }
-           if (gl < NX) vd[o * NXE + gl] += (acc[0] + acc[1]) + (acc[2] + acc[3]);
-           __syncwarp(gm);
-           if (gl == 0) { __threadfence_block(); rb[o] = iter; }
-         }
-         if (it == grp - 2) TR(7);
-         // fill the middle stage: vn_2j = d_2j + T_2j' vn_2j+1
-         if (o + 2 < N) wait_flag(rb + (o + 2), iter);
-         if (gl < NX) vd[2 * it * NXE + gl] += tmv(TD + (size_t)(2 * it) * TBLK, vd + (2 * it + 1) * NXE);
-         __syncwarp(gm);
-         if (it == grp - 2) TR(8);
-       } else if (it == 0) {  // stage 0 reads vn_1: the end of the chain
-         if (N > 1) wait_flag(rb + 1, iter);
-       }
-       for (int k = item_hi(it); k >= item_lo(it); k--) {
+      // phases E and A (of the next iteration) for one stage whose vn_k+1 is final
+      auto stage_EA = [&](int k) {
         const bool term = (k == N);
         const int cls = term ? 2 : (k == 0 ? 0 : 1);
         const int dim = term ? NX : A, np = term ? NT : NY;
@@ -781,7 +832,72 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
         // phase A of the next iteration for this stage, straight from the registers (its inputs are stage-local;
         // va[k] / vc[k] have no reader left in this iteration)
         stage_A(k, xnew, zp, yp, zd, yd);
+      };
+      if (LK) {
+        for (int it = (wid >= 1 && wid - 1 < NI) ? (wid - 1) + ((NI - 1 - (wid - 1)) / NWK) * NWK : -1; it >= 0; it -= NWK) {
+          const int k = half_stage(it);
+          if (it >= 1 && it <= J) {
+            const int o = 2 * it - 1;
+            if (gw == 1) {
+              if (!(kf[o] & 2)) {  // vn_o comes down the tree (see the other variant below)
+                const int t = __ffs(o - 1) - 1, src = o + (1 << t);
+                double2 rowv[NX / 2];
+                ld_rows(md(t, ((o - 1) >> t) + 1), rowv);
+                if (src < N) wait_flag(rb + src, iter);
+                const double add = dot_rows(rowv, vd + src * NXE);
+                if (gl < NX) vd[o * NXE + gl] += add;
+                __syncwarp(gm);
+                if (gl == 0) { __threadfence_block(); rb[o] = iter; }
+              }
+              // the middle stage: vn_2j = d_2j + T_2j' vn_2j+1
+              if (o + 2 < N) wait_flag(rb + (o + 2), iter);
+              if (gl < NX) vd[2 * it * NXE + gl] += tmv(TD + (size_t)(2 * it) * TBLK, vd + (2 * it + 1) * NXE);
+            } else {
+              if (o + 2 < N) wait_flag(rb + (o + 2), iter);
+            }
+            __syncwarp(FULL);
+          } else if (it == 0) {
+            if (N > 1) wait_flag(rb + 1, iter);
+          }
+          if (it == wid - 1) TR(8);
+          if (k >= 0) stage_EA(k);
+          __syncwarp(FULL);
+          if (gw == 0) pre_fwd(it);  // c_2j += T_2j c_2j-1
+          __syncwarp(FULL);
+          if (it == wid - 1) TR(9);
+        }
+      }
+      for (int it = (!LK && grp >= 2 && grp - 2 < NI) ? (grp - 2) + ((NI - 1 - (grp - 2)) / NGW) * NGW : -1; it >= 0; it -= NGW) {
+       if (it >= 1 && it <= J) {
+         const int o = 2 * it - 1;
+         if (!(kf[o] & 2)) {  // vn_o comes down the tree: the start of a right child of width 2^t
+           const int t = __ffs(o - 1) - 1, src = o + (1 << t);
+           const double2 *r = reinterpret_cast<const double2 *>(md(t, ((o - 1) >> t) + 1) + (gl < NX ? gl : 0) * TS);
+           double2 rowv[NX / 2];
+#pragma unroll
+           for (int j = 0; j < NX / 2; j++) rowv[j] = __ldcg(r + j);  // in flight while the flag is polled
+           if (src < N) wait_flag(rb + src, iter);
+           const double *v = vd + src * NXE;
+           double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+           for (int j = 0; j < NX / 2; j++) {
+             acc[(2 * j) & 3] = fma(rowv[j].x, v[2 * j], acc[(2 * j) & 3]);
+             acc[(2 * j + 1) & 3] = fma(rowv[j].y, v[2 * j + 1], acc[(2 * j + 1) & 3]);
+           }
+           if (gl < NX) vd[o * NXE + gl] += (acc[0] + acc[1]) + (acc[2] + acc[3]);
+           __syncwarp(gm);
+           if (gl == 0) { __threadfence_block(); rb[o] = iter; }
+         }
+         if (it == grp - 2) TR(7);
+         // fill the middle stage: vn_2j = d_2j + T_2j' vn_2j+1
+         if (o + 2 < N) wait_flag(rb + (o + 2), iter);
+         if (gl < NX) vd[2 * it * NXE + gl] += tmv(TD + (size_t)(2 * it) * TBLK, vd + (2 * it + 1) * NXE);
+         __syncwarp(gm);
+         if (it == grp - 2) TR(8);
+       } else if (it == 0) {  // stage 0 reads vn_1: the end of the chain
+         if (N > 1) wait_flag(rb + 1, iter);
        }
+       for (int k = item_hi(it); k >= item_lo(it); k--) stage_EA(k);
        pre_fwd(it);
        if (it == grp - 2) TR(9);
       }

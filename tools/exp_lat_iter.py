@@ -15,6 +15,7 @@ q, l, u = mdl.vectors(mpc.sample_x0(mdl, batch, bench.SEED), N)
 s = dict(bench.SETTINGS); s.update(max_iter=iters, eps_abs=1e-12, eps_rel=1e-12)
 gb = R.Batch(mdl, N, N, q, l, u, R.default_settings(**s))
 gb.set_tuning(lat_below=100000)
+if os.environ.get("LAT_LOCKSTEP"): gb.set_tuning(lat_lockstep=int(os.environ["LAT_LOCKSTEP"]))
 if knob != "lat_levels" and os.environ.get("LAT_LEVELS"): gb.set_tuning(lat_levels=int(os.environ["LAT_LEVELS"]))
 ref = None
 for rep in range(2):
