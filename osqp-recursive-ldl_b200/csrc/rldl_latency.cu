@@ -23,6 +23,11 @@
 //        D  (scan)      vn_k
 //        E  (parallel)  nu^d_k, v_k = e_k + Xinv_k F_k' Sinv_k vn_{k+1}, ADMM step
 //    (reference src/auxil.c:164-228, src/proj.c:4-14);
+//    The two recurrences run over a block tree (pairs of stages by default, deeper with the "lat_levels" knob): one
+//    group walks the chain of the widest nodes, the other groups fill in the stages behind it as soon as a per-position
+//    ready flag says their input is final.  With two lane groups per warp a warp owns an item (a pair of stages) and
+//    its groups take the two stages side by side ("lat_lockstep", default); timeline of one iteration and the
+//    variants measured on the way: profiles/r02_latency_kernel_timeline.txt, DESIGN.md section 3;
 //  * residuals / termination / rho adaptation (src/auxil.c:243-789) by one group every
 //    check_termination iterations, with the same device functions as the other kernels.
 //

@@ -176,7 +176,8 @@ def test_other_specialised_shapes_match_reference(nx, nu, monkeypatch):
 def test_latency_mode_block_tree_levels_match_reference(nx, nu, N):
     """The latency-mode kernel with 1..5 levels of the block tree under its sequential chain (tuning knob
     "lat_levels": 1 = pairs of stages, the default; deeper trees shorten the chain and add hops behind it), over
-    horizons with every shape of leftover (N - 1 = 1, 6, 11, 21, ...): each against the unmodified reference."""
+    horizons with every shape of leftover (N - 1 = 1, 6, 11, 21, ...), with lockstep items ("lat_lockstep") and
+    without: each against the unmodified reference."""
     from rldl_b200 import mpc
     batch = 12
     mdl = mpc.random_model(nx, nu, seed=500 + nx * 10 + nu)
@@ -184,11 +185,12 @@ def test_latency_mode_block_tree_levels_match_reference(nx, nu, N):
     res = ref_run(mdl, N, N, q, l, u, [("solve",), ("get",), ("dims",)])
     ref, (n, m) = res[1], res[2]
     gb = R.Batch(mdl, N, N, q, l, u, gpu_settings())
-    for lv in (1, 2, 3, 4, 5):
-        gb.set_tuning(lat_below=100000, lat_levels=lv)
-        assert gb.solve() == 0
-        bad = compare(gb.get(), ref, n, m)
-        assert not bad, (nx, nu, N, lv, bad[:5])
+    for lockstep in (1, 0):     # a warp per item (two lane groups per warp only) / a lane group per item
+        for lv in (1, 2, 3, 4, 5):
+            gb.set_tuning(lat_below=100000, lat_levels=lv, lat_lockstep=lockstep)
+            assert gb.solve() == 0
+            bad = compare(gb.get(), ref, n, m)
+            assert not bad, (nx, nu, N, lockstep, lv, bad[:5])
     gb.free()
 
 
