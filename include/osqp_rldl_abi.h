@@ -495,8 +495,8 @@ c_int rldl_batch_select_kernel(RLDLBatch *b, c_int which);
  *                 chain runs over pairs of stages; k = over runs of 2^k stages, with k - 1 more hops behind it;
  *                 1..6; measured neutral on B200)
  *   "lat_lockstep"  1 (default): in the latency-mode kernel a warp owns an item and its two lane groups take the two
- *                 stages of the item side by side (shapes with two lane groups per warp, 9 <= nx + nu <= 16; other
- *                 shapes ignore it); 0: a lane group per item, its stages one after the other
+ *                 stages of the item side by side (shapes with two or four lane groups per warp, nx + nu <= 16;
+ *                 wider shapes ignore it); 0: a lane group per item, its stages one after the other
  * value = -1 restores the default.  Returns 0, or 1 for an unknown name / invalid value. */
 c_int rldl_batch_set_tuning(RLDLBatch *b, const char *name, c_int value);
 /* statistics of the concurrent latency-mode lane in the last streaming launch (6 values): instances handed over,

@@ -25,7 +25,7 @@
 //    (reference src/auxil.c:164-228, src/proj.c:4-14);
 //    The two recurrences run over a block tree (pairs of stages by default, deeper with the "lat_levels" knob): one
 //    group walks the chain of the widest nodes, the other groups fill in the stages behind it as soon as a per-position
-//    ready flag says their input is final.  With two lane groups per warp a warp owns an item (a pair of stages) and
+//    ready flag says their input is final.  With two or four lane groups per warp a warp owns an item (a pair of stages) and
 //    its groups take the two stages side by side ("lat_lockstep", default); timeline of one iteration and the
 //    variants measured on the way: profiles/r02_latency_kernel_timeline.txt, DESIGN.md section 3;
 //  * residuals / termination / rho adaptation (src/auxil.c:243-789) by one group every
@@ -346,9 +346,12 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
   // groups take the two stages of the item side by side — the upper stage by group 0 of the warp, the lower one by
   // group 1 — so the groups of a warp are released together and never run diverged, and the item released last
   // costs one stage, not two.  Warp 0 keeps the scan.
-  const bool LK = (SH::GPW == 2) && B.lat_lockstep != 0;
+  // (With four lane groups per warp the groups 2 and 3 of a worker warp stay idle: the items of small shapes are
+  // fewer than the warps anyway.)
+  const bool LK = (SH::GPW >= 2) && B.lat_lockstep != 0;
   constexpr int NWK = kLatThreads / 32 - 1;
   auto half_stage = [&](int it) -> int {
+    if (gw >= 2) return -1;
     if (it == 0) return gw == 0 ? 0 : -1;
     if (it <= J) return gw == 0 ? 2 * it : 2 * it - 1;
     return gw == 0 ? N : (LEFT ? N - 1 : -1);
@@ -670,7 +673,7 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_admm_cta(ModelDev M, BatchDe
                 } else {
                   wait_flag(rf + e, iter);  // sp_2j from the chain
                 }
-              } else {  // the middle stage: sp_2j-1 = c_2j-1 + T_2j-1 sp_2j-2
+              } else if (gw == 1) {  // the middle stage: sp_2j-1 = c_2j-1 + T_2j-1 sp_2j-2
                 if (e > 2) wait_flag(rf + (e - 2), iter);
                 if (gl < NX) vc[(e - 1) * NXE + gl] += tmv(TB + (size_t)(e - 1) * TBLK, vc + (e - 2) * NXE);
               }
