@@ -208,7 +208,7 @@ def scenario_c1_scalar():
             "iterations": it, "parity": {"compared": 1, "status_mismatch": int(stv != r["status"][0]),
                                          "iter_mismatch": int(it != r["iter"][0]),
                                          "max_rel_obj": abs(obj - r["obj"][0]) / max(abs(r["obj"][0]), 1e-12)},
-            "note": "a batch of one is launch- and latency-bound on a GPU (one 512-thread CTA); the path is built for batches"}
+            "note": "a batch of one is launch- and latency-bound on a GPU (one 384-thread CTA); the path is built for batches"}
 
 
 def scenario_c2():

@@ -43,7 +43,7 @@
 
 namespace rldl {
 
-constexpr int kLatThreads = 512;
+constexpr int kLatThreads = 384;
 
 // nx x (nx+2) blocks of global scratch per CTA: T_k and T_k' per stage, the products of the block tree above
 // them (levels 1.., both forms) and the chain blocks in scan order (both forms)
