@@ -18,7 +18,7 @@
 //    (T_k is formed once per instance from the resident factor; the same matrix serves both
 //    sweeps by symmetry).  Phases per iteration:
 //        A  (parallel)  rhs build, a_k = Xinv_k r^v_k, c_k
-//        B  (scan)      sp_k                                   — one group, shuffles only
+//        B  (scan)      sp_k                                   — one group, operands by broadcast LDS.128
 //        C  (parallel)  e_k = a_k + Xinv_k (F_k' sp_k - J' sp_{k-1}),  d_k = e_k[0:nx]
 //        D  (scan)      vn_k
 //        E  (parallel)  nu^d_k, v_k = e_k + Xinv_k F_k' Sinv_k vn_{k+1}, ADMM step
@@ -77,7 +77,7 @@ struct LatLayout {  // shared-memory layout (doubles) of k_admm_cta for horizon 
     scr = vd + (N + 1) * SH::NXE;
     bar = scr + NG * SH::SC;
     ctl = bar + 2;
-    tring = ctl + 4;  // ctl: 4 ints (instance, leave flag, forward / backward scan progress) padded to 16 bytes
+    tring = ctl + 4;  // ctl: 4 ints (instance, leave flag, number of chain nodes, spare) padded to 16 bytes
     tbar = tring + NS * CH * TBLK;
     qs = tbar + NS + (NS & 1);
     red = qs + 3 * SH::A * SH::A;  // dense cost blocks padded to A x A (residuals)
